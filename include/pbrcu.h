@@ -1,0 +1,199 @@
+/* pbrcu.h -- the C-ABI boundary of the B200-native shading hot path (libpbrcu.so).
+ *
+ * The reference (WeaponizedSchizophrenia/physically-based-renderer) has no FFI layer: the path sits
+ * behind two C++ classes, pbr::PbrRenderSystem and pbr::TonemapperSystem, that RECORD Vulkan commands
+ * which run GLSL shaders.  Each entry point below replaces one recorded pass; the C++ facade in
+ * include/pbr/ (same class / method names as the reference) is a thin wrapper over this header.
+ *
+ *   pbrcu_lighting_blinnphong   <- PbrRenderSystem::recordLightingPass  (PbrRenderSystem.cpp:466-501)
+ *                                  running assets/shaders/pbr/lighting.glsl:19-29
+ *   pbrcu_tonemap_aces_gamma    <- TonemapperSystem::run                (TonemapperSystem.cpp:97-134)
+ *                                  running assets/shaders/tonemappers/aces+gamma.glsl:30-40
+ *   pbrcu_lighting_tonemap_fused<- the two above back to back (App.cpp:387-392) without the HDR trip
+ *   pbrcu_gbuffer_alloc/free    <- PbrRenderSystem::allocateGBuffer     (PbrRenderSystem.cpp:342-355,
+ *                                  GBuffer.cpp:41-95; formats GBuffer.hpp:13-16)
+ *   pbrcu_image_alloc/free      <- TonemapperSystem::allocateHdrImage   (TonemapperSystem.cpp:87-95)
+ *   pbrcu_frame_host            <- one App::renderAndPresent iteration (App.cpp:444-483) with host
+ *                                  buffers: upload, shade, tonemap, read back
+ * Tier B (north-star extension; the reference has no counterpart -- SURVEY.md section 0):
+ *   pbrcu_shade_ggx_ibl, pbrcu_cluster_lights, pbrcu_ibl_* (K3..K9)
+ *
+ * Conventions: every function is extern "C", returns 0 on success or a pbrcu_status (never throws);
+ * pbrcu_last_error() gives a thread-local message.  Device work is ENQUEUED on the given stream
+ * (a cudaStream_t passed as void*; NULL = the legacy default stream) and is asynchronous.  Buffers
+ * are caller-owned device memory unless the name ends in _host.  There is no CPU fallback: without
+ * a CUDA device every compute entry point fails with PBRCU_ERR_CUDA.
+ */
+#ifndef PBRCU_H
+#define PBRCU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden */
+#endif
+
+#define PBRCU_VERSION 100
+
+typedef enum {
+  PBRCU_OK = 0,
+  PBRCU_ERR_INVALID = 1, /* bad argument (NULL plane, misaligned pitch, empty rect outside image...) */
+  PBRCU_ERR_CUDA = 2,    /* a CUDA runtime call failed; see pbrcu_last_error() */
+  PBRCU_ERR_NOMEM = 3
+} pbrcu_status;
+
+typedef struct pbrcu_ctx pbrcu_ctx; /* device ordinal + SM count + scratch */
+typedef void* pbrcu_stream;         /* cudaStream_t */
+
+/* The reference G-buffer (GBuffer.hpp:13-16) as row-major device planes of 8-byte texels, plus the
+ * two Tier-B planes.  pitch8 = bytes per row of the 8-byte planes, pitch4 of the 4-byte planes. */
+typedef struct {
+  void* positions; /* R16G16B16A16_SFLOAT  world xyz, w = 0 */
+  void* normals;   /* R16G16B16A16_SFLOAT  unit world normal, w = 0; all-zero = cleared texel */
+  void* albedo;    /* R16G16B16A16_UNORM   base colour rgba */
+  float* depth;    /* D32_SFLOAT, optional (the lighting shader reads it into a dead variable) */
+  void* orm;       /* Tier B: R8G8B8A8_UNORM  R occlusion, G roughness, B metallic */
+  void* emissive;  /* Tier B: R16G16B16A16_SFLOAT */
+  uint32_t width, height;
+  size_t pitch8, pitch4;
+} pbrcu_gbuffer;
+
+typedef struct { uint32_t x0, y0, w, h; } pbrcu_rect; /* tile to shade; w = h = 0 means whole image */
+
+/* ---- context, memory, streams -------------------------------------------------------------- */
+int pbrcu_version(void);
+const char* pbrcu_last_error(void);
+int pbrcu_device_count(int* out);
+int pbrcu_ctx_create(int device, pbrcu_ctx** out);
+void pbrcu_ctx_destroy(pbrcu_ctx* ctx);
+int pbrcu_ctx_sm_count(const pbrcu_ctx* ctx);
+int pbrcu_malloc(pbrcu_ctx* ctx, size_t bytes, void** out);
+int pbrcu_free(pbrcu_ctx* ctx, void* ptr);
+int pbrcu_host_alloc(size_t bytes, void** out); /* pinned */
+int pbrcu_host_free(void* ptr);
+int pbrcu_memcpy_h2d(void* dst, const void* src, size_t bytes, pbrcu_stream s);
+int pbrcu_memcpy_d2h(void* dst, const void* src, size_t bytes, pbrcu_stream s);
+int pbrcu_memset(void* dst, int value, size_t bytes, pbrcu_stream s);
+int pbrcu_stream_create(pbrcu_stream* out);
+int pbrcu_stream_destroy(pbrcu_stream s);
+int pbrcu_stream_synchronize(pbrcu_stream s);
+/* CUDA-event timing on stream s around whatever the caller enqueues between start and stop */
+int pbrcu_timer_create(void** out);
+int pbrcu_timer_destroy(void* t);
+int pbrcu_timer_start(void* t, pbrcu_stream s);
+int pbrcu_timer_stop(void* t, pbrcu_stream s);
+int pbrcu_timer_elapsed_ms(void* t, float* ms); /* synchronises on the stop event */
+
+/* tier 0: reference planes only; tier 1: + orm + emissive.  Cleared like the reference
+ * (PbrRenderSystem.cpp:370-415): colour planes 0, depth 1.0. */
+int pbrcu_gbuffer_alloc(pbrcu_ctx* ctx, uint32_t w, uint32_t h, int tier, pbrcu_gbuffer* out);
+int pbrcu_gbuffer_free(pbrcu_ctx* ctx, pbrcu_gbuffer* g);
+int pbrcu_gbuffer_clear(const pbrcu_gbuffer* g, pbrcu_stream s);
+/* a pitched image of `texel_bytes`-byte texels (8: RGBA16F HDR target, 4: RGBA8 LDR output) */
+int pbrcu_image_alloc(pbrcu_ctx* ctx, uint32_t w, uint32_t h, uint32_t texel_bytes, void** out,
+                      size_t* pitch);
+
+/* ---- Tier A: the reference's passes -------------------------------------------------------- */
+/* K1: out = albedo * max(N.V,0) + max(N.H,0)^64 with L = V = normalize(cam - P), RGBA16F out. */
+int pbrcu_lighting_blinnphong(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                              pbrcu_rect rect, void* out_rgba16f, size_t out_pitch, pbrcu_stream s);
+/* K2: RGBA16F -> ACES fit (matrices column-major as written) -> gamma 2.2 -> clamp -> RGBA8. */
+int pbrcu_tonemap_aces_gamma(pbrcu_ctx* ctx, const void* hdr_rgba16f, size_t hdr_pitch,
+                             uint32_t width, uint32_t height, pbrcu_rect rect, void* out_rgba8,
+                             size_t out_pitch, pbrcu_stream s);
+/* K1+K2 in one pass; the tonemapper sees the fp16-ROUNDED lighting value exactly as it would after
+ * the HDR round trip.  out_rgba16f may be NULL (LDR only: 28 B/px instead of 36). */
+int pbrcu_lighting_tonemap_fused(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                                 pbrcu_rect rect, void* out_rgba16f, size_t hdr_pitch,
+                                 void* out_rgba8, size_t ldr_pitch, pbrcu_stream s);
+/* Batched multi-view (BASELINE config 5): n_views G-buffers of identical shape laid out
+ * `view_stride8` / `view_stride4` bytes apart starting at g[0]'s planes; one camera per view. */
+int pbrcu_lighting_blinnphong_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8,
+                                      size_t view_stride4, uint32_t n_views,
+                                      const float* cam_pos_xyz /* host, n_views*3 */,
+                                      void* out_rgba16f, size_t out_pitch, size_t out_view_stride,
+                                      pbrcu_stream s);
+/* One frame through HOST buffers (the end-to-end path): H2D of the three planes, K1 (+K2), D2H of
+ * the HDR and/or LDR result.  Host pointers should be pinned (pbrcu_host_alloc) for full PCIe rate.
+ * hdr_out_host / ldr_out_host may each be NULL.  Synchronises the stream before returning. */
+int pbrcu_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,
+                     const void* albedo_host, uint32_t width, uint32_t height,
+                     const float cam_pos[3], void* hdr_out_host, void* ldr_out_host, pbrcu_stream s);
+
+/* ---- Tier B: GGX + point lights + IBL (no reference counterpart) ---------------------------- */
+typedef struct {
+  float px, py, pz, range; /* range <= 0: unlimited */
+  float r, g, b, intensity;
+} pbrcu_light;
+
+/* cube chain layout: for mip: for face (+X,-X,+Y,-Y,+Z,-Z): row-major (res>>mip)^2 RGBA16F */
+typedef struct {
+  const void* irradiance; uint32_t irr_res;                       /* 6*irr_res^2 RGBA16F (E/pi) */
+  const void* prefiltered; uint32_t pref_res; uint32_t pref_mips; /* GGX-prefiltered chain */
+  const float* lut; uint32_t lut_res;                             /* split-sum RG32F */
+} pbrcu_ibl;
+
+/* tile light lists built by pbrcu_cluster_lights: tiles of PBRCU_TILE x PBRCU_TILE pixels */
+#define PBRCU_TILE 16
+typedef struct {
+  uint32_t* counts;  /* tiles_x*tiles_y */
+  uint16_t* indices; /* tiles_x*tiles_y*max_per_tile, ascending light index */
+  uint32_t tiles_x, tiles_y, max_per_tile;
+} pbrcu_light_tiles;
+
+size_t pbrcu_cube_chain_texels(uint32_t base_res, uint32_t nmips);
+size_t pbrcu_cube_mip_offset(uint32_t base_res, uint32_t mip); /* texels */
+
+/* K3: lights = device array of n_lights pbrcu_light; tiles may be NULL (every pixel loops all
+ * lights); ibl may be NULL (direct light + emissive only). */
+int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                        const pbrcu_light* lights_dev, uint32_t n_lights,
+                        const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
+                        void* out_rgba16f, size_t out_pitch, pbrcu_stream s);
+/* K3c: per 16x16 tile, the lights whose range sphere meets the tile's world-space position AABB */
+int pbrcu_light_tiles_alloc(pbrcu_ctx* ctx, uint32_t width, uint32_t height, uint32_t max_per_tile,
+                            pbrcu_light_tiles* out);
+int pbrcu_light_tiles_free(pbrcu_ctx* ctx, pbrcu_light_tiles* t);
+int pbrcu_cluster_lights(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const pbrcu_light* lights_dev,
+                         uint32_t n_lights, const pbrcu_light_tiles* tiles, pbrcu_stream s);
+
+/* K9: xi_i = (i/n, radical_inverse(i)) as float2, bit-exact vs the oracle */
+int pbrcu_ibl_hammersley(pbrcu_ctx* ctx, uint32_t n, float* out_xy_dev, pbrcu_stream s);
+/* K8: split-sum LUT, res*res RG32F, bit-exact vs the oracle */
+int pbrcu_ibl_brdf_lut(pbrcu_ctx* ctx, uint32_t res, uint32_t nsamples, float* out_rg_dev,
+                       pbrcu_stream s);
+/* K4: lat-long RGBA32F -> cube base level (6*res^2 RGBA16F) */
+int pbrcu_ibl_equirect_to_cube(pbrcu_ctx* ctx, const float* src_rgba32f_dev, uint32_t sw, uint32_t sh,
+                               uint32_t res, void* out_base_dev, pbrcu_stream s);
+/* K5: 2x2 box mip chain in place (levels 1..nmips-1 from level 0), bit-exact vs the oracle.
+ * face_row0/face_rows select a band of base-level rows per face for sharding (0,0 = everything). */
+int pbrcu_ibl_cube_mipgen(pbrcu_ctx* ctx, void* chain_dev, uint32_t base_res, uint32_t nmips,
+                          pbrcu_stream s);
+/* K7: GGX prefilter of levels [first_mip,last_mip] (level 0 = copy), nsamples per texel.
+ * shard/nshards split each level's texels into contiguous blocks for multi-GPU (0,1 = all). */
+int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res,
+                            uint32_t nmips, uint32_t nsamples, void* dst_chain_dev,
+                            uint32_t first_mip, uint32_t last_mip, uint32_t shard, uint32_t nshards,
+                            pbrcu_stream s);
+/* K6: cosine-weighted irradiance (E/pi), 6*res^2 RGBA16F */
+int pbrcu_ibl_irradiance(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
+                         uint32_t res, uint32_t nsamples, void* out_dev, pbrcu_stream s);
+
+/* ---- synthetic inputs for benchmarks (generated on the device; never timed) ------------------ */
+/* kind 0 = gbuf_noise (every texel a hit, no coherence), 1 = gbuf_spheres (ray-cast spheres + plane,
+ * ~25 % cleared background).  Fills every plane the G-buffer has. */
+int pbrcu_synth_gbuffer(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, int kind, uint64_t seed,
+                        const float cam_pos[3], const float cam_target[3], pbrcu_stream s);
+int pbrcu_synth_environment(pbrcu_ctx* ctx, float* equirect_rgba32f_dev, uint32_t sw, uint32_t sh,
+                            uint64_t seed, pbrcu_stream s);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* PBRCU_H */

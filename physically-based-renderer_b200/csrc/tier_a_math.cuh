@@ -1,0 +1,71 @@
+// tier_a_math.cuh -- per-texel device math of the reference's two passes.
+//   blinnphong_texel : assets/shaders/pbr/lighting.glsl:19-29 + BlinnPhong.lib.glsl:4-10
+//   tonemap_texel    : assets/shaders/tonemappers/aces+gamma.glsl:10-40 + Gamma.lib.glsl:4-6
+// All arithmetic fp32; one RNE rounding at each store (fp16 / unorm8).
+#pragma once
+#include "common.cuh"
+
+namespace pbrcu {
+
+struct F4 { float x, y, z, w; };
+
+// lighting.glsl:19-29.  pos/nrm: RGBA16F texel (two packed half2 words); alb: RGBA16_UNORM texel.
+// With L = V (:26), H = normalize(V+V); the shader's operation order is kept so NaN propagation for
+// normalize(0) (cleared texel seen from a camera at the origin) ends in max(NaN,0) = 0 like the
+// oracle: fmaxf is IEEE maxNum.
+__device__ __forceinline__ F4 blinnphong_texel(uint2 pos, uint2 nrm, uint2 alb, float cx, float cy,
+                                               float cz) {
+  float2 pxy = h2_to_f2(pos.x), pzw = h2_to_f2(pos.y);
+  float2 nxy = h2_to_f2(nrm.x), nzw = h2_to_f2(nrm.y);
+  float dx = cx - pxy.x, dy = cy - pxy.y, dz = cz - pzw.x;
+  float inv = rsqrtf(dx * dx + dy * dy + dz * dz);                 // :25 normalize(cam - P)
+  float vx = dx * inv, vy = dy * inv, vz = dz * inv;
+  float ndv = fmaxf(nxy.x * vx + nxy.y * vy + nzw.x * vz, 0.0f);   // BlinnPhong.lib.glsl:5
+  float hx = vx + vx, hy = vy + vy, hz = vz + vz;                  // :6 H = normalize(V + L)
+  float hinv = rsqrtf(hx * hx + hy * hy + hz * hz);
+  hx *= hinv; hy *= hinv; hz *= hinv;
+  float ndh = fmaxf(nxy.x * hx + nxy.y * hy + nzw.x * hz, 0.0f);   // :7
+  float s = ndh * ndh;                                             // :8 pow(NdotH, 64) = 6 squarings
+  s *= s; s *= s; s *= s; s *= s; s *= s;
+  F4 o;                                                            // :9 all four channels
+  o.x = unorm16_lo(alb.x) * ndv + s;
+  o.y = unorm16_hi(alb.x) * ndv + s;
+  o.z = unorm16_lo(alb.y) * ndv + s;
+  o.w = unorm16_hi(alb.y) * ndv + s;
+  return o;
+}
+
+__device__ __forceinline__ uint2 pack_rgba16f(F4 c) {
+  return make_uint2(f2_to_h2(c.x, c.y), f2_to_h2(c.z, c.w));
+}
+__device__ __forceinline__ F4 unpack_rgba16f(uint2 t) {
+  float2 a = h2_to_f2(t.x), b = h2_to_f2(t.y);
+  return F4{a.x, a.y, b.x, b.y};
+}
+
+// aces+gamma.glsl:20-24
+__device__ __forceinline__ float rrt_odt_fit(float c) {
+  float num = c * (c + 0.0245786f) - 0.000090537f;
+  float den = c * (0.983729f * c + 0.4329510f) + 0.238081f;
+  return __fdividef(num, den);
+}
+// Gamma.lib.glsl:4-6 with the pinned negative-base behaviour: pow(max(x,0), 1/2.2).
+// x = 0 -> lg2 = -inf -> ex2(-inf) = 0.
+__device__ __forceinline__ float gamma22(float x) {
+  return exp2f(__log2f(fmaxf(x, 0.0f)) * (1.0f / 2.2f));
+}
+// aces+gamma.glsl:30-40.  mat3x3(a,b,c,d,e,f,g,h,i) fills COLUMNS: (M v).x = a v.x + d v.y + g v.z.
+__device__ __forceinline__ uint32_t tonemap_texel(F4 hdr) {
+  float ax = 0.59719f * hdr.x + 0.07600f * hdr.y + 0.02840f * hdr.z;
+  float ay = 0.35458f * hdr.x + 0.90834f * hdr.y + 0.13383f * hdr.z;
+  float az = 0.04823f * hdr.x + 0.01566f * hdr.y + 0.83777f * hdr.z;
+  float fx = rrt_odt_fit(ax), fy = rrt_odt_fit(ay), fz = rrt_odt_fit(az);
+  float ox = 1.60475f * fx + -0.10208f * fy + -0.00327f * fz;
+  float oy = -0.53108f * fx + 1.10813f * fy + -0.07276f * fz;
+  float oz = -0.07367f * fx + -0.00605f * fy + 1.07602f * fz;
+  uint32_t r = to_unorm8(gamma22(ox)), g = to_unorm8(gamma22(oy)), b = to_unorm8(gamma22(oz));
+  uint32_t a = to_unorm8(hdr.w);
+  return r | (g << 8) | (b << 16) | (a << 24);
+}
+
+}  // namespace pbrcu
