@@ -1,0 +1,310 @@
+// shade_ggx.cu -- K3 metallic-roughness Cook-Torrance shading (GGX D, height-correlated Smith V,
+// Schlick F) with point lights, occlusion, emissive and split-sum IBL over the extended G-buffer, and
+// K3c the per-tile light lists.  No reference counterpart; definition:
+// oracle/pbr_oracle_ibl.c:pbro_shade_pixel (glTF 2.0 Appendix B, KHR_lights_punctual, Karis 2013).
+//
+// One CTA = one 16x16 pixel tile (persistent loop over tiles): a warp reads two 128-byte row segments
+// per plane, the tile's light list is staged once in shared memory, and the IBL fetches of
+// neighbouring pixels hit the same L1 lines.
+#include "cube.cuh"
+
+namespace pbrcu {
+
+constexpr int kTile = PBRCU_TILE;
+constexpr int kShadeThreads = kTile * kTile;
+constexpr int kMaxSmemLights = 1024;
+constexpr float kInvPi = 0.31830988618379067154f;
+
+struct ShadeParams {
+  const uint8_t *pos, *nrm, *alb, *orm, *emi;
+  uint8_t* out;
+  size_t pitch8, pitch4, out_pitch;
+  uint32_t x0, y0, x1, y1;        // rect in image coordinates (x1, y1 exclusive)
+  uint32_t tx0, ty0, ntx, nty;    // tile range covering the rect
+  float cx, cy, cz;
+  const pbrcu_light* lights;
+  uint32_t n_lights;
+  const uint32_t* tile_counts;    // NULL: every pixel loops all lights
+  const uint16_t* tile_indices;
+  uint32_t tiles_x, max_per_tile;
+  int has_ibl;
+  CubeChain irr, pref;
+  const float2* lut;
+  uint32_t lut_res;
+};
+
+__device__ __forceinline__ float2 lut_sample(const float2* lut, int res, float u, float v) {
+  const float fx = u * float(res) - 0.5f, fy = v * float(res) - 0.5f;
+  const float x0f = floorf(fx), y0f = floorf(fy);
+  const float tx = fx - x0f, ty = fy - y0f;
+  const int hi = res - 1;
+  const int x0 = min(max(int(x0f), 0), hi), x1 = min(max(int(x0f) + 1, 0), hi);
+  const int y0 = min(max(int(y0f), 0), hi), y1 = min(max(int(y0f) + 1, 0), hi);
+  const float2 t00 = __ldg(lut + y0 * res + x0), t10 = __ldg(lut + y0 * res + x1);
+  const float2 t01 = __ldg(lut + y1 * res + x0), t11 = __ldg(lut + y1 * res + x1);
+  return make_float2(lerpf(lerpf(t00.x, t10.x, tx), lerpf(t01.x, t11.x, tx), ty),
+                     lerpf(lerpf(t00.y, t10.y, tx), lerpf(t01.y, t11.y, tx), ty));
+}
+
+__device__ __forceinline__ float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
+
+__global__ void __launch_bounds__(kShadeThreads) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
+  __shared__ float4 s_light[kMaxSmemLights * 2];  // {px,py,pz,range}, {r,g,b,intensity}
+  __shared__ uint32_t s_count;
+  const int lx = threadIdx.x % kTile, ly = threadIdx.x / kTile;
+  const uint32_t ntiles = p.ntx * p.nty;
+  const bool stage_all = (p.tile_counts == nullptr) && p.n_lights <= kMaxSmemLights;
+  if (stage_all) {
+    for (uint32_t i = threadIdx.x; i < p.n_lights * 2; i += kShadeThreads)
+      s_light[i] = __ldg(reinterpret_cast<const float4*>(p.lights) + i);
+    if (threadIdx.x == 0) s_count = p.n_lights;
+    __syncthreads();
+  }
+  for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const uint32_t tx = p.tx0 + t % p.ntx, ty = p.ty0 + t / p.ntx;
+    if (p.tile_counts != nullptr) {  // stage this tile's light list
+      __syncthreads();
+      const uint32_t tile = ty * p.tiles_x + tx;
+      const uint32_t cnt = min(__ldg(p.tile_counts + tile), min(p.max_per_tile, uint32_t(kMaxSmemLights)));
+      const uint16_t* idx = p.tile_indices + size_t(tile) * p.max_per_tile;
+      for (uint32_t i = threadIdx.x; i < cnt * 2; i += kShadeThreads) {
+        const uint32_t li = __ldg(idx + (i >> 1));
+        s_light[i] = __ldg(reinterpret_cast<const float4*>(p.lights) + li * 2 + (i & 1));
+      }
+      if (threadIdx.x == 0) s_count = cnt;
+      __syncthreads();
+    }
+    const uint32_t x = tx * kTile + lx, y = ty * kTile + ly;
+    if (x < p.x0 || x >= p.x1 || y < p.y0 || y >= p.y1) continue;
+    const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8;
+    const uint2 tp = ldg_stream8(p.pos + o8), tn = ldg_stream8(p.nrm + o8), ta = ldg_stream8(p.alb + o8);
+    const uint2 te = ldg_stream8(p.emi + o8);
+    const uint32_t to = ldg_stream4(p.orm + size_t(y) * p.pitch4 + size_t(x) * 4);
+    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8;
+
+    const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
+    if (nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f) {  // cleared (background) texel
+      stg_stream8(outp, make_uint2(0u, 0u));
+      continue;
+    }
+    const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
+    const float3 P = make_float3(pxy.x, pxy.y, pzw.x);
+    const float3 N = normalize3(make_float3(nxy.x, nxy.y, nzw.x));
+    const float3 V = normalize3(make_float3(p.cx - P.x, p.cy - P.y, p.cz - P.z));
+    const float NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
+    const float NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
+    const float base_r = unorm16_lo(ta.x), base_g = unorm16_hi(ta.x), base_b = unorm16_lo(ta.y), base_a = unorm16_hi(ta.y);
+    const float occ = float(to & 0xFFu) * (1.0f / 255.0f);
+    const float rough = fminf(fmaxf(float((to >> 8) & 0xFFu) * (1.0f / 255.0f), 0.045f), 1.0f);
+    const float metal = float((to >> 16) & 0xFFu) * (1.0f / 255.0f);
+    const float omm = 1.0f - metal;
+    const float F0r = 0.04f * omm + base_r * metal, F0g = 0.04f * omm + base_g * metal, F0b = 0.04f * omm + base_b * metal;
+    const float cdr = base_r * omm, cdg = base_g * omm, cdb = base_b * omm;
+    const float alpha = rough * rough, a2 = alpha * alpha, oma2 = 1.0f - a2;
+    const float visV = sqrtf(NoV * NoV * oma2 + a2);
+    float Lr = 0.f, Lg = 0.f, Lb = 0.f;
+
+    const uint32_t nl = (stage_all || p.tile_counts) ? s_count : p.n_lights;
+    for (uint32_t i = 0; i < nl; ++i) {
+      float4 la, lb;
+      if (stage_all || p.tile_counts) { la = s_light[2 * i]; lb = s_light[2 * i + 1]; }
+      else { la = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * i); lb = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * i + 1); }
+      const float dx = la.x - P.x, dy = la.y - P.y, dz = la.z - P.z;
+      const float d2 = dx * dx + dy * dy + dz * dz;
+      const float invd = rsqrtf(d2);
+      const float ldx = dx * invd, ldy = dy * invd, ldz = dz * invd;
+      const float NoL = clamp01(N.x * ldx + N.y * ldy + N.z * ldz);
+      float att = __fdividef(1.0f, fmaxf(d2, 1e-8f));
+      if (la.w > 0.0f) {  // KHR_lights_punctual range window: clamp(1 - (d/range)^4, 0, 1)
+        const float q = __fdividef(d2, la.w * la.w);
+        att *= clamp01(1.0f - q * q);
+      }
+      if (NoL > 0.0f && att > 0.0f) {
+        float hx = V.x + ldx, hy = V.y + ldy, hz = V.z + ldz;
+        const float hinv = rsqrtf(hx * hx + hy * hy + hz * hz);
+        hx *= hinv; hy *= hinv; hz *= hinv;
+        const float NoH = clamp01(N.x * hx + N.y * hy + N.z * hz);
+        const float VoH = clamp01(V.x * hx + V.y * hy + V.z * hz);
+        const float dd = NoH * NoH * (a2 - 1.0f) + 1.0f;
+        const float D = __fdividef(a2, 3.14159265358979f * dd * dd);
+        const float vis = __fdividef(0.5f, NoL * visV + NoV * sqrtf(NoL * NoL * oma2 + a2));
+        const float tt = 1.0f - VoH, t2 = tt * tt, fc = t2 * t2 * tt;
+        const float sc = lb.w * att * NoL, dv = D * vis;
+        const float Fr = F0r + (1.0f - F0r) * fc, Fg = F0g + (1.0f - F0g) * fc, Fb = F0b + (1.0f - F0b) * fc;
+        Lr += ((1.0f - Fr) * cdr * kInvPi + Fr * dv) * (lb.x * sc);
+        Lg += ((1.0f - Fg) * cdg * kInvPi + Fg * dv) * (lb.y * sc);
+        Lb += ((1.0f - Fb) * cdb * kInvPi + Fb * dv) * (lb.z * sc);
+      }
+    }
+    if (p.has_ibl) {
+      const float3 R = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
+      const RGB irr = cube_sample(p.irr, N, 0.0f);
+      const RGB pre = cube_sample(p.pref, R, rough * float(p.pref.nmips - 1));
+      const float2 ab = lut_sample(p.lut, int(p.lut_res), NoV, rough);
+      Lr += (irr.r * cdr + pre.r * (F0r * ab.x + ab.y)) * occ;
+      Lg += (irr.g * cdg + pre.g * (F0g * ab.x + ab.y)) * occ;
+      Lb += (irr.b * cdb + pre.b * (F0b * ab.x + ab.y)) * occ;
+    }
+    const float2 exy = h2_to_f2(te.x), ezw = h2_to_f2(te.y);
+    Lr = fminf(Lr + exy.x, 65504.0f); Lg = fminf(Lg + exy.y, 65504.0f); Lb = fminf(Lb + ezw.x, 65504.0f);
+    stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+  }
+}
+
+// ---- K3c: per 16x16 tile, world-space AABB of the tile's non-cleared positions, then every light
+// whose range sphere meets it, in ascending light index (so K3 sums in the oracle's order).
+__global__ void __launch_bounds__(kShadeThreads) cluster_lights_kernel(
+    const uint8_t* pos, const uint8_t* nrm, size_t pitch8, uint32_t width, uint32_t height,
+    const pbrcu_light* lights, uint32_t n_lights, uint32_t* counts, uint16_t* indices, uint32_t tiles_x,
+    uint32_t max_per_tile) {
+  __shared__ float s_min[3][kShadeThreads / 32], s_max[3][kShadeThreads / 32];
+  __shared__ float s_box[6];
+  __shared__ uint32_t s_warp_cnt[kShadeThreads / 32];
+  __shared__ uint32_t s_base;
+  const uint32_t tile = blockIdx.y * tiles_x + blockIdx.x;
+  const uint32_t x = blockIdx.x * kTile + threadIdx.x % kTile, y = blockIdx.y * kTile + threadIdx.x / kTile;
+  float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+  if (x < width && y < height) {
+    const size_t o8 = size_t(y) * pitch8 + size_t(x) * 8;
+    const uint2 tn = __ldg(reinterpret_cast<const uint2*>(nrm + o8));
+    const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
+    if (!(nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f)) {
+      const uint2 tp = __ldg(reinterpret_cast<const uint2*>(pos + o8));
+      const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
+      mn[0] = mx[0] = pxy.x; mn[1] = mx[1] = pxy.y; mn[2] = mx[2] = pzw.x;
+    }
+  }
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      mn[c] = fminf(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], off));
+      mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], off));
+    }
+    if (lane == 0) { s_min[c][warp] = mn[c]; s_max[c][warp] = mx[c]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    float a = s_min[threadIdx.x][0], b = s_max[threadIdx.x][0];
+    for (int w = 1; w < kShadeThreads / 32; ++w) { a = fminf(a, s_min[threadIdx.x][w]); b = fmaxf(b, s_max[threadIdx.x][w]); }
+    s_box[threadIdx.x] = a; s_box[3 + threadIdx.x] = b;
+  }
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  const bool empty = s_box[0] > s_box[3];
+  for (uint32_t base = 0; base < n_lights; base += kShadeThreads) {
+    const uint32_t i = base + threadIdx.x;
+    bool hit = false;
+    if (i < n_lights && !empty) {
+      const float4 la = __ldg(reinterpret_cast<const float4*>(lights) + 2 * i);
+      if (la.w <= 0.0f) hit = true;  // unlimited range
+      else {
+        // fp16 positions are exact in fp32; widen the sphere by 1 ulp-ish so K3's window (which is
+        // exactly 0 at d >= range) can never see a light this test dropped
+        const float ddx = fmaxf(fmaxf(s_box[0] - la.x, la.x - s_box[3]), 0.0f);
+        const float ddy = fmaxf(fmaxf(s_box[1] - la.y, la.y - s_box[4]), 0.0f);
+        const float ddz = fmaxf(fmaxf(s_box[2] - la.z, la.z - s_box[5]), 0.0f);
+        hit = ddx * ddx + ddy * ddy + ddz * ddz <= la.w * la.w * 1.0001f;
+      }
+    }
+    // ordered compaction: ballot within the warp, prefix over the 8 warps
+    const uint32_t ballot = __ballot_sync(0xffffffffu, hit);
+    if (lane == 0) s_warp_cnt[warp] = __popc(ballot);
+    __syncthreads();
+    uint32_t before = s_base;
+    for (int w = 0; w < warp; ++w) before += s_warp_cnt[w];
+    const uint32_t slot = before + __popc(ballot & ((1u << lane) - 1u));
+    if (hit && slot < max_per_tile) indices[size_t(tile) * max_per_tile + slot] = uint16_t(i);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t tot = 0;
+      for (int w = 0; w < kShadeThreads / 32; ++w) tot += s_warp_cnt[w];
+      s_base += tot;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) counts[tile] = min(s_base, max_per_tile);
+}
+
+}  // namespace pbrcu
+
+using namespace pbrcu;
+
+extern "C" int pbrcu_light_tiles_alloc(pbrcu_ctx* ctx, uint32_t width, uint32_t height, uint32_t max_per_tile,
+                                       pbrcu_light_tiles* out) {
+  PBRCU_REQUIRE(ctx && out, "NULL argument");
+  PBRCU_REQUIRE(width > 0 && height > 0 && max_per_tile > 0 && max_per_tile <= uint32_t(kMaxSmemLights), "extent or max_per_tile out of range");
+  out->tiles_x = (width + kTile - 1) / kTile;
+  out->tiles_y = (height + kTile - 1) / kTile;
+  out->max_per_tile = max_per_tile;
+  out->counts = nullptr; out->indices = nullptr;
+  const size_t nt = size_t(out->tiles_x) * out->tiles_y;
+  int rc;
+  if ((rc = pbrcu_malloc(ctx, nt * 4, reinterpret_cast<void**>(&out->counts)))) return rc;
+  if ((rc = pbrcu_malloc(ctx, nt * max_per_tile * 2, reinterpret_cast<void**>(&out->indices)))) { pbrcu_free(ctx, out->counts); out->counts = nullptr; return rc; }
+  return PBRCU_OK;
+}
+
+extern "C" int pbrcu_light_tiles_free(pbrcu_ctx* ctx, pbrcu_light_tiles* t) {
+  if (!t) return PBRCU_OK;
+  pbrcu_free(ctx, t->counts);
+  pbrcu_free(ctx, t->indices);
+  t->counts = nullptr; t->indices = nullptr;
+  return PBRCU_OK;
+}
+
+extern "C" int pbrcu_cluster_lights(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const pbrcu_light* lights_dev, uint32_t n_lights,
+                                    const pbrcu_light_tiles* tiles, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && g && tiles && tiles->counts && tiles->indices, "NULL argument");
+  PBRCU_REQUIRE(g->positions && g->normals, "gbuffer plane is NULL");
+  PBRCU_REQUIRE(n_lights <= 65535 && (n_lights == 0 || lights_dev), "n_lights out of range or lights NULL");
+  PBRCU_REQUIRE(tiles->tiles_x == (g->width + kTile - 1) / kTile && tiles->tiles_y == (g->height + kTile - 1) / kTile, "tile grid does not match the gbuffer");
+  dim3 grid(tiles->tiles_x, tiles->tiles_y);
+  cluster_lights_kernel<<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(
+      static_cast<const uint8_t*>(g->positions), static_cast<const uint8_t*>(g->normals), g->pitch8, g->width, g->height,
+      lights_dev, n_lights, tiles->counts, tiles->indices, tiles->tiles_x, tiles->max_per_tile);
+  return launch_check("cluster_lights_kernel");
+}
+
+extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                                   const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
+                                   const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && g && cam_pos && out_rgba16f, "NULL argument");
+  PBRCU_REQUIRE(g->positions && g->normals && g->albedo && g->orm && g->emissive, "gbuffer plane is NULL (K3 needs the tier-1 planes)");
+  PBRCU_REQUIRE(g->pitch8 >= size_t(g->width) * 8 && g->pitch8 % 8 == 0 && g->pitch4 >= size_t(g->width) * 4 && g->pitch4 % 4 == 0, "bad gbuffer pitch");
+  PBRCU_REQUIRE(out_pitch >= size_t(g->width) * 8 && out_pitch % 8 == 0, "out_pitch too small or not a multiple of 8");
+  PBRCU_REQUIRE(n_lights <= 65535 && (n_lights == 0 || lights_dev), "n_lights out of range or lights NULL");
+  if (rect.w == 0 && rect.h == 0) rect = pbrcu_rect{0, 0, g->width, g->height};
+  PBRCU_REQUIRE(uint64_t(rect.x0) + rect.w <= g->width && uint64_t(rect.y0) + rect.h <= g->height, "rect outside the image");
+  if (rect.w == 0 || rect.h == 0) return PBRCU_OK;
+  ShadeParams p{};
+  p.pos = static_cast<const uint8_t*>(g->positions); p.nrm = static_cast<const uint8_t*>(g->normals);
+  p.alb = static_cast<const uint8_t*>(g->albedo); p.orm = static_cast<const uint8_t*>(g->orm);
+  p.emi = static_cast<const uint8_t*>(g->emissive); p.out = static_cast<uint8_t*>(out_rgba16f);
+  p.pitch8 = g->pitch8; p.pitch4 = g->pitch4; p.out_pitch = out_pitch;
+  p.x0 = rect.x0; p.y0 = rect.y0; p.x1 = rect.x0 + rect.w; p.y1 = rect.y0 + rect.h;
+  p.tx0 = rect.x0 / kTile; p.ty0 = rect.y0 / kTile;
+  p.ntx = (p.x1 + kTile - 1) / kTile - p.tx0; p.nty = (p.y1 + kTile - 1) / kTile - p.ty0;
+  p.cx = cam_pos[0]; p.cy = cam_pos[1]; p.cz = cam_pos[2];
+  p.lights = lights_dev; p.n_lights = n_lights;
+  if (tiles) {
+    PBRCU_REQUIRE(tiles->counts && tiles->indices, "light tiles not allocated");
+    PBRCU_REQUIRE(tiles->tiles_x == (g->width + kTile - 1) / kTile && tiles->tiles_y == (g->height + kTile - 1) / kTile, "tile grid does not match the gbuffer");
+    p.tile_counts = tiles->counts; p.tile_indices = tiles->indices; p.tiles_x = tiles->tiles_x; p.max_per_tile = tiles->max_per_tile;
+  }
+  if (ibl) {
+    PBRCU_REQUIRE(ibl->irradiance && ibl->prefiltered && ibl->lut, "ibl texture is NULL");
+    PBRCU_REQUIRE(ibl->irr_res > 0 && ibl->pref_res > 0 && ibl->pref_mips >= 1 && ibl->pref_mips <= 16 && (ibl->pref_res >> (ibl->pref_mips - 1)) >= 1 && ibl->lut_res > 0, "bad ibl shape");
+    p.has_ibl = 1;
+    p.irr = make_chain(ibl->irradiance, ibl->irr_res, 1);
+    p.pref = make_chain(ibl->prefiltered, ibl->pref_res, ibl->pref_mips);
+    p.lut = reinterpret_cast<const float2*>(ibl->lut);
+    p.lut_res = ibl->lut_res;
+  }
+  const uint32_t ntiles = p.ntx * p.nty;
+  uint32_t grid = uint32_t(ctx->sm_count) * 4;
+  if (grid > ntiles) grid = ntiles;
+  shade_ggx_kernel<<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
+  return launch_check("shade_ggx_kernel");
+}
