@@ -28,9 +28,8 @@ constexpr int kThreads = 256;
 constexpr int kUnroll = 2;  // independent texel PAIRS per thread per iteration
 
 template <int MODE>
-__device__ __forceinline__ void process_pair(const TierAParams& p, uint4 a, uint4 b, uint4 c,
-                                             size_t hdr_off, size_t ldr_off, float cx, float cy,
-                                             float cz) {
+__device__ __forceinline__ void process_pair(uint8_t* hdr, uint8_t* ldr, uint4 a, uint4 b, uint4 c,
+                                             float cx, float cy, float cz) {
   F4 c0, c1;
   if (MODE == MODE_TONEMAP) {
     c0 = unpack_rgba16f(make_uint2(a.x, a.y));
@@ -41,48 +40,48 @@ __device__ __forceinline__ void process_pair(const TierAParams& p, uint4 a, uint
   }
   if (MODE == MODE_LIGHT || MODE == MODE_FUSED_HDR_LDR || MODE == MODE_FUSED_LDR) {
     uint2 h0 = pack_rgba16f(c0), h1 = pack_rgba16f(c1);
-    if (MODE != MODE_FUSED_LDR) stg_stream(p.hdr + hdr_off, make_uint4(h0.x, h0.y, h1.x, h1.y));
+    if (MODE != MODE_FUSED_LDR) stg_stream(hdr, make_uint4(h0.x, h0.y, h1.x, h1.y));
     if (MODE != MODE_LIGHT) {  // the tonemapper reads the fp16-rounded attachment value
       c0 = unpack_rgba16f(h0);
       c1 = unpack_rgba16f(h1);
     }
   }
-  if (MODE != MODE_LIGHT) stg_stream8(p.ldr + ldr_off, make_uint2(tonemap_texel(c0), tonemap_texel(c1)));
+  if (MODE != MODE_LIGHT) stg_stream8(ldr, make_uint2(tonemap_texel(c0), tonemap_texel(c1)));
 }
 
 template <int MODE>
-__device__ __forceinline__ void process_single(const TierAParams& p, size_t off8, size_t hdr_off,
-                                               size_t ldr_off, float cx, float cy, float cz) {
+__device__ __forceinline__ void process_single(const uint8_t* in0, const uint8_t* in1, const uint8_t* in2,
+                                               uint8_t* hdr, uint8_t* ldr, float cx, float cy, float cz) {
   F4 c0;
   if (MODE == MODE_TONEMAP) {
-    c0 = unpack_rgba16f(ldg_stream8(p.hdr_in + off8));
+    c0 = unpack_rgba16f(ldg_stream8(in0));
   } else {
-    c0 = blinnphong_texel(ldg_stream8(p.pos + off8), ldg_stream8(p.nrm + off8),
-                          ldg_stream8(p.alb + off8), cx, cy, cz);
+    c0 = blinnphong_texel(ldg_stream8(in0), ldg_stream8(in1), ldg_stream8(in2), cx, cy, cz);
   }
   if (MODE != MODE_TONEMAP) {
     uint2 h0 = pack_rgba16f(c0);
-    if (MODE != MODE_FUSED_LDR) stg_stream8(p.hdr + hdr_off, h0);
+    if (MODE != MODE_FUSED_LDR) stg_stream8(hdr, h0);
     if (MODE != MODE_LIGHT) c0 = unpack_rgba16f(h0);
   }
-  if (MODE != MODE_LIGHT) stg_stream4(p.ldr + ldr_off, tonemap_texel(c0));
+  if (MODE != MODE_LIGHT) stg_stream4(ldr, tonemap_texel(c0));
 }
 
 // VEC = 2: every row start and pitch is 16-byte aligned -> 128-bit accesses of texel pairs.
 // VEC = 1: arbitrary alignment (odd x0, odd pitch): 64-bit accesses, one texel per item.
 template <int MODE, int VEC>
 __global__ void __launch_bounds__(kThreads) tier_a_kernel(const __grid_constant__ TierAParams p) {
-  TierAParams q = p;
   float cx = p.cx, cy = p.cy, cz = p.cz;
-  if (p.cams != nullptr) {  // batched multi-view
-    uint32_t v = blockIdx.y;
+  const uint8_t *pos = p.pos, *nrm = p.nrm, *alb = p.alb, *hdr_in = p.hdr_in;
+  uint8_t *hdr = p.hdr, *ldr = p.ldr;
+  if (p.cams != nullptr) {  // batched multi-view: blockIdx.y selects the view
+    const uint32_t v = blockIdx.y;
     cx = __ldg(p.cams + 3 * v);
     cy = __ldg(p.cams + 3 * v + 1);
     cz = __ldg(p.cams + 3 * v + 2);
-    size_t o8 = size_t(v) * p.view_stride8;
-    q.pos += o8; q.nrm += o8; q.alb += o8;
-    if (q.hdr) q.hdr += size_t(v) * p.hdr_view_stride;
-    if (q.ldr) q.ldr += size_t(v) * p.ldr_view_stride;
+    const size_t o8 = size_t(v) * p.view_stride8;
+    pos += o8; nrm += o8; alb += o8;
+    if (hdr) hdr += size_t(v) * p.hdr_view_stride;
+    if (ldr) ldr += size_t(v) * p.ldr_view_stride;
   }
   const uint32_t items_per_row = (VEC == 2) ? (p.w + 1) / 2 : p.w;
   const uint64_t total = uint64_t(items_per_row) * p.h;
@@ -108,19 +107,20 @@ __global__ void __launch_bounds__(kThreads) tier_a_kernel(const __grid_constant_
       offl[u] = size_t(row) * p.ldr_pitch + size_t(x) * 4;
       if (valid[u] && pair[u]) {  // issue every load of the iteration before any math
         if (MODE == MODE_TONEMAP) {
-          a[u] = ldg_stream(q.hdr_in + offh[u]);
+          a[u] = ldg_stream(hdr_in + offh[u]);
         } else {
-          a[u] = ldg_stream(q.pos + off8[u]);
-          b[u] = ldg_stream(q.nrm + off8[u]);
-          c[u] = ldg_stream(q.alb + off8[u]);
+          a[u] = ldg_stream(pos + off8[u]);
+          b[u] = ldg_stream(nrm + off8[u]);
+          c[u] = ldg_stream(alb + off8[u]);
         }
       }
     }
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
       if (!valid[u]) continue;
-      if (pair[u]) process_pair<MODE>(q, a[u], b[u], c[u], offh[u], offl[u], cx, cy, cz);
-      else process_single<MODE>(q, MODE == MODE_TONEMAP ? offh[u] : off8[u], offh[u], offl[u], cx, cy, cz);
+      if (pair[u]) process_pair<MODE>(hdr + offh[u], ldr + offl[u], a[u], b[u], c[u], cx, cy, cz);
+      else if (MODE == MODE_TONEMAP) process_single<MODE>(hdr_in + offh[u], nullptr, nullptr, hdr + offh[u], ldr + offl[u], cx, cy, cz);
+      else process_single<MODE>(pos + off8[u], nrm + off8[u], alb + off8[u], hdr + offh[u], ldr + offl[u], cx, cy, cz);
     }
   }
 }
