@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native shading hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Metric (BASELINE.json): shaded Mpix/s at 4K GGX+IBL.  One "step" = one pass of the hot path over one
+batch = K3 (`pbrcu_shade_ggx_ibl`: GGX/Smith/Schlick + 4 point lights + occlusion/emissive + split-sum
+IBL) over one 3840x2160 synthetic G-buffer (BASELINE config[1]).  `value` is measured with the inputs
+resident in HBM (CUDA events on the launching stream, max over ranks); `e2e` is the same metric through
+the C-ABI call with HOST buffers (`pbrcu_shade_frame_host`: H2D of the five G-buffer planes, shade, D2H
+of the RGBA16F result, all inside the timed region).
+
+Multi-GPU (torchrun, one rank per GPU): frames (views) are independent, so every rank shades its own
+frames with no data-path collective ("weak" scaling); torch.distributed is used for the barrier and the
+max-over-ranks time only.
+
+`--impl reference` times the CPU side on the box's host cores.  The reference has NO GGX/IBL code
+(SURVEY.md section 0), so for this metric the CPU arm is the oracle port (oracle/pbr_oracle_ibl.c); the
+Tier-A figure beside it (`tier_a`) is the reference's own GLSL compiled for the CPU (oracle/_ref).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+W4K, H4K = 3840, 2160
+N_LIGHTS = 4
+B_PER_PX_K3 = 44   # 36 read (pos 8 + nrm 8 + albedo 8 + emissive 8 + orm 4) + 8 written
+B_PER_PX_K1 = 32   # 24 read + 8 written
+ENV_W, ENV_H = 4096, 2048
+CUBE_RES, CUBE_MIPS, IBL_SAMPLES, IRR_RES, LUT_RES = 2048, 12, 1024, 64, 512
+CAM = (0.0, -1.0, -12.0)
+SEED = 0x5EED0002
+
+
+def measured_peak_gbs():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons through NVML while the timed regions run."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.h = None
+
+    def run(self):
+        if self.h is None:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=1.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+class Scene:
+    """Device-resident benchmark inputs: rotating 4K G-buffer sets, lights, and the precomputed IBL."""
+
+    def __init__(self, pbr, dev, torch, n_sets=3):
+        self.pbr, self.dev, self.torch = pbr, dev, torch
+        lib, ctx = dev.lib, dev.ctx
+        cuda = torch.device("cuda", dev.ordinal)
+        self.keep = []
+
+        def buf(nbytes):
+            t = torch.empty(int(nbytes), dtype=torch.uint8, device=cuda)
+            self.keep.append(t)
+            return t
+
+        self.buf = buf
+        self.gbufs, self.outs = [], []
+        for i in range(n_sets):
+            g = pbr.GBuffer()
+            g.width, g.height, g.pitch8, g.pitch4 = W4K, H4K, W4K * 8, W4K * 4
+            planes = {k: buf(W4K * H4K * (4 if k in ("depth", "orm") else 8))
+                      for k in ("positions", "normals", "albedo", "depth", "orm", "emissive")}
+            for k, t in planes.items():
+                setattr(g, k, t.data_ptr())
+            lib.synth_gbuffer(ctx, C.byref(g), 1, SEED + i, pbr.f3(*CAM), pbr.f3(0, 0, 0), None)
+            self.gbufs.append((g, planes))
+            self.outs.append(buf(W4K * H4K * 8))
+        self.ldr = buf(W4K * H4K * 4)
+        from oracle import synth_lights
+        self.lights_host = synth_lights(N_LIGHTS, seed=2)
+        self.lights = buf(self.lights_host.nbytes)
+        self.lights.copy_(torch.from_numpy(self.lights_host.view(np.uint8).reshape(-1)))
+        # ---- IBL precompute (config[2] shapes), each kernel timed once with CUDA events ----
+        self.ibl_ms = {}
+        env = buf(ENV_W * ENV_H * 16)
+        lib.synth_environment(ctx, env.data_ptr(), ENV_W, ENV_H, SEED, None)
+        chain_bytes = lib.cube_chain_texels(CUBE_RES, CUBE_MIPS) * 8
+        self.src_chain, self.pref = buf(chain_bytes), buf(chain_bytes)
+        self.irr, self.lut = buf(6 * IRR_RES * IRR_RES * 8), buf(LUT_RES * LUT_RES * 8)
+        self.ham = buf(IBL_SAMPLES * 8)
+        torch.cuda.synchronize()
+        steps = [
+            ("hammersley", lambda: lib.ibl_hammersley(ctx, IBL_SAMPLES, self.ham.data_ptr(), self.stream())),
+            ("equirect_to_cube", lambda: lib.ibl_equirect_to_cube(ctx, env.data_ptr(), ENV_W, ENV_H, CUBE_RES, self.src_chain.data_ptr(), self.stream())),
+            ("cube_mipgen", lambda: lib.ibl_cube_mipgen(ctx, self.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, self.stream())),
+            ("prefilter_ggx", lambda: lib.ibl_prefilter_ggx(ctx, self.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, self.pref.data_ptr(), 0, CUBE_MIPS - 1, 0, 1, self.stream())),
+            ("irradiance", lambda: lib.ibl_irradiance(ctx, self.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IRR_RES, IBL_SAMPLES, self.irr.data_ptr(), self.stream())),
+            ("brdf_lut", lambda: lib.ibl_brdf_lut(ctx, LUT_RES, IBL_SAMPLES, self.lut.data_ptr(), self.stream())),
+        ]
+        for name, fn in steps:
+            fn()  # warm (also the run whose outputs are used)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            self.ibl_ms[name] = round(a.elapsed_time(b), 4)
+        s = pbr.Ibl()
+        s.irradiance, s.irr_res = self.irr.data_ptr(), IRR_RES
+        s.prefiltered, s.pref_res, s.pref_mips = self.pref.data_ptr(), CUBE_RES, CUBE_MIPS
+        s.lut, s.lut_res = self.lut.data_ptr(), LUT_RES
+        self.ibl = s
+
+    def stream(self):
+        return self.torch.cuda.current_stream().cuda_stream
+
+    def shade(self, i):
+        g, _ = self.gbufs[i % len(self.gbufs)]
+        self.dev.lib.shade_ggx_ibl(self.dev.ctx, C.byref(g), self.pbr.f3(*CAM), self.lights.data_ptr(), N_LIGHTS, None,
+                                   C.byref(self.ibl), self.pbr.WHOLE, self.outs[i % len(self.outs)].data_ptr(), W4K * 8, self.stream())
+
+    def lighting(self, i):
+        g, _ = self.gbufs[i % len(self.gbufs)]
+        self.dev.lib.lighting_blinnphong(self.dev.ctx, C.byref(g), self.pbr.f3(*CAM), self.pbr.WHOLE,
+                                         self.outs[i % len(self.outs)].data_ptr(), W4K * 8, self.stream())
+
+    def fused(self, i):
+        g, _ = self.gbufs[i % len(self.gbufs)]
+        self.dev.lib.lighting_tonemap_fused(self.dev.ctx, C.byref(g), self.pbr.f3(*CAM), self.pbr.WHOLE, None, 0,
+                                            self.ldr.data_ptr(), W4K * 4, self.stream())
+
+
+def timed(torch, dist, fn, steps, warmup):
+    """W untimed + exactly K timed calls of fn(i), barrier + synchronize on both sides, CUDA events on the
+    launching stream; returns max-over-ranks milliseconds for the K steps."""
+    for i in range(warmup):
+        fn(i)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(steps):
+        fn(warmup + i)
+    b.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = a.elapsed_time(b)
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def host_frame(scene, torch):
+    """Pinned host copies of G-buffer set 0 (the e2e inputs) and a pinned result buffer."""
+    g, planes = scene.gbufs[0]
+    host = {k: torch.empty(t.numel(), dtype=torch.uint8, pin_memory=True) for k, t in planes.items() if k != "depth"}
+    for k, t in host.items():
+        t.copy_(planes[k])
+    out = torch.empty(W4K * H4K * 8, dtype=torch.uint8, pin_memory=True)
+    torch.cuda.synchronize()
+    return host, out
+
+
+def run_e2e(scene, torch, dist, host, out, steps, warmup):
+    lib, ctx, pbr = scene.dev.lib, scene.dev.ctx, scene.pbr
+    lights = scene.lights_host
+    cam = pbr.f3(*CAM)
+
+    def step(_):
+        lib.shade_frame_host(ctx, host["positions"].data_ptr(), host["normals"].data_ptr(), host["albedo"].data_ptr(),
+                             host["orm"].data_ptr(), host["emissive"].data_ptr(), W4K, H4K, cam, lights.ctypes.data,
+                             N_LIGHTS, C.byref(scene.ibl), out.data_ptr(), 8, scene.stream())
+
+    return timed(torch, dist, step, steps, warmup)
+
+
+def cpu_sample(scene, torch, budget_s=12.0):
+    """Times the CPU oracle (port of the published formulas; the reference has no GGX/IBL code) on a
+    bounded band of rows of the SAME 4K G-buffer and IBL textures, all host threads; also returns the
+    GPU-vs-oracle parity of that band."""
+    from oracle import Oracle
+    o = Oracle()
+    g, planes = scene.gbufs[0]
+    np_of = lambda t, dt, shape: t.cpu().numpy().view(dt).reshape(shape)
+    pos = np_of(planes["positions"], np.float16, (H4K, W4K, 4))
+    nrm = np_of(planes["normals"], np.float16, (H4K, W4K, 4))
+    alb = np_of(planes["albedo"], np.uint16, (H4K, W4K, 4))
+    orm = np_of(planes["orm"], np.uint8, (H4K, W4K, 4))
+    emi = np_of(planes["emissive"], np.float16, (H4K, W4K, 4))
+    ibl = dict(irr=np_of(scene.irr, np.uint16, (6, IRR_RES, IRR_RES, 4)), pref=np_of(scene.pref, np.uint16, (-1, 4)),
+               pref_res=CUBE_RES, pref_mips=CUBE_MIPS, lut=np_of(scene.lut, np.float32, (LUT_RES, LUT_RES, 2)))
+    rows, y0 = 16, H4K // 2
+    t0 = time.perf_counter()
+    o.shade(pos, nrm, alb, orm, emi, CAM, scene.lights_host, ibl, rect=(0, y0, W4K, rows))
+    dt = time.perf_counter() - t0
+    rows = int(min(H4K // 2, max(16, rows * budget_s / max(dt, 1e-6))))
+    t0 = time.perf_counter()
+    _, want = o.shade(pos, nrm, alb, orm, emi, CAM, scene.lights_host, ibl, rect=(0, y0, W4K, rows))
+    dt = time.perf_counter() - t0
+    scene.shade(0)
+    torch.cuda.synchronize()
+    got = np_of(scene.outs[0], np.uint16, (H4K, W4K, 4))[y0:y0 + rows]
+    gf, wf = got.view(np.float16).astype(np.float32), want[y0:y0 + rows].view(np.float16).astype(np.float32)
+    err = np.abs(gf - wf)
+    rel_excess = float((err - (1e-3 + 2.0 ** -9 * np.abs(wf))).max())
+    mse = float(np.mean((gf.astype(np.float64) - wf) ** 2))
+    peak = float(max(wf.max(), 1.0))
+    parity = {"rows": rows, "max_abs_err": float(err.max()), "tolerance": "1e-3 + 2^-9*|ref|", "within": rel_excess <= 0,
+              "psnr_db": (None if mse == 0 else round(10 * np.log10(peak * peak / mse), 1)), "vs": "oracle (no reference counterpart)"}
+    mpix = rows * W4K / dt / 1e6
+    return {"value": round(mpix, 3), "unit": "Mpix/s", "cores": o.max_threads(), "kind": "port",
+            "sample": f"{rows} rows x {W4K} px of the 4K frame, {N_LIGHTS} lights + IBL, oracle/pbr_oracle_ibl.c, {dt:.1f} s"}, parity
+
+
+def main_ours(args):
+    import torch
+    import pbr_b200 as pbr
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+    dev = pbr.Device(local)  # raises when libpbrcu.so or the GPU is missing: there is no fallback
+    scene = Scene(pbr, dev, torch)
+    sampler = ClockSampler(local)
+    sampler.start()
+
+    ms = timed(torch, dist, scene.shade, args.steps, args.warmup)
+    px_step = W4K * H4K
+    value = world * px_step * args.steps / (ms * 1e-3) / 1e6
+    launch_ms = ms / args.steps  # one K3 launch per step
+    peak, peak_src = measured_peak_gbs()
+    achieved = B_PER_PX_K3 * px_step / (launch_ms * 1e-3) / 1e9
+
+    # Tier A (reference-pinned) kernels, same protocol
+    ms_k1 = timed(torch, dist, scene.lighting, args.steps, args.warmup)
+    ms_fused = timed(torch, dist, scene.fused, args.steps, args.warmup)
+
+    host, out = host_frame(scene, torch)
+    e2e_steps = max(3, min(args.steps, 20))
+    ms_e2e = run_e2e(scene, torch, dist, host, out, e2e_steps, 3)
+    e2e_value = world * px_step * e2e_steps / (ms_e2e * 1e-3) / 1e6
+    clocks = sampler.stop()
+
+    cpu, parity = (None, None)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu, parity = cpu_sample(scene, torch)
+
+    if rank == 0:
+        k1_gbs = B_PER_PX_K1 * px_step * args.steps / (ms_k1 * 1e-3) / 1e9
+        line = {
+            "metric": "shaded Mpix/s at 4K GGX+IBL", "value": round(value, 1), "unit": "Mpix/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 5),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "3840x2160 synthetic G-buffer (gbuf_spheres), GGX metallic-roughness + 4 point lights + "
+                                   "precomputed IBL (2048^2 12-mip prefiltered cube, 64^2 irradiance, 512^2 LUT), 1 frame per step per GPU",
+                       "l2": "inputs larger than L2 (365 MB per frame) and 3 rotating buffer sets", "parallelism": f"frames x{world}"},
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "kernel": "shade_ggx_kernel", "algorithmic_bytes_per_px": B_PER_PX_K3},
+            "e2e": {"value": round(e2e_value, 1), "unit": "Mpix/s", "h2d_bytes_per_step": px_step * 36,
+                    "d2h_bytes_per_step": px_step * 8, "steps": e2e_steps, "api": "pbrcu_shade_frame_host (pinned host planes, 8 pipelined row bands)"},
+            "gpu_launches": args.steps,
+            "clocks": clocks,
+            "cpu_baseline": cpu,
+            "parity": parity,
+            "tier_a": {"note": "reference-pinned passes (lighting.glsl / aces+gamma.glsl) at 4K, same protocol",
+                       "lighting_mpix_s": round(world * px_step * args.steps / (ms_k1 * 1e-3) / 1e6, 1),
+                       "lighting_gbs": round(k1_gbs, 1), "lighting_roofline_frac": round(k1_gbs / peak, 4),
+                       "fused_ldr_mpix_s": round(world * px_step * args.steps / (ms_fused * 1e-3) / 1e6, 1),
+                       "fused_ldr_roofline_frac": round(28 * px_step * args.steps / (ms_fused * 1e-3) / 1e9 / peak, 4)},
+            "ibl_precompute_ms": scene.ibl_ms,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm (--impl reference)
+# ---------------------------------------------------------------------------------------------------
+def main_reference(args):
+    """The reference's CPU side of the path on the box's host cores.  For GGX+IBL the reference has no
+    implementation at all, so this arm times the oracle port; the reference's own shaders
+    (oracle/_ref, lighting.glsl compiled for the CPU) are timed beside it as `tier_a`."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle import Oracle, RefShaders, synth_environment, synth_gbuffer, synth_lights
+    o = Oracle()
+    threads = o.max_threads()
+    rows_total = H4K  # the whole 4K frame is generated; each step shades a bounded band of it
+    g = synth_gbuffer(W4K, rows_total, seed=SEED & 0xFFFF, background=0.25, tier_b=True)
+    lights = synth_lights(N_LIGHTS, seed=2)
+    res, mips, ns = 128, 8, 128
+    env = synth_environment(512, 256, 1)
+    chain = o.make_chain(o.equirect_to_cube(env, res), mips)
+    ibl = dict(irr=o.irradiance(chain, res, mips, 16, ns), pref=o.prefilter(chain, res, mips, ns), pref_res=res,
+               pref_mips=mips, lut=o.brdf_lut(128, ns))
+
+    def shade(rows):
+        o.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], CAM, lights, ibl, rect=(0, 0, W4K, rows))
+
+    t0 = time.perf_counter(); shade(8); dt8 = time.perf_counter() - t0
+    per_step = min(2.0, 150.0 / (args.steps + args.warmup))
+    rows = int(max(1, min(rows_total, 8 * per_step / max(dt8, 1e-6))))
+    for _ in range(args.warmup):
+        shade(rows)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        shade(rows)
+    dt = time.perf_counter() - t0
+    value = rows * W4K * args.steps / dt / 1e6
+    sample = f"{rows} rows x {W4K} px per step of a 4K-wide synthetic G-buffer, {N_LIGHTS} lights + IBL ({res}^2 x{mips} mips), all host threads"
+    tier_a = None
+    try:
+        r = RefShaders()
+        t0 = time.perf_counter(); r.lighting(g["pos"], g["nrm"], g["alb"], CAM); d = time.perf_counter() - t0
+        tier_a = {"lighting_mpix_s": round(rows_total * W4K / d / 1e6, 2), "kind": "reference",
+                  "what": "assets/shaders/pbr/lighting.glsl compiled for the CPU (oracle/_ref), all host threads"}
+    except Exception as e:  # oracle/_ref not built
+        tier_a = {"unavailable": str(e)}
+    line = {
+        "impl": "reference", "metric": "shaded Mpix/s at 4K GGX+IBL", "value": round(value, 3), "unit": "Mpix/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "3840x2160 synthetic G-buffer, GGX metallic-roughness + 4 point lights + precomputed IBL (bounded row-band sample per step)"},
+        "cpu_baseline": {"value": round(value, 3), "unit": "Mpix/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": round(value, 3), "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "tier_a": tier_a,
+        "note": "the reference has no GGX/IBL implementation and its Vulkan path is unavailable on this box; CPU arm = oracle port",
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        main_reference(args)
+    else:
+        main_ours(args)
+
+
+if __name__ == "__main__":
+    main()

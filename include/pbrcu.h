@@ -153,6 +153,15 @@ int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
                         const pbrcu_light* lights_dev, uint32_t n_lights,
                         const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
                         void* out_rgba16f, size_t out_pitch, pbrcu_stream s);
+/* One GGX+IBL frame through HOST buffers (the end-to-end path of the headline metric): the frame is
+ * cut into n_bands row bands (0 = 8) pipelined over two internal streams, so the H2D copy of band
+ * i+1 overlaps the shading and D2H read-back of band i.  lights_host is a host array; ibl textures
+ * are device-resident (precomputed once).  Host planes should be pinned.  Synchronises before return. */
+int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,
+                           const void* albedo_host, const void* orm_host, const void* emissive_host,
+                           uint32_t width, uint32_t height, const float cam_pos[3],
+                           const pbrcu_light* lights_host, uint32_t n_lights, const pbrcu_ibl* ibl,
+                           void* hdr_out_host, uint32_t n_bands, pbrcu_stream s);
 /* K3c: per 16x16 tile, the lights whose range sphere meets the tile's world-space position AABB */
 int pbrcu_light_tiles_alloc(pbrcu_ctx* ctx, uint32_t width, uint32_t height, uint32_t max_per_tile,
                             pbrcu_light_tiles* out);

@@ -102,6 +102,7 @@ _SIGNATURES = {
     "pbrcu_cube_chain_texels": (_sz, [_u32, _u32]),
     "pbrcu_cube_mip_offset": (_sz, [_u32, _u32]),
     "pbrcu_shade_ggx_ibl": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, _vp]),
+    "pbrcu_shade_frame_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _f3, _vp, _u32, _PI, _vp, _u32, _vp]),
     "pbrcu_light_tiles_alloc": (_i, [_vp, _u32, _u32, _u32, _PT]),
     "pbrcu_light_tiles_free": (_i, [_vp, _PT]),
     "pbrcu_cluster_lights": (_i, [_vp, _PG, _vp, _u32, _PT, _vp]),

@@ -63,9 +63,15 @@ extern "C" int pbrcu_ctx_create(int device, pbrcu_ctx** out) {
 
 extern "C" void pbrcu_ctx_destroy(pbrcu_ctx* ctx) {
   if (!ctx) return;
-  for (int i = 0; i < 5; ++i)
+  for (int i = 0; i < 8; ++i)
     if (ctx->stage[i]) cudaFree(ctx->stage[i]);
   if (ctx->cams_dev) cudaFree(ctx->cams_dev);
+  if (ctx->lights_dev) cudaFree(ctx->lights_dev);
+  for (int i = 0; i < 2; ++i) {
+    if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
+    if (ctx->pipe_done[i]) cudaEventDestroy(ctx->pipe_done[i]);
+  }
+  if (ctx->pipe_start) cudaEventDestroy(ctx->pipe_start);
   delete ctx;
 }
 
@@ -267,6 +273,71 @@ extern "C" int pbrcu_frame_host(pbrcu_ctx* ctx, const void* positions_host, cons
   if (rc) return rc;
   if (hdr_out_host) PBRCU_CUDA(cudaMemcpyAsync(hdr_out_host, ctx->stage[3], b8, cudaMemcpyDeviceToHost, st));
   if (ldr_out_host) PBRCU_CUDA(cudaMemcpyAsync(ldr_out_host, ctx->stage[4], b4, cudaMemcpyDeviceToHost, st));
+  PBRCU_CUDA(cudaStreamSynchronize(st));
+  return PBRCU_OK;
+}
+
+// ---- one GGX+IBL frame through host buffers, pipelined in row bands ---------------------------
+static int ensure_pipe(pbrcu_ctx* ctx) {
+  if (ctx->pipe[0]) return PBRCU_OK;
+  for (int i = 0; i < 2; ++i) {
+    PBRCU_CUDA(cudaStreamCreateWithFlags(&ctx->pipe[i], cudaStreamNonBlocking));
+    PBRCU_CUDA(cudaEventCreateWithFlags(&ctx->pipe_done[i], cudaEventDisableTiming));
+  }
+  PBRCU_CUDA(cudaEventCreateWithFlags(&ctx->pipe_start, cudaEventDisableTiming));
+  return PBRCU_OK;
+}
+
+extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,
+                                      const void* albedo_host, const void* orm_host, const void* emissive_host,
+                                      uint32_t width, uint32_t height, const float cam_pos[3],
+                                      const pbrcu_light* lights_host, uint32_t n_lights, const pbrcu_ibl* ibl,
+                                      void* hdr_out_host, uint32_t n_bands, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && positions_host && normals_host && albedo_host && orm_host && emissive_host && cam_pos && hdr_out_host, "NULL argument");
+  PBRCU_REQUIRE(width > 0 && height > 0, "empty extent");
+  PBRCU_REQUIRE(n_lights == 0 || lights_host, "lights_host is NULL");
+  if (n_bands == 0) n_bands = 8;
+  if (n_bands > height) n_bands = height;
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  const size_t p8 = size_t(width) * 8, p4 = size_t(width) * 4;
+  int rc;
+  const size_t need[6] = {p8 * height, p8 * height, p8 * height, p4 * height, p8 * height, p8 * height};
+  for (int i = 0; i < 6; ++i)
+    if ((rc = ensure_stage(ctx, i, need[i]))) return rc;
+  if ((rc = ensure_pipe(ctx))) return rc;
+  if (ctx->lights_cap < n_lights) {
+    if (ctx->lights_dev) PBRCU_CUDA(cudaFree(ctx->lights_dev));
+    ctx->lights_dev = nullptr; ctx->lights_cap = 0;
+    PBRCU_CUDA(cudaMalloc(&ctx->lights_dev, size_t(n_lights) * sizeof(pbrcu_light)));
+    ctx->lights_cap = n_lights;
+  }
+  if (n_lights) PBRCU_CUDA(cudaMemcpyAsync(ctx->lights_dev, lights_host, size_t(n_lights) * sizeof(pbrcu_light), cudaMemcpyHostToDevice, st));
+  PBRCU_CUDA(cudaEventRecord(ctx->pipe_start, st));
+  for (int i = 0; i < 2; ++i) PBRCU_CUDA(cudaStreamWaitEvent(ctx->pipe[i], ctx->pipe_start, 0));
+  pbrcu_gbuffer g{};
+  g.positions = ctx->stage[0]; g.normals = ctx->stage[1]; g.albedo = ctx->stage[2];
+  g.orm = ctx->stage[3]; g.emissive = ctx->stage[4];
+  g.width = width; g.height = height; g.pitch8 = p8; g.pitch4 = p4;
+  const void* src[5] = {positions_host, normals_host, albedo_host, orm_host, emissive_host};
+  for (uint32_t b = 0; b < n_bands; ++b) {
+    cudaStream_t ps = ctx->pipe[b & 1];
+    const uint32_t y0 = uint32_t(uint64_t(height) * b / n_bands), y1 = uint32_t(uint64_t(height) * (b + 1) / n_bands);
+    if (y1 == y0) continue;
+    for (int i = 0; i < 5; ++i) {
+      const size_t pitch = (i == 3) ? p4 : p8;
+      PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(ctx->stage[i]) + y0 * pitch, static_cast<const uint8_t*>(src[i]) + y0 * pitch,
+                                 size_t(y1 - y0) * pitch, cudaMemcpyHostToDevice, ps));
+    }
+    if ((rc = pbrcu_shade_ggx_ibl(ctx, &g, cam_pos, ctx->lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, y0, width, y1 - y0},
+                                  ctx->stage[5], p8, ps)))
+      return rc;
+    PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(hdr_out_host) + y0 * p8, static_cast<uint8_t*>(ctx->stage[5]) + y0 * p8,
+                               size_t(y1 - y0) * p8, cudaMemcpyDeviceToHost, ps));
+  }
+  for (int i = 0; i < 2; ++i) {
+    PBRCU_CUDA(cudaEventRecord(ctx->pipe_done[i], ctx->pipe[i]));
+    PBRCU_CUDA(cudaStreamWaitEvent(st, ctx->pipe_done[i], 0));
+  }
   PBRCU_CUDA(cudaStreamSynchronize(st));
   return PBRCU_OK;
 }

@@ -11,8 +11,14 @@ struct pbrcu_ctx {
   int sm_count;
   int max_smem_optin;
   // staging for pbrcu_frame_host (grown on demand)
-  void* stage[5];
-  size_t stage_bytes[5];
+  void* stage[8];
+  size_t stage_bytes[8];
+  // two internal streams (+ events) that pipeline row bands of a host frame: H2D | shade | D2H
+  cudaStream_t pipe[2];
+  cudaEvent_t pipe_done[2];
+  cudaEvent_t pipe_start;
+  pbrcu_light* lights_dev;
+  uint32_t lights_cap;
   // per-view camera positions for the batched multi-view launch (grown on demand)
   float* cams_dev;
   uint32_t cams_cap;
