@@ -420,11 +420,11 @@ void pbro_shade_pixel(const uint16_t pos_h[4], const uint16_t nrm_h[4], const ui
   for (int i = 0; i < nlights; ++i) {
     const pbro_light* lt = &lights[i];
     float Lv[3] = {lt->px - P[0], lt->py - P[1], lt->pz - P[2]};
-    float d2 = Lv[0] * Lv[0] + Lv[1] * Lv[1] + Lv[2] * Lv[2];
+    float d2 = fmaxf(Lv[0] * Lv[0] + Lv[1] * Lv[1] + Lv[2] * Lv[2], 1e-8f); /* light inside the surface point */
     float invd = 1.0f / sqrtf(d2);
     float Ld[3] = {Lv[0] * invd, Lv[1] * invd, Lv[2] * invd};
     float NoL = clamp01(N[0] * Ld[0] + N[1] * Ld[1] + N[2] * Ld[2]);
-    float att = 1.0f / fmaxf(d2, 1e-8f);
+    float att = 1.0f / d2; /* KHR_lights_punctual: inverse-square falloff */
     if (lt->range > 0.0f) {
       float q = d2 / (lt->range * lt->range);
       att *= clamp01(1.0f - q * q);

@@ -36,30 +36,20 @@ __device__ __forceinline__ float3 normalize3(float3 v) {
 }
 
 __device__ __forceinline__ void cube_dir_to_face_uv(float3 d, int& face, float& u, float& v) {
+  // branchless (select-only) form of the OpenGL/Vulkan major-axis rule; ties go X, then Y, then Z
   const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-  float sc, tc, ma;
-  if (ax >= ay && ax >= az) {
-    ma = ax;
-    const bool pos = d.x >= 0.0f;
-    face = pos ? 0 : 1;
-    sc = pos ? -d.z : d.z;
-    tc = -d.y;
-  } else if (ay >= az) {
-    ma = ay;
-    const bool pos = d.y >= 0.0f;
-    face = pos ? 2 : 3;
-    sc = d.x;
-    tc = pos ? d.z : -d.z;
-  } else {
-    ma = az;
-    const bool pos = d.z >= 0.0f;
-    face = pos ? 4 : 5;
-    sc = pos ? d.x : -d.x;
-    tc = -d.y;
-  }
-  const float inv = __fdividef(1.0f, ma);
-  u = 0.5f * (sc * inv + 1.0f);
-  v = 0.5f * (tc * inv + 1.0f);
+  const bool isx = ax >= ay && ax >= az;
+  const bool isy = !isx && ay >= az;
+  const float ma = isx ? ax : (isy ? ay : az);
+  const float major = isx ? d.x : (isy ? d.y : d.z);
+  const bool neg = major < 0.0f;
+  face = (isx ? 0 : (isy ? 2 : 4)) + (neg ? 1 : 0);
+  // +X: sc=-z  -X: sc=+z  +-Y: sc=+x  +Z: sc=+x  -Z: sc=-x ;  +Y: tc=+z  -Y: tc=-z  others: tc=-y
+  const float sc = isx ? (neg ? d.z : -d.z) : ((isy || !neg) ? d.x : -d.x);
+  const float tc = isy ? (neg ? -d.z : d.z) : -d.y;
+  const float inv = __fdividef(0.5f, ma);
+  u = fmaf(sc, inv, 0.5f);
+  v = fmaf(tc, inv, 0.5f);
 }
 
 __device__ __forceinline__ float lerpf(float a, float b, float t) { return fmaf(t, b - a, a); }

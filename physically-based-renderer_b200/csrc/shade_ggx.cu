@@ -1,7 +1,7 @@
 // shade_ggx.cu -- K3 metallic-roughness Cook-Torrance shading (GGX D, height-correlated Smith V,
 // Schlick F) with point lights, occlusion, emissive and split-sum IBL over the extended G-buffer, and
 // K3c the per-tile light lists.  No reference counterpart; definition:
-// oracle/pbr_oracle_ibl.c:pbro_shade_pixel (glTF 2.0 Appendix B, KHR_lights_punctual, Karis 2013).
+// glTF 2.0 Appendix B + KHR_lights_punctual + Karis 2013 (restated for the CPU checker as pbro_shade_pixel).
 //
 // One CTA = one 16x16 pixel tile (persistent loop over tiles): a warp reads two 128-byte row segments
 // per plane, the tile's light list is staged once in shared memory, and the IBL fetches of
@@ -12,7 +12,8 @@ namespace pbrcu {
 
 constexpr int kTile = PBRCU_TILE;
 constexpr int kShadeThreads = kTile * kTile;
-constexpr int kMaxSmemLights = 1024;
+constexpr int kMaxLights = 1024;   // API limit for max_per_tile
+constexpr int kLightChunk = 128;   // lights staged in shared memory at a time
 constexpr float kInvPi = 0.31830988618379067154f;
 
 struct ShadeParams {
@@ -20,7 +21,7 @@ struct ShadeParams {
   uint8_t* out;
   size_t pitch8, pitch4, out_pitch;
   uint32_t x0, y0, x1, y1;        // rect in image coordinates (x1, y1 exclusive)
-  uint32_t tx0, ty0, ntx, nty;    // tile range covering the rect
+  uint32_t tx0, ty0;              // first tile of the grid (blockIdx is relative to it)
   float cx, cy, cz;
   const pbrcu_light* lights;
   uint32_t n_lights;
@@ -46,111 +47,126 @@ __device__ __forceinline__ float2 lut_sample(const float2* lut, int res, float u
                      lerpf(lerpf(t00.y, t10.y, tx), lerpf(t01.y, t11.y, tx), ty));
 }
 
-__device__ __forceinline__ float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
+__device__ __forceinline__ float sat(float x) { return __saturatef(x); }
 
-__global__ void __launch_bounds__(kShadeThreads) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
-  __shared__ float4 s_light[kMaxSmemLights * 2];  // {px,py,pz,range}, {r,g,b,intensity}
-  __shared__ uint32_t s_count;
-  const int lx = threadIdx.x % kTile, ly = threadIdx.x / kTile;
-  const uint32_t ntiles = p.ntx * p.nty;
-  const bool stage_all = (p.tile_counts == nullptr) && p.n_lights <= kMaxSmemLights;
-  if (stage_all) {
-    for (uint32_t i = threadIdx.x; i < p.n_lights * 2; i += kShadeThreads)
-      s_light[i] = __ldg(reinterpret_cast<const float4*>(p.lights) + i);
-    if (threadIdx.x == 0) s_count = p.n_lights;
-    __syncthreads();
-  }
-  for (uint32_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-    const uint32_t tx = p.tx0 + t % p.ntx, ty = p.ty0 + t / p.ntx;
-    if (p.tile_counts != nullptr) {  // stage this tile's light list
-      __syncthreads();
-      const uint32_t tile = ty * p.tiles_x + tx;
-      const uint32_t cnt = min(__ldg(p.tile_counts + tile), min(p.max_per_tile, uint32_t(kMaxSmemLights)));
-      const uint16_t* idx = p.tile_indices + size_t(tile) * p.max_per_tile;
-      for (uint32_t i = threadIdx.x; i < cnt * 2; i += kShadeThreads) {
-        const uint32_t li = __ldg(idx + (i >> 1));
-        s_light[i] = __ldg(reinterpret_cast<const float4*>(p.lights) + li * 2 + (i & 1));
-      }
-      if (threadIdx.x == 0) s_count = cnt;
-      __syncthreads();
-    }
-    const uint32_t x = tx * kTile + lx, y = ty * kTile + ly;
-    if (x < p.x0 || x >= p.x1 || y < p.y0 || y >= p.y1) continue;
+// One CTA = one 16x16 pixel tile (blockIdx = tile).  Lights are staged kLightChunk at a time in shared
+// memory in a pre-digested form: {position, 1/range^2 (0 = unlimited)} and {colour * intensity}.
+__global__ void __launch_bounds__(kShadeThreads, 4) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
+  __shared__ float4 s_pos[kLightChunk];
+  __shared__ float4 s_col[kLightChunk];
+  const uint32_t tx = p.tx0 + blockIdx.x, ty = p.ty0 + blockIdx.y;
+  const uint32_t x = tx * kTile + (threadIdx.x % kTile), y = ty * kTile + (threadIdx.x / kTile);
+  const bool inside = x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1;
+
+  // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
+  float3 P = make_float3(0.f, 0.f, 0.f), N = P, V = P;
+  float NoVraw = 0.f, NoV = 1.f, rough = 1.f, occ = 0.f, a2 = 1.f, oma2 = 0.f, visV = 1.f, base_a = 0.f;
+  float F0r = 0.f, F0g = 0.f, F0b = 0.f, cdr = 0.f, cdg = 0.f, cdb = 0.f;
+  float Lr = 0.f, Lg = 0.f, Lb = 0.f;
+  bool lit = false;
+  if (inside) {
     const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8;
     const uint2 tp = ldg_stream8(p.pos + o8), tn = ldg_stream8(p.nrm + o8), ta = ldg_stream8(p.alb + o8);
     const uint2 te = ldg_stream8(p.emi + o8);
     const uint32_t to = ldg_stream4(p.orm + size_t(y) * p.pitch4 + size_t(x) * 4);
-    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8;
-
     const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
-    if (nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f) {  // cleared (background) texel
-      stg_stream8(outp, make_uint2(0u, 0u));
-      continue;
+    lit = !(nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f);  // all-zero normal = cleared texel
+    if (lit) {
+      const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
+      P = make_float3(pxy.x, pxy.y, pzw.x);
+      N = normalize3(make_float3(nxy.x, nxy.y, nzw.x));
+      V = normalize3(make_float3(p.cx - P.x, p.cy - P.y, p.cz - P.z));
+      NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
+      NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
+      const float base_r = unorm16_lo(ta.x), base_g = unorm16_hi(ta.x), base_b = unorm16_lo(ta.y);
+      base_a = unorm16_hi(ta.y);
+      occ = float(to & 0xFFu) * (1.0f / 255.0f);
+      rough = fminf(fmaxf(float((to >> 8) & 0xFFu) * (1.0f / 255.0f), 0.045f), 1.0f);
+      const float metal = float((to >> 16) & 0xFFu) * (1.0f / 255.0f), omm = 1.0f - metal;
+      F0r = 0.04f * omm + base_r * metal; F0g = 0.04f * omm + base_g * metal; F0b = 0.04f * omm + base_b * metal;
+      cdr = base_r * omm; cdg = base_g * omm; cdb = base_b * omm;
+      const float alpha = rough * rough;
+      a2 = alpha * alpha; oma2 = 1.0f - a2;
+      const float vv = NoV * NoV * oma2 + a2;
+      visV = vv * rsqrtf(vv);
+      const float2 exy = h2_to_f2(te.x), ezw = h2_to_f2(te.y);
+      Lr = exy.x; Lg = exy.y; Lb = ezw.x;  // emissive
     }
-    const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
-    const float3 P = make_float3(pxy.x, pxy.y, pzw.x);
-    const float3 N = normalize3(make_float3(nxy.x, nxy.y, nzw.x));
-    const float3 V = normalize3(make_float3(p.cx - P.x, p.cy - P.y, p.cz - P.z));
-    const float NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
-    const float NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
-    const float base_r = unorm16_lo(ta.x), base_g = unorm16_hi(ta.x), base_b = unorm16_lo(ta.y), base_a = unorm16_hi(ta.y);
-    const float occ = float(to & 0xFFu) * (1.0f / 255.0f);
-    const float rough = fminf(fmaxf(float((to >> 8) & 0xFFu) * (1.0f / 255.0f), 0.045f), 1.0f);
-    const float metal = float((to >> 16) & 0xFFu) * (1.0f / 255.0f);
-    const float omm = 1.0f - metal;
-    const float F0r = 0.04f * omm + base_r * metal, F0g = 0.04f * omm + base_g * metal, F0b = 0.04f * omm + base_b * metal;
-    const float cdr = base_r * omm, cdg = base_g * omm, cdb = base_b * omm;
-    const float alpha = rough * rough, a2 = alpha * alpha, oma2 = 1.0f - a2;
-    const float visV = sqrtf(NoV * NoV * oma2 + a2);
-    float Lr = 0.f, Lg = 0.f, Lb = 0.f;
-
-    const uint32_t nl = (stage_all || p.tile_counts) ? s_count : p.n_lights;
-    for (uint32_t i = 0; i < nl; ++i) {
-      float4 la, lb;
-      if (stage_all || p.tile_counts) { la = s_light[2 * i]; lb = s_light[2 * i + 1]; }
-      else { la = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * i); lb = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * i + 1); }
-      const float dx = la.x - P.x, dy = la.y - P.y, dz = la.z - P.z;
-      const float d2 = dx * dx + dy * dy + dz * dz;
-      const float invd = rsqrtf(d2);
-      const float ldx = dx * invd, ldy = dy * invd, ldz = dz * invd;
-      const float NoL = clamp01(N.x * ldx + N.y * ldy + N.z * ldz);
-      float att = __fdividef(1.0f, fmaxf(d2, 1e-8f));
-      if (la.w > 0.0f) {  // KHR_lights_punctual range window: clamp(1 - (d/range)^4, 0, 1)
-        const float q = __fdividef(d2, la.w * la.w);
-        att *= clamp01(1.0f - q * q);
-      }
-      if (NoL > 0.0f && att > 0.0f) {
-        float hx = V.x + ldx, hy = V.y + ldy, hz = V.z + ldz;
-        const float hinv = rsqrtf(hx * hx + hy * hy + hz * hz);
-        hx *= hinv; hy *= hinv; hz *= hinv;
-        const float NoH = clamp01(N.x * hx + N.y * hy + N.z * hz);
-        const float VoH = clamp01(V.x * hx + V.y * hy + V.z * hz);
-        // 1 - NoH^2 = |N x H|^2: NoH^2 (a2 - 1) + 1 cancels catastrophically in fp32 for smooth surfaces
-        const float kx = N.y * hz - N.z * hy, ky = N.z * hx - N.x * hz, kz = N.x * hy - N.y * hx;
-        const float dd = (kx * kx + ky * ky + kz * kz) + NoH * NoH * a2;
-        const float D = __fdividef(a2, 3.14159265358979f * dd * dd);
-        const float vis = __fdividef(0.5f, NoL * visV + NoV * sqrtf(NoL * NoL * oma2 + a2));
-        const float tt = 1.0f - VoH, t2 = tt * tt, fc = t2 * t2 * tt;
-        const float sc = lb.w * att * NoL, dv = D * vis;
-        const float Fr = F0r + (1.0f - F0r) * fc, Fg = F0g + (1.0f - F0g) * fc, Fb = F0b + (1.0f - F0b) * fc;
-        Lr += ((1.0f - Fr) * cdr * kInvPi + Fr * dv) * (lb.x * sc);
-        Lg += ((1.0f - Fg) * cdg * kInvPi + Fg * dv) * (lb.y * sc);
-        Lb += ((1.0f - Fb) * cdb * kInvPi + Fb * dv) * (lb.z * sc);
-      }
-    }
-    if (p.has_ibl) {
-      const float3 R = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
-      const RGB irr = cube_sample(p.irr, N, 0.0f);
-      const RGB pre = cube_sample(p.pref, R, rough * float(p.pref.nmips - 1));
-      const float2 ab = lut_sample(p.lut, int(p.lut_res), NoV, rough);
-      Lr += (irr.r * cdr + pre.r * (F0r * ab.x + ab.y)) * occ;
-      Lg += (irr.g * cdg + pre.g * (F0g * ab.x + ab.y)) * occ;
-      Lb += (irr.b * cdb + pre.b * (F0b * ab.x + ab.y)) * occ;
-    }
-    const float2 exy = h2_to_f2(te.x), ezw = h2_to_f2(te.y);
-    Lr = fminf(Lr + exy.x, 65504.0f); Lg = fminf(Lg + exy.y, 65504.0f); Lb = fminf(Lb + ezw.x, 65504.0f);
-    stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
   }
+  const float cdpr = cdr * kInvPi, cdpg = cdg * kInvPi, cdpb = cdb * kInvPi;
+  const float omF0r = 1.0f - F0r, omF0g = 1.0f - F0g, omF0b = 1.0f - F0b;
+  const float a2h = a2 * (0.5f * kInvPi);
+
+  // ---- direct lighting: KHR_lights_punctual point lights, Cook-Torrance GGX / Smith / Schlick ----
+  uint32_t nl = p.n_lights;
+  const uint16_t* idx = nullptr;
+  if (p.tile_counts != nullptr) {
+    const uint32_t tile = ty * p.tiles_x + tx;
+    nl = min(__ldg(p.tile_counts + tile), p.max_per_tile);
+    idx = p.tile_indices + size_t(tile) * p.max_per_tile;
+  }
+  float dr = 0.f, dg = 0.f, db = 0.f;  // summed separately, in light order, like the oracle
+  for (uint32_t base = 0; base < nl; base += kLightChunk) {
+    const uint32_t cnt = min(nl - base, uint32_t(kLightChunk));
+    if (base > 0) __syncthreads();
+    if (threadIdx.x < cnt) {
+      const uint32_t li = idx ? uint32_t(__ldg(idx + base + threadIdx.x)) : base + threadIdx.x;
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * li);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * li + 1);
+      s_pos[threadIdx.x] = make_float4(a.x, a.y, a.z, a.w > 0.0f ? __fdividef(1.0f, a.w * a.w) : 0.0f);
+      s_col[threadIdx.x] = make_float4(b.x * b.w, b.y * b.w, b.z * b.w, 0.0f);
+    }
+    __syncthreads();
+    if (!lit) continue;
+    for (uint32_t i = 0; i < cnt; ++i) {
+      const float4 lp = s_pos[i];
+      const float dx = lp.x - P.x, dy = lp.y - P.y, dz = lp.z - P.z;
+      const float d2 = fmaxf(dx * dx + dy * dy + dz * dz, 1e-8f);
+      const float invd = rsqrtf(d2);
+      const float NoL = sat((N.x * dx + N.y * dy + N.z * dz) * invd);
+      const float q = d2 * lp.w;                      // (d/range)^2; 0 for unlimited range
+      const float att = invd * invd * sat(1.0f - q * q);  // inverse square * clamp(1 - (d/range)^4, 0, 1)
+      const float w = att * NoL;
+      if (w > 0.0f) {
+        const float hx = fmaf(dx, invd, V.x), hy = fmaf(dy, invd, V.y), hz = fmaf(dz, invd, V.z);  // V + L
+        const float hinv = rsqrtf(hx * hx + hy * hy + hz * hz);
+        const float NoH = sat((N.x * hx + N.y * hy + N.z * hz) * hinv);
+        const float VoH = sat((V.x * hx + V.y * hy + V.z * hz) * hinv);
+        // 1 - NoH^2 = |N x H|^2 (Lagrange): NoH^2 (a2 - 1) + 1 cancels catastrophically for smooth surfaces
+        const float kx = N.y * hz - N.z * hy, ky = N.z * hx - N.x * hz, kz = N.x * hy - N.y * hx;
+        const float dd = (kx * kx + ky * ky + kz * kz) * (hinv * hinv) + NoH * NoH * a2;
+        const float vl = NoL * NoL * oma2 + a2;
+        const float den = NoL * visV + NoV * (vl * rsqrtf(vl));
+        const float dv = __fdividef(a2h, dd * dd * den);  // D * Vis = a2/(pi dd^2) * 0.5/den
+        const float t = 1.0f - VoH, t2 = t * t, fc = t2 * t2 * t;
+        const float Fr = fmaf(omF0r, fc, F0r), Fg = fmaf(omF0g, fc, F0g), Fb = fmaf(omF0b, fc, F0b);
+        const float4 lc = s_col[i];
+        dr = fmaf(fmaf(Fr, dv, cdpr - cdpr * Fr), lc.x * w, dr);
+        dg = fmaf(fmaf(Fg, dv, cdpg - cdpg * Fg), lc.y * w, dg);
+        db = fmaf(fmaf(Fb, dv, cdpb - cdpb * Fb), lc.z * w, db);
+      }
+    }
+  }
+  if (!inside) return;
+  uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8;
+  if (!lit) {
+    stg_stream8(outp, make_uint2(0u, 0u));
+    return;
+  }
+  // ---- ambient: split-sum image-based lighting (Karis 2013) ----
+  float ar = 0.f, ag = 0.f, ab = 0.f;
+  if (p.has_ibl) {
+    const float3 R = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
+    const RGB irr = cube_sample(p.irr, N, 0.0f);
+    const RGB pre = cube_sample(p.pref, R, rough * float(p.pref.nmips - 1));
+    const float2 sb = lut_sample(p.lut, int(p.lut_res), NoV, rough);
+    ar = (irr.r * cdr + pre.r * (F0r * sb.x + sb.y)) * occ;
+    ag = (irr.g * cdg + pre.g * (F0g * sb.x + sb.y)) * occ;
+    ab = (irr.b * cdb + pre.b * (F0b * sb.x + sb.y)) * occ;
+  }
+  // oracle order: (direct + ambient) + emissive
+  Lr = fminf((dr + ar) + Lr, 65504.0f); Lg = fminf((dg + ag) + Lg, 65504.0f); Lb = fminf((db + ab) + Lb, 65504.0f);
+  stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
 }
 
 // ---- K3c: per 16x16 tile, world-space AABB of the tile's non-cleared positions, then every light
@@ -236,7 +252,7 @@ using namespace pbrcu;
 extern "C" int pbrcu_light_tiles_alloc(pbrcu_ctx* ctx, uint32_t width, uint32_t height, uint32_t max_per_tile,
                                        pbrcu_light_tiles* out) {
   PBRCU_REQUIRE(ctx && out, "NULL argument");
-  PBRCU_REQUIRE(width > 0 && height > 0 && max_per_tile > 0 && max_per_tile <= uint32_t(kMaxSmemLights), "extent or max_per_tile out of range");
+  PBRCU_REQUIRE(width > 0 && height > 0 && max_per_tile > 0 && max_per_tile <= uint32_t(kMaxLights), "extent or max_per_tile out of range");
   out->tiles_x = (width + kTile - 1) / kTile;
   out->tiles_y = (height + kTile - 1) / kTile;
   out->max_per_tile = max_per_tile;
@@ -287,7 +303,6 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
   p.pitch8 = g->pitch8; p.pitch4 = g->pitch4; p.out_pitch = out_pitch;
   p.x0 = rect.x0; p.y0 = rect.y0; p.x1 = rect.x0 + rect.w; p.y1 = rect.y0 + rect.h;
   p.tx0 = rect.x0 / kTile; p.ty0 = rect.y0 / kTile;
-  p.ntx = (p.x1 + kTile - 1) / kTile - p.tx0; p.nty = (p.y1 + kTile - 1) / kTile - p.ty0;
   p.cx = cam_pos[0]; p.cy = cam_pos[1]; p.cz = cam_pos[2];
   p.lights = lights_dev; p.n_lights = n_lights;
   if (tiles) {
@@ -304,9 +319,7 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
     p.lut = reinterpret_cast<const float2*>(ibl->lut);
     p.lut_res = ibl->lut_res;
   }
-  const uint32_t ntiles = p.ntx * p.nty;
-  uint32_t grid = uint32_t(ctx->sm_count) * 4;
-  if (grid > ntiles) grid = ntiles;
+  dim3 grid((p.x1 + kTile - 1) / kTile - p.tx0, (p.y1 + kTile - 1) / kTile - p.ty0);
   shade_ggx_kernel<<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
   return launch_check("shade_ggx_kernel");
 }
