@@ -174,3 +174,4 @@ def f3(x, y, z):
 WHOLE = Rect(0, 0, 0, 0)
 
 from .device import Device, DeviceBuffer  # noqa: E402  (numpy-level conveniences for tests / bench)
+from . import partition  # noqa: E402

@@ -1,0 +1,53 @@
+"""Host-side partitioning of the hot path across the GPUs of one box.
+
+Every unit of the path is independent (pixels, views, cube texels), so ranks own disjoint, contiguous
+blocks and there is NO data-path collective; NCCL (through torch.distributed) is used only to gather
+finished tiles / faces when a caller wants the whole image on every rank."""
+from __future__ import annotations
+
+
+def split_range(n: int, parts: int, index: int) -> tuple[int, int]:
+    """[begin, end) of block `index` when `n` units are cut into `parts` near-equal contiguous blocks
+    (the same rule the C ABI uses for prefilter shards: begin = n*index // parts)."""
+    if parts < 1 or not (0 <= index < parts):
+        raise ValueError(f"bad partition {index}/{parts}")
+    return n * index // parts, n * (index + 1) // parts
+
+
+def row_band(height: int, world: int, rank: int, align: int = 1) -> tuple[int, int]:
+    """Rows [y0, y1) of a frame owned by `rank` (single-frame configs 2 and 4).  With align=16 the bands
+    start on light-tile boundaries so per-band light clustering equals whole-frame clustering."""
+    units = (height + align - 1) // align
+    b, e = split_range(units, world, rank)
+    return min(b * align, height), min(e * align, height)
+
+
+def view_block(n_views: int, world: int, rank: int) -> tuple[int, int]:
+    """Views [v0, v1) owned by `rank` (batched multi-view, config 5)."""
+    return split_range(n_views, world, rank)
+
+
+def gather_rows(tensor, y0: int, y1: int, world: int, height: int, dist=None):
+    """All-gathers row bands of a (H, ...) tensor so every rank holds the full frame.  `tensor` is the
+    full-size buffer with only rows [y0, y1) valid on this rank.  Uses all_gather when the bands are
+    equal-sized, broadcast per band otherwise.  Works with any torch.distributed backend (NCCL on the
+    GPUs, gloo in the CPU tests)."""
+    if dist is None or world == 1:
+        return tensor
+    bands = [row_band(height, world, r) for r in range(world)]
+    sizes = {e - b for b, e in bands}
+    if len(sizes) == 1:
+        dist.all_gather_into_tensor(tensor, tensor[y0:y1].contiguous()) if hasattr(dist, "all_gather_into_tensor") and tensor.is_cuda \
+            else _gather_list(tensor, bands, y0, y1, dist)
+    else:
+        for r, (b, e) in enumerate(bands):
+            if e > b:
+                dist.broadcast(tensor[b:e], src=r)
+    return tensor
+
+
+def _gather_list(tensor, bands, y0, y1, dist):
+    parts = [tensor[b:e].clone() for b, e in bands]
+    dist.all_gather(parts, tensor[y0:y1].contiguous())
+    for (b, e), p in zip(bands, parts):
+        tensor[b:e] = p

@@ -78,6 +78,10 @@ class Oracle:
         L.pbro_aces_tonemap.argtypes = [vp, vp]
         L.pbro_gamma_correct.argtypes = [vp, cf, vp]
         L.pbro_max_threads.restype = ci
+        L.pbro_cube_texel_dir.argtypes = [ci, ci, ci, ci, vp]
+        L.pbro_cube_dir_to_face_uv.argtypes = [vp, vp, vp, vp]
+        L.pbro_brdf_lut_texel.argtypes = [ci, ci, ci, ci, vp]
+        L.pbro_tonemap_pixel.argtypes = [vp, vp]
 
     def max_threads(self) -> int:
         return self.lib.pbro_max_threads()

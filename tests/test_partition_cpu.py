@@ -1,0 +1,57 @@
+"""CPU tests of the multi-GPU host logic: partitions are disjoint and complete, and a world_size-2 gloo
+run of the gather reassembles a frame from per-rank row bands (the N>1 path of bench.py, minus the GPU)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+
+def test_partitions_cover_exactly(pbr):
+    P = pbr.partition
+    for n in (1, 7, 256, 2160, 4320, 12288):
+        for world in (1, 2, 3, 4, 8):
+            blocks = [P.split_range(n, world, r) for r in range(world)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            assert all(blocks[i][1] == blocks[i + 1][0] for i in range(world - 1))
+            assert max(e - b for b, e in blocks) - min(e - b for b, e in blocks) <= 1
+    assert P.row_band(2160, 8, 3) == (810, 1080)
+    bands = [P.row_band(2160, 8, r, align=16) for r in range(8)]
+    assert bands[0][0] == 0 and bands[-1][1] == 2160 and all(b % 16 == 0 for b, _ in bands)
+    assert P.view_block(256, 8, 7) == (224, 256)
+    with pytest.raises(ValueError):
+        P.split_range(10, 2, 2)
+
+
+def _worker(rank, world, port, height, q):
+    import torch
+    import torch.distributed as dist
+    import pbr_b200 as pbr
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    y0, y1 = pbr.partition.row_band(height, world, rank)
+    frame = torch.zeros(height, 8, 4, dtype=torch.int32)
+    full = torch.arange(height * 32, dtype=torch.int32).reshape(height, 8, 4)
+    frame[y0:y1] = full[y0:y1]  # "shade" only the rows this rank owns
+    pbr.partition.gather_rows(frame, y0, y1, world, height, dist)
+    t = torch.tensor([float(rank + 1)])
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)  # the max-over-ranks timing reduction of bench.py
+    q.put((rank, bool(torch.equal(frame, full)), float(t.item())))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("height", [64, 37])
+def test_gloo_world2_gather(height):
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, height, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == [(0, True, 2.0), (1, True, 2.0)]
