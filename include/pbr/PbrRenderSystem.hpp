@@ -1,0 +1,114 @@
+// pbr/PbrRenderSystem.hpp -- the shading render system, same public surface as the reference's
+// (src/pbr_engine/engine/pbr/PbrRenderSystem.hpp:13-55):
+//     PbrRenderSystem(core::SharedGpuHandle gpu, PbrRenderSystemCreateInfo info);
+//     auto allocateGBuffer(IAllocator&, vk::Extent2D) -> GBuffer;
+//     auto render(vk::CommandBuffer, Scene const&, GBuffer const&, Image2D const& renderTarget,
+//                 vk::Extent2D renderExtent) -> void;
+// render() in the reference records a rasterised geometry pass that fills the G-buffer and a
+// full-screen lighting pass that shades it (PbrRenderSystem.cpp:357-365).  Here the lighting pass is a
+// CUDA kernel enqueued on the command buffer's stream:
+//   ShadingModel::BlinnPhong  (default) = assets/shaders/pbr/lighting.glsl, bit-for-bit the reference
+//   ShadingModel::MetallicRoughness     = GGX + point lights + IBL (Tier B, no reference counterpart)
+// The geometry pass runs when the scene holds mesh nodes; a scene without meshes shades whatever the
+// caller put into the G-buffer (the deferred hot path on its own).
+#pragma once
+#include "pbr/Environment.hpp"
+#include "pbr/GBuffer.hpp"
+#include "pbr/Scene.hpp"
+
+#include <memory>
+#include <stdexcept>
+
+namespace pbr {
+enum class ShadingModel { BlinnPhong, MetallicRoughness };
+
+struct PbrRenderSystemCreateInfo {
+  vk::PipelineShaderStageCreateInfo geometryVertexShader {};
+  vk::PipelineShaderStageCreateInfo geometryFragmentShader {};
+  vk::PipelineShaderStageCreateInfo lightingVertexShader {};
+  vk::PipelineShaderStageCreateInfo lightingFragmentShader {};
+  ShadingModel shadingModel {ShadingModel::BlinnPhong};  // CUDA addition
+};
+
+class PbrRenderSystem {
+public:
+  static constexpr auto LIGHTING_PASS_OUTPUT_FORMAT = vk::Format::eR16G16B16A16Sfloat;
+
+private:
+  core::SharedGpuHandle _gpu;
+  PbrRenderSystemCreateInfo _info;
+  std::shared_ptr<Environment const> _environment;
+  Allocation _lightsDevice;  // grown on demand
+  std::size_t _lightsCapacity {};
+
+public:
+  PbrRenderSystem(core::SharedGpuHandle gpu, PbrRenderSystemCreateInfo info) : _gpu(std::move(gpu)), _info(info) {}
+
+  [[nodiscard]] auto allocateGBuffer(IAllocator& allocator, vk::Extent2D extent) -> GBuffer {
+    return GBuffer {allocator, extent, _info.shadingModel == ShadingModel::MetallicRoughness};
+  }
+
+  auto setEnvironment(std::shared_ptr<Environment const> env) -> void { _environment = std::move(env); }
+
+  auto render(vk::CommandBuffer cmdBuffer, Scene const& scene, GBuffer const& gBuffer, Image2D const& renderTarget,
+              vk::Extent2D renderExtent) -> void {
+    recordGeometryPass(cmdBuffer, scene, gBuffer);
+    recordLightingPass(cmdBuffer, scene, gBuffer, renderTarget, vk::Rect2D {.offset = {}, .extent = renderExtent});
+  }
+
+private:
+  auto recordGeometryPass(vk::CommandBuffer, Scene const& scene, GBuffer const&) -> void {
+    for (auto const& node : scene.iterateAllNodes())
+      if (node.getMesh())
+        throw std::runtime_error(
+            "pbr::PbrRenderSystem::render: the CUDA geometry pass (rasteriser, SURVEY 8(f) next-1) is not "
+            "built yet; shade a caller-filled G-buffer with a scene that holds no mesh nodes");
+  }
+
+  auto recordLightingPass(vk::CommandBuffer cmdBuffer, Scene const& scene, GBuffer const& gBuffer,
+                          Image2D const& renderTo, vk::Rect2D renderArea) -> void {
+    if (renderTo.getFormat() != LIGHTING_PASS_OUTPUT_FORMAT)
+      throw std::runtime_error("pbr::PbrRenderSystem::render: render target must be R16G16B16A16_SFLOAT");
+    auto* ctx = _gpu->getContext();
+    auto* stream = cmdBuffer.stream();
+    auto const target = renderTo.getImage();
+    auto const ext = gBuffer.getExtent();
+    pbrcu_rect rect {0, 0, renderArea.extent.width < ext.width ? renderArea.extent.width : ext.width,
+                     renderArea.extent.height < ext.height ? renderArea.extent.height : ext.height};
+    // loadOp = clear to 0 over the render area (PbrRenderSystem.cpp:470-480) -- and nothing else is
+    // drawn when the scene has no camera (:486-499)
+    auto const camera = scene.findCamera();
+    if (!camera) {
+      for (std::uint32_t y = 0; y < rect.h; ++y)
+        core::check(pbrcu_memset(static_cast<char*>(target.data) + y * target.pitch, 0, std::size_t(rect.w) * 8, stream), "PbrRenderSystem: clear");
+      return;
+    }
+    if (rect.w == 0 || rect.h == 0) return;
+    auto const g = gBuffer.raw();
+    auto const pos = camera.value()->get().position;
+    float const cam[3] = {pos.x, pos.y, pos.z};
+    if (_info.shadingModel == ShadingModel::BlinnPhong) {
+      core::check(pbrcu_lighting_blinnphong(ctx, &g, cam, rect, target.data, target.pitch, stream), "PbrRenderSystem: lighting pass");
+      return;
+    }
+    if (!gBuffer.isExtended())
+      throw std::runtime_error("pbr::PbrRenderSystem::render: MetallicRoughness shading needs an extended G-buffer");
+    auto const lights = scene.getLights();
+    if (lights.size() > _lightsCapacity) {
+      _lightsDevice = Allocation {};
+      void* p = nullptr;
+      core::check(pbrcu_malloc(ctx, lights.size() * sizeof(pbrcu_light), &p), "PbrRenderSystem: light buffer");
+      _lightsDevice = Allocation {_gpu, p, lights.size() * sizeof(pbrcu_light), false};
+      _lightsCapacity = lights.size();
+    }
+    if (!lights.empty())
+      core::check(pbrcu_memcpy_h2d(_lightsDevice.get(), lights.data(), lights.size() * sizeof(pbrcu_light), stream), "PbrRenderSystem: light upload");
+    pbrcu_ibl ibl {};
+    if (_environment) ibl = _environment->raw();
+    core::check(pbrcu_shade_ggx_ibl(ctx, &g, cam, static_cast<pbrcu_light const*>(_lightsDevice.get()),
+                                    static_cast<std::uint32_t>(lights.size()), nullptr, _environment ? &ibl : nullptr, rect,
+                                    target.data, target.pitch, stream),
+                "PbrRenderSystem: GGX shading pass");
+  }
+};
+}  // namespace pbr
