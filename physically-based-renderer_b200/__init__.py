@@ -51,7 +51,7 @@ class Light(C.Structure):
 class Ibl(C.Structure):
     _fields_ = [("irradiance", C.c_void_p), ("irr_res", C.c_uint32),
                 ("prefiltered", C.c_void_p), ("pref_res", C.c_uint32), ("pref_mips", C.c_uint32),
-                ("lut", C.c_void_p), ("lut_res", C.c_uint32)]
+                ("lut", C.c_void_p), ("lut_res", C.c_uint32), ("accel", C.c_void_p)]
 
 
 class LightTiles(C.Structure):
@@ -103,6 +103,9 @@ _SIGNATURES = {
     "pbrcu_cube_mip_offset": (_sz, [_u32, _u32]),
     "pbrcu_shade_ggx_ibl": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, _vp]),
     "pbrcu_shade_frame_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _f3, _vp, _u32, _PI, _vp, _u32, _vp]),
+    "pbrcu_ibl_accel_build": (_i, [_vp, _PI, C.POINTER(_vp), _vp]),
+    "pbrcu_ibl_accel_free": (_i, [_vp, _vp]),
+    "pbrcu_ibl_accel_bytes": (_sz, [_vp]),
     "pbrcu_light_tiles_alloc": (_i, [_vp, _u32, _u32, _u32, _PT]),
     "pbrcu_light_tiles_free": (_i, [_vp, _PT]),
     "pbrcu_cluster_lights": (_i, [_vp, _PG, _vp, _u32, _PT, _vp]),
@@ -117,7 +120,7 @@ _SIGNATURES = {
 }
 
 _NO_STATUS = {"pbrcu_version", "pbrcu_last_error", "pbrcu_ctx_destroy", "pbrcu_ctx_sm_count",
-              "pbrcu_cube_chain_texels", "pbrcu_cube_mip_offset"}
+              "pbrcu_cube_chain_texels", "pbrcu_cube_mip_offset", "pbrcu_ibl_accel_bytes"}
 
 
 class Lib:

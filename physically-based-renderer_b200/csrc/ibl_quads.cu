@@ -1,0 +1,85 @@
+// ibl_quads.cu -- builds the footprint-record copies of the IBL textures (see ibl_quads.cuh).
+// HBM-bound gather: every record reads 4 texels (3 of them L1/L2 hits from neighbouring threads) and
+// writes 32 bytes; 2048^2 x 12 mips = 33.5 M records = 1.07 GB written.
+#include "ibl_quads.cuh"
+
+#include <new>
+
+namespace pbrcu {
+
+// faces of one level: n = 6*res*res records (n_faces*res*res in general)
+__global__ void __launch_bounds__(256) build_quads8_kernel(const uint2* __restrict__ src, uint4* __restrict__ dst, int res, size_t n) {
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const int x = int(i % res);
+    const int y = int((i / res) % res);
+    const size_t face = i / (size_t(res) * res);
+    const int x1 = min(x + 1, res - 1), y1 = min(y + 1, res - 1);
+    const uint2* f = src + face * size_t(res) * res;
+    const uint2 t00 = __ldg(f + size_t(y) * res + x), t10 = __ldg(f + size_t(y) * res + x1);
+    const uint2 t01 = __ldg(f + size_t(y1) * res + x), t11 = __ldg(f + size_t(y1) * res + x1);
+    dst[2 * i] = make_uint4(t00.x, t00.y, t10.x, t10.y);
+    dst[2 * i + 1] = make_uint4(t01.x, t01.y, t11.x, t11.y);
+  }
+}
+
+static int build_level(const uint2* src, uint4* dst, int res, int faces, int sms, cudaStream_t st) {
+  const size_t n = size_t(faces) * res * res;
+  const size_t want = (n + 255) / 256;
+  const unsigned blocks = unsigned(want < size_t(sms) * 16 ? want : size_t(sms) * 16);
+  build_quads8_kernel<<<blocks, 256, 0, st>>>(src, dst, res, n);
+  return launch_check("build_quads8_kernel");
+}
+
+}  // namespace pbrcu
+
+using namespace pbrcu;
+
+extern "C" int pbrcu_ibl_accel_free(pbrcu_ctx* ctx, pbrcu_ibl_accel* a) {
+  (void)ctx;
+  if (!a) return PBRCU_OK;
+  if (a->pref) cudaFree(a->pref);
+  if (a->irr) cudaFree(a->irr);
+  if (a->lut) cudaFree(a->lut);
+  delete a;
+  return PBRCU_OK;
+}
+
+extern "C" size_t pbrcu_ibl_accel_bytes(const pbrcu_ibl_accel* a) { return a ? a->bytes : 0; }
+
+extern "C" int pbrcu_ibl_accel_build(pbrcu_ctx* ctx, const pbrcu_ibl* ibl, pbrcu_ibl_accel** out, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && ibl && out, "NULL argument");
+  PBRCU_REQUIRE(ibl->irradiance && ibl->prefiltered && ibl->lut, "ibl texture is NULL");
+  PBRCU_REQUIRE(ibl->irr_res > 0 && ibl->irr_res <= 4096 && ibl->pref_res > 0 && ibl->pref_res <= 4096 && ibl->pref_mips >= 1 &&
+                    ibl->pref_mips <= 16 && (ibl->pref_res >> (ibl->pref_mips - 1)) >= 1 && ibl->lut_res > 0 && ibl->lut_res <= 4096,
+                "bad ibl shape");
+  *out = nullptr;
+  pbrcu_ibl_accel* a = new (std::nothrow) pbrcu_ibl_accel();
+  if (!a) return PBRCU_ERR_NOMEM;
+  a->pref_res = ibl->pref_res; a->pref_mips = ibl->pref_mips; a->irr_res = ibl->irr_res; a->lut_res = ibl->lut_res;
+  const size_t n_pref = cube_mip_offset(ibl->pref_res, ibl->pref_mips);
+  const size_t n_irr = size_t(6) * ibl->irr_res * ibl->irr_res, n_lut = size_t(ibl->lut_res) * ibl->lut_res;
+  a->bytes = (n_pref + n_irr + n_lut) * 32;
+  int rc;
+  if ((rc = pbrcu_malloc(ctx, n_pref * 32, reinterpret_cast<void**>(&a->pref))) ||
+      (rc = pbrcu_malloc(ctx, n_irr * 32, reinterpret_cast<void**>(&a->irr))) ||
+      (rc = pbrcu_malloc(ctx, n_lut * 32, reinterpret_cast<void**>(&a->lut)))) {
+    pbrcu_ibl_accel_free(ctx, a);
+    return rc;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  for (uint32_t m = 0; m < ibl->pref_mips; ++m) {
+    const size_t off = cube_mip_offset(ibl->pref_res, m);
+    if ((rc = build_level(static_cast<const uint2*>(ibl->prefiltered) + off, a->pref + 2 * off, int(ibl->pref_res >> m), 6, ctx->sm_count, st))) {
+      pbrcu_ibl_accel_free(ctx, a);
+      return rc;
+    }
+  }
+  // the LUT's float2 texels are 8 bytes like an RGBA16F texel: the same gather builds its records
+  if ((rc = build_level(static_cast<const uint2*>(ibl->irradiance), a->irr, int(ibl->irr_res), 6, ctx->sm_count, st)) ||
+      (rc = build_level(reinterpret_cast<const uint2*>(ibl->lut), a->lut, int(ibl->lut_res), 1, ctx->sm_count, st))) {
+    pbrcu_ibl_accel_free(ctx, a);
+    return rc;
+  }
+  *out = a;
+  return PBRCU_OK;
+}

@@ -1,0 +1,87 @@
+// ibl_quads.cuh -- "footprint record" layout of the IBL textures for the GGX shading kernel (K3).
+// Record of texel (x, y) of a face = the four texels {(x,y), (x+1,y), (x,y+1), (x+1,y+1)} with x+1 / y+1
+// clamped to the face edge, 4 x RGBA16F = 32 bytes (LUT: 4 x float2 = 32 bytes).  A bilinear tap with
+// clamp-to-edge is then one 256-bit load: with fx = max(u*res - 0.5, 0) the footprint origin is
+// floor(fx) in [0, res-1] and the weights frac(fx) are 0 where the oracle's clamp makes both taps equal,
+// so the result is bit-identical to cube.cuh's four-load face_bilinear.
+#pragma once
+#include "cube.cuh"
+
+struct pbrcu_ibl_accel {
+  uint4* pref;      // chain_texels(pref_res, pref_mips) records, same level/face/row order as the chain
+  uint4* irr;       // 6*irr_res^2 records
+  uint4* lut;       // lut_res^2 records of 4 x float2
+  uint32_t pref_res, pref_mips, irr_res, lut_res;
+  size_t bytes;
+};
+
+namespace pbrcu {
+
+struct Quad8 { uint32_t w[8]; };
+
+// one 256-bit load; the records are re-read by neighbouring pixels, so let them allocate in L1
+__device__ __forceinline__ Quad8 ldg_quad(const uint4* p) {
+  Quad8 q;
+  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(q.w[0]), "=r"(q.w[1]), "=r"(q.w[2]), "=r"(q.w[3]), "=r"(q.w[4]), "=r"(q.w[5]), "=r"(q.w[6]), "=r"(q.w[7])
+               : "l"(p));
+  return q;
+}
+
+// f16 halves of a packed word as f32, and the mixed-precision difference b(f16) - a(f32) in ONE
+// instruction (sm_100 FHADD): the rounding is the same single rounding as cvt + sub.
+__device__ __forceinline__ float h_lo(uint32_t w) {
+  float f;
+  asm("{.reg .b16 l,h; mov.b32 {l,h},%1; cvt.f32.f16 %0,l;}" : "=f"(f) : "r"(w));
+  return f;
+}
+__device__ __forceinline__ float h_hi(uint32_t w) {
+  float f;
+  asm("{.reg .b16 l,h; mov.b32 {l,h},%1; cvt.f32.f16 %0,h;}" : "=f"(f) : "r"(w));
+  return f;
+}
+__device__ __forceinline__ float hsub_lo(uint32_t w, float a) {
+  float f;
+  asm("{.reg .b16 l,h; mov.b32 {l,h},%1; sub.rn.f32.f16 %0,l,%2;}" : "=f"(f) : "r"(w), "f"(a));
+  return f;
+}
+__device__ __forceinline__ float hsub_hi(uint32_t w, float a) {
+  float f;
+  asm("{.reg .b16 l,h; mov.b32 {l,h},%1; sub.rn.f32.f16 %0,h,%2;}" : "=f"(f) : "r"(w), "f"(a));
+  return f;
+}
+
+// footprint origin and weights of a bilinear tap at normalised (u, v) in a res x res face
+struct Tap { float tx, ty; int idx; };
+__device__ __forceinline__ Tap make_tap(float u, float v, float resf) {
+  const float fx = fmaxf(fmaf(u, resf, -0.5f), 0.0f), fy = fmaxf(fmaf(v, resf, -0.5f), 0.0f);
+  const float x0 = floorf(fx), y0 = floorf(fy);
+  Tap t;
+  t.tx = fx - x0;
+  t.ty = fy - y0;
+  t.idx = __float2int_rz(fmaf(y0, resf, x0));  // exact: < 2^24 for res <= 4096
+  return t;
+}
+
+// bilinear of the RGB channels of one record: lerp(lerp(t00,t10,tx), lerp(t01,t11,tx), ty), lerp(a,b,t) = fma(t,b-a,a)
+__device__ __forceinline__ RGB quad_bilinear_rgb(const Quad8& q, float tx, float ty) {
+  RGB o;
+  {
+    const float a = h_lo(q.w[0]), c = h_lo(q.w[4]);
+    const float top = fmaf(tx, hsub_lo(q.w[2], a), a), bot = fmaf(tx, hsub_lo(q.w[6], c), c);
+    o.r = fmaf(ty, bot - top, top);
+  }
+  {
+    const float a = h_hi(q.w[0]), c = h_hi(q.w[4]);
+    const float top = fmaf(tx, hsub_hi(q.w[2], a), a), bot = fmaf(tx, hsub_hi(q.w[6], c), c);
+    o.g = fmaf(ty, bot - top, top);
+  }
+  {
+    const float a = h_lo(q.w[1]), c = h_lo(q.w[5]);
+    const float top = fmaf(tx, hsub_lo(q.w[3], a), a), bot = fmaf(tx, hsub_lo(q.w[7], c), c);
+    o.b = fmaf(ty, bot - top, top);
+  }
+  return o;
+}
+
+}  // namespace pbrcu

@@ -3,15 +3,17 @@
 // K3c the per-tile light lists.  No reference counterpart; definition:
 // glTF 2.0 Appendix B + KHR_lights_punctual + Karis 2013 (restated for the CPU checker as pbro_shade_pixel).
 //
-// One CTA = one 16x16 pixel tile (persistent loop over tiles): a warp reads two 128-byte row segments
-// per plane, the tile's light list is staged once in shared memory, and the IBL fetches of
-// neighbouring pixels hit the same L1 lines.
-#include "cube.cuh"
+// Persistent CTAs (4 per SM) walk the 16x16 pixel tiles of the rect.  The five G-buffer planes of the
+// NEXT tile are staged into shared memory with cp.async while the current tile is shaded, so the DRAM
+// latency of the streaming reads never sits on a warp's critical path; the tile's light list is staged
+// in shared memory; the IBL footprint records of a pixel are prefetched into L1 before its light loop.
+#include "ibl_quads.cuh"
 
 namespace pbrcu {
 
 constexpr int kTile = PBRCU_TILE;
 constexpr int kShadeThreads = kTile * kTile;
+constexpr int kShadeCtasPerSm = 3;  // 85 registers: the four IBL records stay in registers across the light loop
 constexpr int kMaxLights = 1024;   // API limit for max_per_tile
 constexpr int kLightChunk = 128;   // lights staged in shared memory at a time
 constexpr float kInvPi = 0.31830988618379067154f;
@@ -21,7 +23,8 @@ struct ShadeParams {
   uint8_t* out;
   size_t pitch8, pitch4, out_pitch;
   uint32_t x0, y0, x1, y1;        // rect in image coordinates (x1, y1 exclusive)
-  uint32_t tx0, ty0;              // first tile of the grid (blockIdx is relative to it)
+  uint32_t tx0, ty0;              // first tile of the rect
+  uint32_t ntx, ntiles;           // tiles per row of the rect, tiles in the rect
   float cx, cy, cz;
   const pbrcu_light* lights;
   uint32_t n_lights;
@@ -32,6 +35,7 @@ struct ShadeParams {
   CubeChain irr, pref;
   const float2* lut;
   uint32_t lut_res;
+  const uint4 *q_pref, *q_irr, *q_lut;  // footprint records (pbrcu_ibl_accel); NULL: plain textures
 };
 
 __device__ __forceinline__ float2 lut_sample(const float2* lut, int res, float u, float v) {
@@ -48,67 +52,76 @@ __device__ __forceinline__ float2 lut_sample(const float2* lut, int res, float u
 }
 
 __device__ __forceinline__ float sat(float x) { return __saturatef(x); }
+// single MUFU ops (no denormal fix-up code: every argument here is a normal number or the result is
+// multiplied by an exact 0)
+__device__ __forceinline__ float rsq(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
-// One CTA = one 16x16 pixel tile (blockIdx = tile).  Lights are staged kLightChunk at a time in shared
-// memory in a pre-digested form: {position, 1/range^2 (0 = unlimited)} and {colour * intensity}.
-__global__ void __launch_bounds__(kShadeThreads, 4) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
-  __shared__ float4 s_pos[kLightChunk];
-  __shared__ float4 s_col[kLightChunk];
-  const uint32_t tx = p.tx0 + blockIdx.x, ty = p.ty0 + blockIdx.y;
+// The four records a pixel's ambient term needs: irradiance(N), prefiltered(R) at two levels, LUT(NoV, rough).
+struct IblTaps {
+  int i_irr, i_p0, i_p1, i_lut;
+  float irr_tx, irr_ty, p0_tx, p0_ty, p1_tx, p1_ty, lut_tx, lut_ty, lod_f;
+};
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+__device__ __forceinline__ IblTaps make_ibl_taps(const ShadeParams& p, float3 N, float3 R, float NoV, float rough) {
+  IblTaps t;
+  int face;
+  float u, v;
+  cube_dir_to_face_uv(N, face, u, v);
+  const int ires = int(p.irr.base_res);
+  Tap a = make_tap(u, v, float(ires));
+  t.i_irr = face * ires * ires + a.idx; t.irr_tx = a.tx; t.irr_ty = a.ty;
+  cube_dir_to_face_uv(R, face, u, v);
+  const float lod = fminf(rough * float(p.pref.nmips - 1), float(p.pref.nmips - 1));  // rough >= 0.045 > 0
+  const float l0f = floorf(lod);
+  t.lod_f = lod - l0f;
+  const int l0 = int(l0f), l1 = min(l0 + 1, int(p.pref.nmips) - 1);
+  const int r0 = int(p.pref.base_res >> l0), r1 = int(p.pref.base_res >> l1);
+  a = make_tap(u, v, float(r0));
+  t.i_p0 = int(p.pref.mip_offset[l0]) + face * r0 * r0 + a.idx; t.p0_tx = a.tx; t.p0_ty = a.ty;
+  a = make_tap(u, v, float(r1));
+  t.i_p1 = int(p.pref.mip_offset[l1]) + face * r1 * r1 + a.idx; t.p1_tx = a.tx; t.p1_ty = a.ty;
+  a = make_tap(NoV, rough, float(p.lut_res));
+  t.i_lut = a.idx; t.lut_tx = a.tx; t.lut_ty = a.ty;
+  return t;
+}
+
+// ---- cp.async staging of one pixel's five texels into this thread's shared-memory slots ----
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(uint32_t(__cvta_generic_to_shared(smem))), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(uint32_t(__cvta_generic_to_shared(smem))), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct TileStage {
+  uint2 px[4][kShadeThreads];   // pos, nrm, alb, emi
+  uint32_t orm[kShadeThreads];
+};
+
+__device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, uint32_t tile) {
+  const uint32_t ty = p.ty0 + tile / p.ntx, tx = p.tx0 + tile % p.ntx;
   const uint32_t x = tx * kTile + (threadIdx.x % kTile), y = ty * kTile + (threadIdx.x / kTile);
-  const bool inside = x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1;
-
-  // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
-  float3 P = make_float3(0.f, 0.f, 0.f), N = P, V = P;
-  float NoVraw = 0.f, NoV = 1.f, rough = 1.f, occ = 0.f, a2 = 1.f, oma2 = 0.f, visV = 1.f, base_a = 0.f;
-  float F0r = 0.f, F0g = 0.f, F0b = 0.f, cdr = 0.f, cdg = 0.f, cdb = 0.f;
-  float Lr = 0.f, Lg = 0.f, Lb = 0.f;
-  bool lit = false;
-  if (inside) {
+  if (x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1) {
     const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8;
-    const uint2 tp = ldg_stream8(p.pos + o8), tn = ldg_stream8(p.nrm + o8), ta = ldg_stream8(p.alb + o8);
-    const uint2 te = ldg_stream8(p.emi + o8);
-    const uint32_t to = ldg_stream4(p.orm + size_t(y) * p.pitch4 + size_t(x) * 4);
-    const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
-    lit = !(nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f);  // all-zero normal = cleared texel
-    if (lit) {
-      const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
-      P = make_float3(pxy.x, pxy.y, pzw.x);
-      N = normalize3(make_float3(nxy.x, nxy.y, nzw.x));
-      V = normalize3(make_float3(p.cx - P.x, p.cy - P.y, p.cz - P.z));
-      NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
-      NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
-      const float base_r = unorm16_lo(ta.x), base_g = unorm16_hi(ta.x), base_b = unorm16_lo(ta.y);
-      base_a = unorm16_hi(ta.y);
-      occ = float(to & 0xFFu) * (1.0f / 255.0f);
-      rough = fminf(fmaxf(float((to >> 8) & 0xFFu) * (1.0f / 255.0f), 0.045f), 1.0f);
-      const float metal = float((to >> 16) & 0xFFu) * (1.0f / 255.0f), omm = 1.0f - metal;
-      F0r = 0.04f * omm + base_r * metal; F0g = 0.04f * omm + base_g * metal; F0b = 0.04f * omm + base_b * metal;
-      cdr = base_r * omm; cdg = base_g * omm; cdb = base_b * omm;
-      const float alpha = rough * rough;
-      a2 = alpha * alpha; oma2 = 1.0f - a2;
-      const float vv = NoV * NoV * oma2 + a2;
-      visV = vv * rsqrtf(vv);
-      const float2 exy = h2_to_f2(te.x), ezw = h2_to_f2(te.y);
-      Lr = exy.x; Lg = exy.y; Lb = ezw.x;  // emissive
-    }
+    cp_async8(&st.px[1][threadIdx.x], p.nrm + o8);
+    cp_async8(&st.px[0][threadIdx.x], p.pos + o8);
+    cp_async8(&st.px[2][threadIdx.x], p.alb + o8);
+    cp_async8(&st.px[3][threadIdx.x], p.emi + o8);
+    cp_async4(&st.orm[threadIdx.x], p.orm + size_t(y) * p.pitch4 + size_t(x) * 4);
   }
-  const float cdpr = cdr * kInvPi, cdpg = cdg * kInvPi, cdpb = cdb * kInvPi;
-  const float omF0r = 1.0f - F0r, omF0g = 1.0f - F0g, omF0b = 1.0f - F0b;
-  const float a2h = a2 * (0.5f * kInvPi);
+}
 
-  // ---- direct lighting: KHR_lights_punctual point lights, Cook-Torrance GGX / Smith / Schlick ----
-  uint32_t nl = p.n_lights;
-  const uint16_t* idx = nullptr;
-  if (p.tile_counts != nullptr) {
-    const uint32_t tile = ty * p.tiles_x + tx;
-    nl = min(__ldg(p.tile_counts + tile), p.max_per_tile);
-    idx = p.tile_indices + size_t(tile) * p.max_per_tile;
-  }
-  float dr = 0.f, dg = 0.f, db = 0.f;  // summed separately, in light order, like the oracle
-  for (uint32_t base = 0; base < nl; base += kLightChunk) {
-    const uint32_t cnt = min(nl - base, uint32_t(kLightChunk));
-    if (base > 0) __syncthreads();
+template <bool ACCEL>
+__global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
+  __shared__ float4 s_pos[kLightChunk];   // {position, 1/range^2 (0 = unlimited)}
+  __shared__ float4 s_col[kLightChunk];   // {colour * intensity}
+  __shared__ TileStage s_tile[2];
+
+  auto stage_lights = [&](const uint16_t* idx, uint32_t base, uint32_t cnt) {
     if (threadIdx.x < cnt) {
       const uint32_t li = idx ? uint32_t(__ldg(idx + base + threadIdx.x)) : base + threadIdx.x;
       const float4 a = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * li);
@@ -116,57 +129,165 @@ __global__ void __launch_bounds__(kShadeThreads, 4) shade_ggx_kernel(const __gri
       s_pos[threadIdx.x] = make_float4(a.x, a.y, a.z, a.w > 0.0f ? __fdividef(1.0f, a.w * a.w) : 0.0f);
       s_col[threadIdx.x] = make_float4(b.x * b.w, b.y * b.w, b.z * b.w, 0.0f);
     }
-    __syncthreads();
-    if (!lit) continue;
-    for (uint32_t i = 0; i < cnt; ++i) {
-      const float4 lp = s_pos[i];
-      const float dx = lp.x - P.x, dy = lp.y - P.y, dz = lp.z - P.z;
-      const float d2 = fmaxf(dx * dx + dy * dy + dz * dz, 1e-8f);
-      const float invd = rsqrtf(d2);
-      const float NoL = sat((N.x * dx + N.y * dy + N.z * dz) * invd);
-      const float q = d2 * lp.w;                      // (d/range)^2; 0 for unlimited range
-      const float att = invd * invd * sat(1.0f - q * q);  // inverse square * clamp(1 - (d/range)^4, 0, 1)
-      const float w = att * NoL;
-      if (w > 0.0f) {
-        const float hx = fmaf(dx, invd, V.x), hy = fmaf(dy, invd, V.y), hz = fmaf(dz, invd, V.z);  // V + L
-        const float hinv = rsqrtf(hx * hx + hy * hy + hz * hz);
-        const float NoH = sat((N.x * hx + N.y * hy + N.z * hz) * hinv);
-        const float VoH = sat((V.x * hx + V.y * hy + V.z * hz) * hinv);
-        // 1 - NoH^2 = |N x H|^2 (Lagrange): NoH^2 (a2 - 1) + 1 cancels catastrophically for smooth surfaces
-        const float kx = N.y * hz - N.z * hy, ky = N.z * hx - N.x * hz, kz = N.x * hy - N.y * hx;
-        const float dd = (kx * kx + ky * ky + kz * kz) * (hinv * hinv) + NoH * NoH * a2;
-        const float vl = NoL * NoL * oma2 + a2;
-        const float den = NoL * visV + NoV * (vl * rsqrtf(vl));
-        const float dv = __fdividef(a2h, dd * dd * den);  // D * Vis = a2/(pi dd^2) * 0.5/den
-        const float t = 1.0f - VoH, t2 = t * t, fc = t2 * t2 * t;
-        const float Fr = fmaf(omF0r, fc, F0r), Fg = fmaf(omF0g, fc, F0g), Fb = fmaf(omF0b, fc, F0b);
-        const float4 lc = s_col[i];
-        dr = fmaf(fmaf(Fr, dv, cdpr - cdpr * Fr), lc.x * w, dr);
-        dg = fmaf(fmaf(Fg, dv, cdpg - cdpg * Fg), lc.y * w, dg);
-        db = fmaf(fmaf(Fb, dv, cdpb - cdpb * Fb), lc.z * w, db);
+  };
+  // without tile lists and with few lights, every tile uses the same staged list: stage it once
+  const bool one_list = p.tile_counts == nullptr && p.n_lights <= uint32_t(kLightChunk);
+  if (one_list) stage_lights(nullptr, 0, p.n_lights);
+
+  uint32_t tile = blockIdx.x;
+  int stage = 0;
+  if (tile < p.ntiles) stage_tile(p, s_tile[0], tile);
+  cp_async_commit();
+  if (one_list) __syncthreads();
+
+  for (; tile < p.ntiles; tile += gridDim.x, stage ^= 1) {
+    if (tile + gridDim.x < p.ntiles) stage_tile(p, s_tile[stage ^ 1], tile + gridDim.x);  // next tile in flight
+    cp_async_commit();
+    cp_async_wait<1>();  // this tile's group has landed (each thread reads only its own slots)
+
+    const uint32_t ty = p.ty0 + tile / p.ntx, tx = p.tx0 + tile % p.ntx;
+    const uint32_t x = tx * kTile + (threadIdx.x % kTile), y = ty * kTile + (threadIdx.x / kTile);
+    const bool inside = x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1;
+
+    // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
+    float3 P = make_float3(0.f, 0.f, 0.f), N = P, V = P;
+    float NoVraw = 0.f, NoV = 1.f, rough = 1.f, occ = 0.f, a2 = 1.f, oma2 = 0.f, visV = 1.f, base_a = 0.f;
+    float F0r = 0.f, F0g = 0.f, F0b = 0.f, cdr = 0.f, cdg = 0.f, cdb = 0.f;
+    float Lr = 0.f, Lg = 0.f, Lb = 0.f;
+    bool lit = false;
+    if (inside) {
+      const TileStage& st = s_tile[stage];
+      const uint2 tn = st.px[1][threadIdx.x];
+      const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
+      lit = !(nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f);  // all-zero normal = cleared texel
+      if (lit) {
+        const uint2 tp = st.px[0][threadIdx.x], ta = st.px[2][threadIdx.x], te = st.px[3][threadIdx.x];
+        const uint32_t to = st.orm[threadIdx.x];
+        const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
+        P = make_float3(pxy.x, pxy.y, pzw.x);
+        const float ninv = rsq(nxy.x * nxy.x + nxy.y * nxy.y + nzw.x * nzw.x);
+        N = make_float3(nxy.x * ninv, nxy.y * ninv, nzw.x * ninv);
+        const float vx = p.cx - P.x, vy = p.cy - P.y, vz = p.cz - P.z;
+        const float vinv = rsq(vx * vx + vy * vy + vz * vz);
+        V = make_float3(vx * vinv, vy * vinv, vz * vinv);
+        NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
+        NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
+        const float base_r = unorm16_lo(ta.x), base_g = unorm16_hi(ta.x), base_b = unorm16_lo(ta.y);
+        base_a = unorm16_hi(ta.y);
+        occ = float(to & 0xFFu) * (1.0f / 255.0f);
+        rough = fminf(fmaxf(float((to >> 8) & 0xFFu) * (1.0f / 255.0f), 0.045f), 1.0f);
+        const float metal = float((to >> 16) & 0xFFu) * (1.0f / 255.0f), omm = 1.0f - metal;
+        F0r = 0.04f * omm + base_r * metal; F0g = 0.04f * omm + base_g * metal; F0b = 0.04f * omm + base_b * metal;
+        cdr = base_r * omm; cdg = base_g * omm; cdb = base_b * omm;
+        const float alpha = rough * rough;
+        a2 = alpha * alpha; oma2 = 1.0f - a2;
+        const float vv = NoV * NoV * oma2 + a2;
+        visV = vv * rsq(vv);
+        const float2 exy = h2_to_f2(te.x), ezw = h2_to_f2(te.y);
+        Lr = exy.x; Lg = exy.y; Lb = ezw.x;  // emissive
       }
     }
+    const float cdpr = cdr * kInvPi, cdpg = cdg * kInvPi, cdpb = cdb * kInvPi;
+    const float omF0r = 1.0f - F0r, omF0g = 1.0f - F0g, omF0b = 1.0f - F0b;
+    const float a2h = a2 * (0.5f * kInvPi);
+
+    // ---- ambient set-up: the four footprint records are LOADED here (32 registers) and consumed after
+    // the light loop, whose ~400 instructions cover their L2 / DRAM latency (a prefetch into L1 does not
+    // survive: 24 warps x 32 lanes x 4 incoherent 128-byte lines exceed the L1) ----
+    IblTaps taps;
+    Quad8 qi, q0, q1, ql;
+    float3 Rv = make_float3(0.f, 0.f, 0.f);
+    if (lit && p.has_ibl) {
+      Rv = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
+      if (ACCEL) {
+        taps = make_ibl_taps(p, N, Rv, NoV, rough);
+        q0 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p0));
+        q1 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p1));
+        qi = ldg_quad(p.q_irr + 2 * size_t(taps.i_irr));
+        ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
+      }
+    }
+
+    // ---- direct lighting: KHR_lights_punctual point lights, Cook-Torrance GGX / Smith / Schlick ----
+    uint32_t nl = p.n_lights;
+    const uint16_t* idx = nullptr;
+    if (p.tile_counts != nullptr) {
+      const uint32_t t = ty * p.tiles_x + tx;
+      nl = min(__ldg(p.tile_counts + t), p.max_per_tile);
+      idx = p.tile_indices + size_t(t) * p.max_per_tile;
+    }
+    float dr = 0.f, dg = 0.f, db = 0.f;  // summed separately, in light order, like the oracle
+    for (uint32_t base = 0; base < nl; base += kLightChunk) {
+      const uint32_t cnt = min(nl - base, uint32_t(kLightChunk));
+      if (!one_list) {
+        __syncthreads();  // everyone is done with the previous chunk / tile
+        stage_lights(idx, base, cnt);
+        __syncthreads();
+      }
+      if (!lit) continue;
+      for (uint32_t i = 0; i < cnt; ++i) {
+        const float4 lp = s_pos[i];
+        const float dx = lp.x - P.x, dy = lp.y - P.y, dz = lp.z - P.z;
+        const float d2 = fmaxf(dx * dx + dy * dy + dz * dz, 1e-8f);
+        const float invd = rsq(d2);
+        const float NoL = sat((N.x * dx + N.y * dy + N.z * dz) * invd);
+        const float q = d2 * lp.w;                          // (d/range)^2; 0 for unlimited range
+        const float att = invd * invd * sat(1.0f - q * q);  // inverse square * clamp(1 - (d/range)^4, 0, 1)
+        const float w = att * NoL;
+        if (w > 0.0f) {
+          const float hx = fmaf(dx, invd, V.x), hy = fmaf(dy, invd, V.y), hz = fmaf(dz, invd, V.z);  // V + L
+          const float hinv = rsq(hx * hx + hy * hy + hz * hz);
+          const float NoH = sat((N.x * hx + N.y * hy + N.z * hz) * hinv);
+          const float VoH = sat((V.x * hx + V.y * hy + V.z * hz) * hinv);
+          // 1 - NoH^2 = |N x H|^2 (Lagrange): NoH^2 (a2 - 1) + 1 cancels catastrophically for smooth surfaces
+          const float kx = N.y * hz - N.z * hy, ky = N.z * hx - N.x * hz, kz = N.x * hy - N.y * hx;
+          const float dd = (kx * kx + ky * ky + kz * kz) * (hinv * hinv) + NoH * NoH * a2;
+          const float vl = NoL * NoL * oma2 + a2;
+          const float den = NoL * visV + NoV * (vl * rsq(vl));
+          const float dv = a2h * rcp(dd * dd * den);  // D * Vis = a2/(pi dd^2) * 0.5/den
+          const float t = 1.0f - VoH, t2 = t * t, fc = t2 * t2 * t;
+          const float Fr = fmaf(omF0r, fc, F0r), Fg = fmaf(omF0g, fc, F0g), Fb = fmaf(omF0b, fc, F0b);
+          const float4 lc = s_col[i];
+          // (1 - F) c_diff/pi + F D Vis = c_diff/pi + F (D Vis - c_diff/pi)
+          dr = fmaf(fmaf(Fr, dv - cdpr, cdpr), lc.x * w, dr);
+          dg = fmaf(fmaf(Fg, dv - cdpg, cdpg), lc.y * w, dg);
+          db = fmaf(fmaf(Fb, dv - cdpb, cdpb), lc.z * w, db);
+        }
+      }
+    }
+    if (!inside) continue;
+    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8;
+    if (!lit) {
+      stg_stream8(outp, make_uint2(0u, 0u));
+      continue;
+    }
+    // ---- ambient: split-sum image-based lighting (Karis 2013) ----
+    float ar = 0.f, ag = 0.f, ab = 0.f;
+    if (p.has_ibl) {
+      RGB irr, pre;
+      float2 sb;
+      if (ACCEL) {
+        irr = quad_bilinear_rgb(qi, taps.irr_tx, taps.irr_ty);
+        pre = quad_bilinear_rgb(q0, taps.p0_tx, taps.p0_ty);
+        const RGB pr1 = quad_bilinear_rgb(q1, taps.p1_tx, taps.p1_ty);
+        pre.r = lerpf(pre.r, pr1.r, taps.lod_f); pre.g = lerpf(pre.g, pr1.g, taps.lod_f); pre.b = lerpf(pre.b, pr1.b, taps.lod_f);
+        const float ax = __uint_as_float(ql.w[0]), ay = __uint_as_float(ql.w[1]), cx = __uint_as_float(ql.w[4]), cy = __uint_as_float(ql.w[5]);
+        sb.x = lerpf(lerpf(ax, __uint_as_float(ql.w[2]), taps.lut_tx), lerpf(cx, __uint_as_float(ql.w[6]), taps.lut_tx), taps.lut_ty);
+        sb.y = lerpf(lerpf(ay, __uint_as_float(ql.w[3]), taps.lut_tx), lerpf(cy, __uint_as_float(ql.w[7]), taps.lut_tx), taps.lut_ty);
+      } else {
+        irr = cube_sample(p.irr, N, 0.0f);
+        pre = cube_sample(p.pref, Rv, rough * float(p.pref.nmips - 1));
+        sb = lut_sample(p.lut, int(p.lut_res), NoV, rough);
+      }
+      ar = (irr.r * cdr + pre.r * (F0r * sb.x + sb.y)) * occ;
+      ag = (irr.g * cdg + pre.g * (F0g * sb.x + sb.y)) * occ;
+      ab = (irr.b * cdb + pre.b * (F0b * sb.x + sb.y)) * occ;
+    }
+    // oracle order: (direct + ambient) + emissive
+    Lr = fminf((dr + ar) + Lr, 65504.0f); Lg = fminf((dg + ag) + Lg, 65504.0f); Lb = fminf((db + ab) + Lb, 65504.0f);
+    stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
   }
-  if (!inside) return;
-  uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8;
-  if (!lit) {
-    stg_stream8(outp, make_uint2(0u, 0u));
-    return;
-  }
-  // ---- ambient: split-sum image-based lighting (Karis 2013) ----
-  float ar = 0.f, ag = 0.f, ab = 0.f;
-  if (p.has_ibl) {
-    const float3 R = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
-    const RGB irr = cube_sample(p.irr, N, 0.0f);
-    const RGB pre = cube_sample(p.pref, R, rough * float(p.pref.nmips - 1));
-    const float2 sb = lut_sample(p.lut, int(p.lut_res), NoV, rough);
-    ar = (irr.r * cdr + pre.r * (F0r * sb.x + sb.y)) * occ;
-    ag = (irr.g * cdg + pre.g * (F0g * sb.x + sb.y)) * occ;
-    ab = (irr.b * cdb + pre.b * (F0b * sb.x + sb.y)) * occ;
-  }
-  // oracle order: (direct + ambient) + emissive
-  Lr = fminf((dr + ar) + Lr, 65504.0f); Lg = fminf((dg + ag) + Lg, 65504.0f); Lb = fminf((db + ab) + Lb, 65504.0f);
-  stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+  cp_async_wait<0>();
 }
 
 // ---- K3c: per 16x16 tile, world-space AABB of the tile's non-cleared positions, then every light
@@ -318,8 +439,18 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
     p.pref = make_chain(ibl->prefiltered, ibl->pref_res, ibl->pref_mips);
     p.lut = reinterpret_cast<const float2*>(ibl->lut);
     p.lut_res = ibl->lut_res;
+    if (ibl->accel) {
+      const pbrcu_ibl_accel* a = ibl->accel;
+      PBRCU_REQUIRE(a->pref_res == ibl->pref_res && a->pref_mips == ibl->pref_mips && a->irr_res == ibl->irr_res && a->lut_res == ibl->lut_res,
+                    "ibl->accel was built for textures of another shape");
+      p.q_pref = a->pref; p.q_irr = a->irr; p.q_lut = a->lut;
+    }
   }
-  dim3 grid((p.x1 + kTile - 1) / kTile - p.tx0, (p.y1 + kTile - 1) / kTile - p.ty0);
-  shade_ggx_kernel<<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
+  p.ntx = (p.x1 + kTile - 1) / kTile - p.tx0;
+  p.ntiles = p.ntx * ((p.y1 + kTile - 1) / kTile - p.ty0);
+  // persistent grid: kShadeCtasPerSm CTAs per SM walk the tiles round-robin
+  const uint32_t grid = min(p.ntiles, uint32_t(ctx->sm_count) * kShadeCtasPerSm);
+  if (p.q_pref) shade_ggx_kernel<true><<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
+  else shade_ggx_kernel<false><<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
   return launch_check("shade_ggx_kernel");
 }

@@ -96,11 +96,16 @@ def build_ibl(dev, oracle, res=32, nmips=6, ns=256, ires=16, lres=32):
     return host, (irr_d, pref_d, lut_d)
 
 
-def make_ibl_struct(pbr, host, bufs):
+def make_ibl_struct(pbr, host, bufs, dev=None, accel=False):
+    """accel=True also builds the footprint-record copies (pbrcu_ibl_accel_build) the fast K3 path samples."""
     s = pbr.Ibl()
     s.irradiance, s.irr_res = bufs[0].ptr, host["irr"].shape[1]
     s.prefiltered, s.pref_res, s.pref_mips = bufs[1].ptr, host["pref_res"], host["pref_mips"]
     s.lut, s.lut_res = bufs[2].ptr, host["lut"].shape[0]
+    if accel:
+        h = C.c_void_p()
+        dev.lib.ibl_accel_build(dev.ctx, C.byref(s), C.byref(h), None)
+        s.accel = h
     return s
 
 
@@ -121,6 +126,15 @@ def test_shade_matches_oracle(pbr, dev, oracle, w, h, nl, use_ibl):
     peak = float(max(f16(want).max(), 1.0))
     assert_hdr_parity(got, want, peak=peak, rel_tol=REL, what=f"shade {w}x{h} nl={nl}")
     assert (got[g["bg"]] == 0).all()
+    if use_ibl:  # the footprint-record path (one 256-bit load per bilinear tap) must be bit-identical
+        ibl2 = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+        assert dev.lib.ibl_accel_bytes(ibl2.accel) == 32 * (oracle.chain_texels(host["pref_res"], host["pref_mips"]) + host["irr"].size // 4 + host["lut"].size // 2)
+        out2 = dev.alloc(w * h * 8)
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr if ld else None, nl, None, C.byref(ibl2), pbr.WHOLE, out2.ptr, w * 8, None)
+        dev.sync()
+        got2 = out2.download((h, w, 4), np.uint16)
+        assert np.array_equal(got2, got), f"accel path differs from the plain path in {np.count_nonzero(got2 != got)} values"
+        dev.lib.ibl_accel_free(dev.ctx, ibl2.accel)
 
 
 def test_shade_tiled_lights_equal_brute_force(pbr, dev, oracle):
