@@ -25,6 +25,7 @@ struct ShadeParams {
   uint32_t x0, y0, x1, y1;        // rect in image coordinates (x1, y1 exclusive)
   uint32_t tx0, ty0;              // first tile of the rect
   uint32_t ntx, ntiles;           // tiles per row of the rect, tiles in the rect
+  uint32_t ntx_magic;             // ceil(2^32 / ntx) (0 if ntx == 1): tile / ntx == __umulhi(tile, magic) while tile * ntx < 2^32
   float cx, cy, cz;
   const pbrcu_light* lights;
   uint32_t n_lights;
@@ -103,7 +104,8 @@ struct TileStage {
 };
 
 __device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, uint32_t tile) {
-  const uint32_t ty = p.ty0 + tile / p.ntx, tx = p.tx0 + tile % p.ntx;
+  const uint32_t trow = p.ntx_magic ? __umulhi(tile, p.ntx_magic) : tile;
+  const uint32_t ty = p.ty0 + trow, tx = p.tx0 + (tile - trow * p.ntx);
   const uint32_t x = tx * kTile + (threadIdx.x % kTile), y = ty * kTile + (threadIdx.x / kTile);
   if (x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1) {
     const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8;
@@ -145,7 +147,8 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     cp_async_commit();
     cp_async_wait<1>();  // this tile's group has landed (each thread reads only its own slots)
 
-    const uint32_t ty = p.ty0 + tile / p.ntx, tx = p.tx0 + tile % p.ntx;
+    const uint32_t trow = p.ntx_magic ? __umulhi(tile, p.ntx_magic) : tile;
+    const uint32_t ty = p.ty0 + trow, tx = p.tx0 + (tile - trow * p.ntx);
     const uint32_t x = tx * kTile + (threadIdx.x % kTile), y = ty * kTile + (threadIdx.x / kTile);
     const bool inside = x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1;
 
@@ -236,12 +239,17 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
         const float w = att * NoL;
         if (w > 0.0f) {
           const float hx = fmaf(dx, invd, V.x), hy = fmaf(dy, invd, V.y), hz = fmaf(dz, invd, V.z);  // V + L
-          const float hinv = rsq(hx * hx + hy * hy + hz * hz);
-          const float NoH = sat((N.x * hx + N.y * hy + N.z * hz) * hinv);
-          const float VoH = sat((V.x * hx + V.y * hy + V.z * hz) * hinv);
-          // 1 - NoH^2 = |N x H|^2 (Lagrange): NoH^2 (a2 - 1) + 1 cancels catastrophically for smooth surfaces
-          const float kx = N.y * hz - N.z * hy, ky = N.z * hx - N.x * hz, kz = N.x * hy - N.y * hx;
-          const float dd = (kx * kx + ky * ky + kz * kz) * (hinv * hinv) + NoH * NoH * a2;
+          const float hh = fmaxf(hx * hx + hy * hy + hz * hz, 1e-12f);  // V = -L: grazing back-facing pixel
+          const float hinv = rsq(hh);
+          // |V| = |L| = 1: V.h = 1 + V.L = |h|^2 / 2, so V.H = |h| / 2 (in [0, 1] by construction)
+          const float VoH = 0.5f * hh * hinv;
+          // 1 - NoH^2 without cancellation: s = |H - N|^2 = 2 - 2 N.H  =>  u = 1 - (N.H)^2 = s (1 - s/4)
+          // (what the oracle takes from |N x H|^2).  D's denominator NoH^2 (a2 - 1) + 1 with
+          // NoH = max(N.H, 0) is then u (1 - a2) + a2, or just u where N.H < 0, i.e. s > 2.
+          const float ex = fmaf(hx, hinv, -N.x), ey = fmaf(hy, hinv, -N.y), ez = fmaf(hz, hinv, -N.z);
+          const float sq = ex * ex + ey * ey + ez * ez;
+          const float u = fmaf(sq * sq, -0.25f, sq);
+          const float dd = sq > 2.0f ? u : fmaf(u, oma2, a2);
           const float vl = NoL * NoL * oma2 + a2;
           const float den = NoL * visV + NoV * (vl * rsq(vl));
           const float dv = a2h * rcp(dd * dd * den);  // D * Vis = a2/(pi dd^2) * 0.5/den
@@ -448,6 +456,8 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
   }
   p.ntx = (p.x1 + kTile - 1) / kTile - p.tx0;
   p.ntiles = p.ntx * ((p.y1 + kTile - 1) / kTile - p.ty0);
+  PBRCU_REQUIRE(uint64_t(p.ntiles) * p.ntx < (1ull << 32), "rect too large");  // 16x16 tiles: beyond 100k x 100k pixels
+  p.ntx_magic = p.ntx == 1 ? 0u : uint32_t(((1ull << 32) + p.ntx - 1) / p.ntx);  // 0: one tile per row
   // persistent grid: kShadeCtasPerSm CTAs per SM walk the tiles round-robin
   const uint32_t grid = min(p.ntiles, uint32_t(ctx->sm_count) * kShadeCtasPerSm);
   if (p.q_pref) shade_ggx_kernel<true><<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
