@@ -161,6 +161,30 @@ class Scene:
             b.record()
             torch.cuda.synchronize()
             self.ibl_ms[name] = round(a.elapsed_time(b), 4)
+        # the same prefilter with software fp32-weight filtering (pbrcu_ibl_set_exact_filtering): time, and
+        # how far the texture-unit result is from it
+        exact = buf(chain_bytes)
+        lib.ibl_set_exact_filtering(ctx, 1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        lib.ibl_prefilter_ggx(ctx, self.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, exact.data_ptr(), 0, CUBE_MIPS - 1, 0, 1, self.stream())
+        b.record()
+        torch.cuda.synchronize()
+        lib.ibl_set_exact_filtering(ctx, 0)
+        self.ibl_ms["prefilter_ggx_fp32_weights"] = round(a.elapsed_time(b), 4)
+        lvl1 = lib.cube_mip_offset(CUBE_RES, 1) * 8
+        f = self.pref[lvl1:].view(torch.float16).float().view(-1, 4)[:, :3]
+        e = exact[lvl1:].view(torch.float16).float().view(-1, 4)[:, :3]
+        err = (f - e).abs()
+        rel = err / (e.abs() + 1e-3)
+        self.prefilter_error = {"what": "texture-unit prefilter vs fp32-weight prefilter, levels 1..11, fp16 outputs",
+                                "max_abs": float(err.max()), "max_rel": float(rel.max()),
+                                "rel_p99.99": float(torch.quantile(rel.flatten()[:: max(1, rel.numel() // 4_000_000)], 0.9999)),
+                                "frac_within_1e-3+2^-9": float((err <= 1e-3 + 2.0 ** -9 * e.abs()).float().mean()),
+                                "psnr_db": float(10 * torch.log10(e.max() ** 2 / (err.double() ** 2).mean()))}
+        del f, e, err, rel
+        self.keep = [t for t in self.keep if t is not exact]
+        del exact
         s = pbr.Ibl()
         s.irradiance, s.irr_res = self.irr.data_ptr(), IRR_RES
         s.prefiltered, s.pref_res, s.pref_mips = self.pref.data_ptr(), CUBE_RES, CUBE_MIPS
@@ -346,6 +370,7 @@ def main_ours(args):
                        "fused_ldr_mpix_s": round(world * px_step * args.steps / (ms_fused * 1e-3) / 1e6, 1),
                        "fused_ldr_roofline_frac": round(28 * px_step * args.steps / (ms_fused * 1e-3) / 1e9 / peak, 4)},
             "ibl_precompute_ms": scene.ibl_ms,
+            "prefilter_error": scene.prefilter_error,
         }
         print(json.dumps(line))
     if dist is not None:

@@ -193,6 +193,13 @@ int pbrcu_ibl_equirect_to_cube(pbrcu_ctx* ctx, const float* src_rgba32f_dev, uin
  * face_row0/face_rows select a band of base-level rows per face for sharding (0,0 = everything). */
 int pbrcu_ibl_cube_mipgen(pbrcu_ctx* ctx, void* chain_dev, uint32_t base_res, uint32_t nmips,
                           pbrcu_stream s);
+/* K6/K7 read the source chain through the texture unit: ONE hardware trilinear cube fetch per sample.
+ * The unit's filter weights are 8-bit fixed point (error <= 3/512 of the value range of the sample's
+ * 8-texel footprint), so the texture copy carries a contrast flag and every sample whose footprint
+ * spans more than 25 % falls back to fp32-weight software filtering: the result is within 1.5e-3
+ * relative of the exact filter.  exact != 0 turns the texture unit off altogether (fp32 weights for
+ * every sample, about 3x slower on a smooth environment). */
+int pbrcu_ibl_set_exact_filtering(pbrcu_ctx* ctx, int exact);
 /* K7: GGX prefilter of levels [first_mip,last_mip] (level 0 = copy), nsamples per texel.
  * shard/nshards split each level's texels into contiguous blocks for multi-GPU (0,1 = all). */
 int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res,

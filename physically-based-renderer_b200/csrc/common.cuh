@@ -22,6 +22,14 @@ struct pbrcu_ctx {
   // per-view camera positions for the batched multi-view launch (grown on demand)
   float* cams_dev;
   uint32_t cams_cap;
+  // cube-map texture (mipmapped CUDA array + texture object) the IBL convolutions sample; kept between
+  // calls and re-created only when the chain shape changes (array allocation costs milliseconds)
+  cudaMipmappedArray_t cube_array;
+  cudaTextureObject_t cube_tex;
+  uint32_t cube_res, cube_mips;
+  void *cube_stage, *cube_mm;  // staging copy with contrast flags in alpha; per-texel 3x3 min/max
+  size_t cube_stage_bytes, cube_mm_bytes;
+  bool exact_ibl_filter;  // K6/K7: software fp32-weight filtering instead of the texture unit
 };
 
 namespace pbrcu {

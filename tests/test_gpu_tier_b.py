@@ -55,9 +55,12 @@ def test_equirect_to_cube_and_mipgen(dev, oracle):
     assert np.array_equal(chain, want_chain), "cube mip chain is not bit-exact"
 
 
-def test_prefilter_and_irradiance(dev, oracle):
+@pytest.mark.parametrize("exact", [0, 1], ids=["texture-unit", "fp32-weights"])
+def test_prefilter_and_irradiance(dev, oracle, exact):
+    """Both K6/K7 filter paths (hardware trilinear cube fetches; software fp32 weights) against the oracle."""
     res, nmips, ns = 32, 6, 1024
     env, chain_d, chain = make_env_chain(dev, oracle, res, nmips)
+    dev.lib.ibl_set_exact_filtering(dev.ctx, exact)
     dst = dev.alloc(chain.nbytes)
     dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, dst.ptr, 0, nmips - 1, 0, 1, None)
     dev.sync()
@@ -80,6 +83,43 @@ def test_prefilter_and_irradiance(dev, oracle):
     dev.lib.ibl_irradiance(dev.ctx, chain_d.ptr, res, nmips, ires, ns, irr.ptr, None)
     dev.sync()
     assert_hdr_parity(irr.download((6, ires, ires, 4), np.uint16), oracle.irradiance(chain, res, nmips, ires, ns), peak=50.0, rel_tol=REL, what="irradiance")
+    dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+
+
+def test_prefilter_texture_unit_on_sharp_environment(dev, oracle):
+    """The hardware-filtered prefilter on a 256^2 chain whose base level holds a hard-edged sun (the worst case
+    for the unit's 8-bit weights): every level within tolerance of the oracle at randomly chosen texels, and
+    within tolerance of the fp32-weight path everywhere."""
+    res, nmips, ns = 256, 9, 1024
+    env = synth_environment(1024, 512, 3, sun=5.0e3)
+    src = dev.upload(env)
+    n = oracle.chain_texels(res, nmips)
+    chain_d = dev.alloc(n * 8)
+    dev.lib.ibl_equirect_to_cube(dev.ctx, src.ptr, 1024, 512, res, chain_d.ptr, None)
+    dev.lib.ibl_cube_mipgen(dev.ctx, chain_d.ptr, res, nmips, None)
+    dev.sync()
+    chain = chain_d.download((n, 4), np.uint16)
+    outs = []
+    for exact in (0, 1):
+        dev.lib.ibl_set_exact_filtering(dev.ctx, exact)
+        dst = dev.alloc(n * 8)
+        dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, dst.ptr, 0, nmips - 1, 0, 1, None)
+        dev.sync()
+        outs.append(dst.download((n, 4), np.uint16))
+        dst.free()
+    dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+    fast, exact_out = outs
+    a = oracle.mip_offset(res, 1)
+    assert_hdr_parity(fast[a:], exact_out[a:], peak=float(f16(exact_out).max()), rel_tol=REL, what="texture-unit vs fp32-weight prefilter")
+    rng = np.random.default_rng(5)
+    for m in range(1, nmips):
+        r = res >> m
+        off = oracle.mip_offset(res, m)
+        for _ in range(24):
+            f, x, y = int(rng.integers(6)), int(rng.integers(r)), int(rng.integers(r))
+            want = oracle.prefilter_texel(chain, res, nmips, m, ns, f, x, y)[:3]
+            got = f16(fast[off + (f * r + y) * r + x])[:3]
+            assert (np.abs(got - want) <= 1e-3 + REL * np.abs(want)).all(), (m, f, x, y, got, want)
 
 
 def build_ibl(dev, oracle, res=32, nmips=6, ns=256, ires=16, lres=32):
