@@ -200,6 +200,13 @@ int pbrcu_ibl_cube_mipgen(pbrcu_ctx* ctx, void* chain_dev, uint32_t base_res, ui
  * relative of the exact filter.  exact != 0 turns the texture unit off altogether (fp32 weights for
  * every sample, about 3x slower on a smooth environment). */
 int pbrcu_ibl_set_exact_filtering(pbrcu_ctx* ctx, int exact);
+/* K3 (when ibl->accel is set): on != 0 fetches the prefiltered and irradiance cubes through the texture
+ * unit (one TEX each; flagged copies, 12 % footprint range -> within 7e-4 relative of the fp32-weight
+ * filter) and falls back to the fp32-weight footprint records where the filtered flag is set.  Default
+ * off: with per-pixel random roughness almost every warp holds a flagged lane (coarse levels differ by
+ * more than 12 % texel to texel), so the fallback runs anyway; measured 229 us vs 219 us per 4K frame.
+ * Worth it only for content whose materials are coherent over a warp (179 us with no fallback). */
+int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on);
 /* K7: GGX prefilter of levels [first_mip,last_mip] (level 0 = copy), nsamples per texel.
  * shard/nshards split each level's texels into contiguous blocks for multi-GPU (0,1 = all). */
 int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res,

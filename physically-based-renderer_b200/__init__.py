@@ -114,6 +114,7 @@ _SIGNATURES = {
     "pbrcu_ibl_equirect_to_cube": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp]),
     "pbrcu_ibl_cube_mipgen": (_i, [_vp, _vp, _u32, _u32, _vp]),
     "pbrcu_ibl_set_exact_filtering": (_i, [_vp, _i]),
+    "pbrcu_shade_set_texture_unit": (_i, [_vp, _i]),
     "pbrcu_ibl_prefilter_ggx": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, _vp]),
     "pbrcu_ibl_irradiance": (_i, [_vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
     "pbrcu_synth_gbuffer": (_i, [_vp, _PG, _i, _u64, _f3, _f3, _vp]),

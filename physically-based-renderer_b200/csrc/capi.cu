@@ -6,7 +6,7 @@
 #include <cstring>
 #include <new>
 
-#include "common.cuh"
+#include "cube_tex.cuh"
 
 namespace pbrcu {
 
@@ -72,8 +72,7 @@ extern "C" void pbrcu_ctx_destroy(pbrcu_ctx* ctx) {
     if (ctx->pipe_done[i]) cudaEventDestroy(ctx->pipe_done[i]);
   }
   if (ctx->pipe_start) cudaEventDestroy(ctx->pipe_start);
-  if (ctx->cube_tex) cudaDestroyTextureObject(ctx->cube_tex);
-  if (ctx->cube_array) cudaFreeMipmappedArray(ctx->cube_array);
+  pbrcu::cube_tex_destroy(&ctx->cube);
   if (ctx->cube_stage) cudaFree(ctx->cube_stage);
   if (ctx->cube_mm) cudaFree(ctx->cube_mm);
   delete ctx;

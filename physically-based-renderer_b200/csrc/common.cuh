@@ -6,6 +6,15 @@
 
 #include "../../include/pbrcu.h"
 
+namespace pbrcu {
+// a cube-map mip chain as a hardware texture with contrast flags in alpha (cube_tex.cuh)
+struct CubeTex {
+  cudaMipmappedArray_t array;
+  cudaTextureObject_t tex;
+  uint32_t res, mips;
+};
+}  // namespace pbrcu
+
 struct pbrcu_ctx {
   int device;
   int sm_count;
@@ -24,12 +33,11 @@ struct pbrcu_ctx {
   uint32_t cams_cap;
   // cube-map texture (mipmapped CUDA array + texture object) the IBL convolutions sample; kept between
   // calls and re-created only when the chain shape changes (array allocation costs milliseconds)
-  cudaMipmappedArray_t cube_array;
-  cudaTextureObject_t cube_tex;
-  uint32_t cube_res, cube_mips;
+  pbrcu::CubeTex cube;
   void *cube_stage, *cube_mm;  // staging copy with contrast flags in alpha; per-texel 3x3 min/max
   size_t cube_stage_bytes, cube_mm_bytes;
   bool exact_ibl_filter;  // K6/K7: software fp32-weight filtering instead of the texture unit
+  bool shade_tex;         // K3: texture-unit fetches of the prefiltered / irradiance cubes (pbrcu_shade_set_texture_unit)
 };
 
 namespace pbrcu {

@@ -7,7 +7,7 @@
 // builds the table {L_local.xyz, source lod} once in shared memory; per sample a thread then does a
 // 3x3 frame rotation, one exact-weight trilinear cube fetch and 4 FMAs.  G lanes share one texel
 // (samples strided by G, warp-shuffle reduction) so the small mips still fill the machine.
-#include "cube.cuh"
+#include "cube_tex.cuh"
 #include "detmath.cuh"
 
 namespace pbrcu {
@@ -67,8 +67,16 @@ __global__ void __launch_bounds__(kConvThreads) conv_kernel(const __grid_constan
   __syncthreads();
 
   const int texel = threadIdx.x / G, lane = threadIdx.x % G;
-  const int x = blockIdx.x * p.tw + texel % p.tw;
-  const int grow = p.row_begin + blockIdx.y * p.th + texel / p.tw;
+  int tx_in = texel % p.tw, ty_in = texel / p.tw;
+  if (G == 1 && p.tw % 8 == 0 && p.th % 4 == 0) {
+    // a warp covers an 8x4 texel patch instead of a 32x1 strip: its 32 fetches of one sample then fall
+    // into a compact 2-D footprint of the source level (fewer texture cache lines per request)
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, wpr = p.tw >> 3;
+    tx_in = (w % wpr) * 8 + (l & 7);
+    ty_in = (w / wpr) * 4 + (l >> 3);
+  }
+  const int x = blockIdx.x * p.tw + tx_in;
+  const int grow = p.row_begin + blockIdx.y * p.th + ty_in;
   const bool valid = x < p.res && grow < p.row_end;
   const int xc = min(x, p.res - 1), gc = min(grow, p.row_end - 1);
   const int face = gc / p.res, y = gc - face * p.res;
@@ -168,12 +176,12 @@ __device__ __forceinline__ void mm_merge(MinMax& a, const uint4* p) {
   a.mx[0] = fmaxf(a.mx[0], b0.x); a.mx[1] = fmaxf(a.mx[1], b0.y); a.mx[2] = fmaxf(a.mx[2], b1.x);
 }
 // pass B: a texel is flagged when the value range over every footprint it can share a trilinear sample
-// with exceeds 25 % of the minimum.  As the finer level of a sample its own 3x3 holds the 2x2 footprint
+// with exceeds rel_range x the minimum.  As the finer level of a sample its own 3x3 holds the 2x2 footprint
 // and its parent's 3x3 holds the coarser footprint; as the coarser level its own 3x3 holds its footprint
 // and the 3x3s of the 4x4 block of texels around its children hold the finer one.
 __global__ void __launch_bounds__(256) contrast_flags_kernel(const uint2* __restrict__ level, const uint4* __restrict__ mm,
                                                              const uint4* __restrict__ mm_up, const uint4* __restrict__ mm_down,
-                                                             uint2* __restrict__ out, int res, size_t n) {
+                                                             uint2* __restrict__ out, int res, size_t n, float rel_range) {
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
     const int x = int(i % res), y = int((i / res) % res);
     const size_t face = i / (size_t(res) * res);
@@ -191,7 +199,7 @@ __global__ void __launch_bounds__(256) contrast_flags_kernel(const uint2* __rest
     }
     bool flag = false;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) flag = flag || !(a.mx[c] <= 1.25f * a.mn[c] + 1.0e-4f);  // NaN -> flagged
+    for (int c = 0; c < 3; ++c) flag = flag || !(a.mx[c] <= fmaf(rel_range, a.mn[c], a.mn[c]) + 1.0e-4f);  // NaN -> flagged
     const uint2 t = __ldg(level + i);
     out[i] = make_uint2(t.x, (t.y & 0xFFFFu) | (flag ? 0x3C000000u : 0u));  // alpha = 1.0h or 0
   }
@@ -206,17 +214,23 @@ static int grow(void** buf, size_t* have, size_t want) {
   return PBRCU_OK;
 }
 
-// (Re)creates the context's cube-map texture for this chain shape and copies the chain into it with the
-// contrast flags in alpha (device-to-device, one 3-D copy per level).
-static int upload_cube_texture(pbrcu_ctx* ctx, const void* chain, uint32_t base_res, uint32_t nmips, cudaStream_t st) {
-  if (!ctx->cube_tex || ctx->cube_res != base_res || ctx->cube_mips != nmips) {
-    if (ctx->cube_tex) { cudaDestroyTextureObject(ctx->cube_tex); ctx->cube_tex = 0; }
-    if (ctx->cube_array) { cudaFreeMipmappedArray(ctx->cube_array); ctx->cube_array = nullptr; }
+}  // namespace pbrcu
+
+void pbrcu::cube_tex_destroy(CubeTex* t) {
+  if (t->tex) cudaDestroyTextureObject(t->tex);
+  if (t->array) cudaFreeMipmappedArray(t->array);
+  t->tex = 0; t->array = nullptr; t->res = t->mips = 0;
+}
+
+int pbrcu::cube_tex_upload(pbrcu_ctx* ctx, CubeTex* t, const void* chain, uint32_t base_res, uint32_t nmips, float rel_range,
+                           bool guard_coarser, cudaStream_t st) {
+  if (!t->tex || t->res != base_res || t->mips != nmips) {  // array allocation costs milliseconds: keep it while the shape holds
+    cube_tex_destroy(t);
     const cudaChannelFormatDesc fmt = cudaCreateChannelDescHalf4();
-    PBRCU_CUDA(cudaMallocMipmappedArray(&ctx->cube_array, &fmt, make_cudaExtent(base_res, base_res, 6), nmips, cudaArrayCubemap));
+    PBRCU_CUDA(cudaMallocMipmappedArray(&t->array, &fmt, make_cudaExtent(base_res, base_res, 6), nmips, cudaArrayCubemap));
     cudaResourceDesc rd{};
     rd.resType = cudaResourceTypeMipmappedArray;
-    rd.res.mipmap.mipmap = ctx->cube_array;
+    rd.res.mipmap.mipmap = t->array;
     cudaTextureDesc td{};
     td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;  // per face: no seamless filtering
     td.filterMode = cudaFilterModeLinear;
@@ -224,9 +238,9 @@ static int upload_cube_texture(pbrcu_ctx* ctx, const void* chain, uint32_t base_
     td.readMode = cudaReadModeElementType;
     td.normalizedCoords = 1;
     td.maxMipmapLevelClamp = float(nmips - 1);
-    PBRCU_CUDA(cudaCreateTextureObject(&ctx->cube_tex, &rd, &td, nullptr));
-    ctx->cube_res = base_res;
-    ctx->cube_mips = nmips;
+    PBRCU_CUDA(cudaCreateTextureObject(&t->tex, &rd, &td, nullptr));
+    t->res = base_res;
+    t->mips = nmips;
   }
   const size_t total = cube_mip_offset(base_res, nmips);
   if (int rc = grow(&ctx->cube_stage, &ctx->cube_stage_bytes, total * 8)) return rc;
@@ -243,12 +257,12 @@ static int upload_cube_texture(pbrcu_ctx* ctx, const void* chain, uint32_t base_
   for (uint32_t m = 0; m < nmips; ++m) {
     const size_t off = cube_mip_offset(base_res, m), r = base_res >> m, n = 6 * r * r;
     contrast_flags_kernel<<<blocks_for(n), 256, 0, st>>>(src + off, mm + off, m + 1 < nmips ? mm + cube_mip_offset(base_res, m + 1) : nullptr,
-                                                          m > 0 ? mm + cube_mip_offset(base_res, m - 1) : nullptr, stage + off, int(r), n);
+                                                          m > 0 && guard_coarser ? mm + cube_mip_offset(base_res, m - 1) : nullptr, stage + off, int(r), n, rel_range);
   }
   if (int rc = launch_check("contrast_flags_kernel")) return rc;
   for (uint32_t m = 0; m < nmips; ++m) {
     cudaArray_t level;
-    PBRCU_CUDA(cudaGetMipmappedArrayLevel(&level, ctx->cube_array, m));
+    PBRCU_CUDA(cudaGetMipmappedArrayLevel(&level, t->array, m));
     const size_t r = base_res >> m;
     cudaMemcpy3DParms cp{};
     cp.srcPtr = make_cudaPitchedPtr(stage + cube_mip_offset(base_res, m), r * 8, r, r);
@@ -259,6 +273,8 @@ static int upload_cube_texture(pbrcu_ctx* ctx, const void* chain, uint32_t base_
   }
   return PBRCU_OK;
 }
+
+namespace pbrcu {
 
 static void shard_rows(int total_rows, uint32_t shard, uint32_t nshards, int& b, int& e) {
   b = int(uint64_t(total_rows) * shard / nshards);
@@ -287,7 +303,7 @@ extern "C" int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev
   cudaStream_t st = static_cast<cudaStream_t>(s);
   const bool tex = !ctx->exact_ibl_filter;
   if (tex && last_mip >= 1)
-    if (int rc = upload_cube_texture(ctx, src_chain_dev, base_res, nmips, st)) return rc;
+    if (int rc = cube_tex_upload(ctx, &ctx->cube, src_chain_dev, base_res, nmips, 0.25f, true, st)) return rc;
   for (uint32_t m = first_mip; m <= last_mip; ++m) {
     const int res = int(base_res >> m);
     int rb, re;
@@ -308,7 +324,7 @@ extern "C" int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev
     p.roughness = float(m) / float(nmips - 1);
     p.row_begin = rb;
     p.row_end = re;
-    p.tex = ctx->cube_tex;
+    p.tex = ctx->cube.tex;
     if (int rc = tex ? launch_conv<CONV_GGX, true>(ctx, p, st) : launch_conv<CONV_GGX, false>(ctx, p, st)) return rc;
   }
   return PBRCU_OK;
@@ -328,7 +344,7 @@ extern "C" int pbrcu_ibl_irradiance(pbrcu_ctx* ctx, const void* src_chain_dev, u
   p.row_end = 6 * int(res);
   cudaStream_t st = static_cast<cudaStream_t>(s);
   if (ctx->exact_ibl_filter) return launch_conv<CONV_COSINE, false>(ctx, p, st);
-  if (int rc = upload_cube_texture(ctx, src_chain_dev, base_res, nmips, st)) return rc;
-  p.tex = ctx->cube_tex;
+  if (int rc = cube_tex_upload(ctx, &ctx->cube, src_chain_dev, base_res, nmips, 0.25f, true, st)) return rc;
+  p.tex = ctx->cube.tex;
   return launch_conv<CONV_COSINE, true>(ctx, p, st);
 }

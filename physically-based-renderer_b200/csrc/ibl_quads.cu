@@ -7,6 +7,8 @@
 
 namespace pbrcu {
 
+constexpr float kShadeTexRelRange = 0.12f;
+
 // faces of one level: n = 6*res*res records (n_faces*res*res in general)
 __global__ void __launch_bounds__(256) build_quads8_kernel(const uint2* __restrict__ src, uint4* __restrict__ dst, int res, size_t n) {
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
@@ -40,6 +42,8 @@ extern "C" int pbrcu_ibl_accel_free(pbrcu_ctx* ctx, pbrcu_ibl_accel* a) {
   if (a->pref) cudaFree(a->pref);
   if (a->irr) cudaFree(a->irr);
   if (a->lut) cudaFree(a->lut);
+  cube_tex_destroy(&a->pref_tex);
+  cube_tex_destroy(&a->irr_tex);
   delete a;
   return PBRCU_OK;
 }
@@ -80,6 +84,14 @@ extern "C" int pbrcu_ibl_accel_build(pbrcu_ctx* ctx, const pbrcu_ibl* ibl, pbrcu
     pbrcu_ibl_accel_free(ctx, a);
     return rc;
   }
+  // hardware-texture copies with contrast flags (12 % footprint range: a flag-free sample is within
+  // 3/512 * 0.12 = 7e-4 relative of the fp32-weight filter; K3 itself rules out level fractions near 1)
+  if ((rc = cube_tex_upload(ctx, &a->pref_tex, ibl->prefiltered, ibl->pref_res, ibl->pref_mips, kShadeTexRelRange, false, st)) ||
+      (rc = cube_tex_upload(ctx, &a->irr_tex, ibl->irradiance, ibl->irr_res, 1, kShadeTexRelRange, false, st))) {
+    pbrcu_ibl_accel_free(ctx, a);
+    return rc;
+  }
+  a->bytes += cube_tex_bytes(a->pref_tex) + cube_tex_bytes(a->irr_tex);
   *out = a;
   return PBRCU_OK;
 }

@@ -5,13 +5,16 @@
 // floor(fx) in [0, res-1] and the weights frac(fx) are 0 where the oracle's clamp makes both taps equal,
 // so the result is bit-identical to cube.cuh's four-load face_bilinear.
 #pragma once
-#include "cube.cuh"
+#include "cube_tex.cuh"
 
 struct pbrcu_ibl_accel {
   uint4* pref;      // chain_texels(pref_res, pref_mips) records, same level/face/row order as the chain
   uint4* irr;       // 6*irr_res^2 records
   uint4* lut;       // lut_res^2 records of 4 x float2
   uint32_t pref_res, pref_mips, irr_res, lut_res;
+  // the prefiltered chain and the irradiance map as flagged hardware textures (cube_tex.cuh): K3 takes
+  // one TEX fetch per map and falls back to the records above where the filtered flag is set
+  pbrcu::CubeTex pref_tex, irr_tex;
   size_t bytes;
 };
 
@@ -82,6 +85,13 @@ __device__ __forceinline__ RGB quad_bilinear_rgb(const Quad8& q, float tx, float
     o.b = fmaf(ty, bot - top, top);
   }
   return o;
+}
+
+// bilinear of a LUT record (4 x float2)
+__device__ __forceinline__ float2 quad_bilinear_lut(const Quad8& q, float tx, float ty) {
+  const float ax = __uint_as_float(q.w[0]), ay = __uint_as_float(q.w[1]), cx = __uint_as_float(q.w[4]), cy = __uint_as_float(q.w[5]);
+  return make_float2(lerpf(lerpf(ax, __uint_as_float(q.w[2]), tx), lerpf(cx, __uint_as_float(q.w[6]), tx), ty),
+                     lerpf(lerpf(ay, __uint_as_float(q.w[3]), tx), lerpf(cy, __uint_as_float(q.w[7]), tx), ty));
 }
 
 }  // namespace pbrcu

@@ -14,6 +14,7 @@ namespace pbrcu {
 constexpr int kTile = PBRCU_TILE;
 constexpr int kShadeThreads = kTile * kTile;
 constexpr int kShadeCtasPerSm = 3;  // 85 registers: the four IBL records stay in registers across the light loop
+constexpr int kShadeCtasPerSmTex = 4;  // texture-unit mode: 8 result registers instead of 24 record registers -> 64 registers
 constexpr int kMaxLights = 1024;   // API limit for max_per_tile
 constexpr int kLightChunk = 128;   // lights staged in shared memory at a time
 constexpr float kInvPi = 0.31830988618379067154f;
@@ -37,6 +38,15 @@ struct ShadeParams {
   const float2* lut;
   uint32_t lut_res;
   const uint4 *q_pref, *q_irr, *q_lut;  // footprint records (pbrcu_ibl_accel); NULL: plain textures
+  cudaTextureObject_t t_pref, t_irr;    // flagged hardware textures of the same maps (IBL_TEX)
+};
+
+// how the ambient term samples the three IBL textures
+enum : int {
+  IBL_PLAIN = 0,    // four 8-byte loads per bilinear tap from the plain chains, fp32 weights
+  IBL_RECORDS = 1,  // one 256-bit footprint-record load per tap, fp32 weights (bit-identical to IBL_PLAIN)
+  IBL_TEX = 2       // texture unit for the prefiltered and irradiance cubes (8-bit weights), records where
+                    // the filtered contrast flag is set and for the LUT
 };
 
 __device__ __forceinline__ float2 lut_sample(const float2* lut, int res, float u, float v) {
@@ -117,8 +127,8 @@ __device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, 
   }
 }
 
-template <bool ACCEL>
-__global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
+template <int IBL>
+__global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerSmTex : kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
   __shared__ float4 s_pos[kLightChunk];   // {position, 1/range^2 (0 = unlimited)}
   __shared__ float4 s_col[kLightChunk];   // {colour * intensity}
   __shared__ TileStage s_tile[2];
@@ -199,15 +209,27 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     // survive: 24 warps x 32 lanes x 4 incoherent 128-byte lines exceed the L1) ----
     IblTaps taps;
     Quad8 qi, q0, q1, ql;
+    float4 tpre = make_float4(0.f, 0.f, 0.f, 0.f), tirr = tpre;
+    Tap tlut;
     float3 Rv = make_float3(0.f, 0.f, 0.f);
     if (lit && p.has_ibl) {
       Rv = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
-      if (ACCEL) {
+      if (IBL == IBL_RECORDS) {
         taps = make_ibl_taps(p, N, Rv, NoV, rough);
         q0 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p0));
         q1 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p1));
         qi = ldg_quad(p.q_irr + 2 * size_t(taps.i_irr));
         ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
+      }
+      if (IBL == IBL_TEX) {
+        // face selection, clamp-to-edge bilinear on two levels and the level blend in the texture unit
+        const float lod = fminf(rough * float(p.pref.nmips - 1), float(p.pref.nmips - 1));
+        tpre = texCubemapLod<float4>(p.t_pref, Rv.x, Rv.y, Rv.z, lod);
+        tirr = texCubemapLod<float4>(p.t_irr, N.x, N.y, N.z, 0.0f);
+        // a level fraction the unit would round to 1 hides the finer level's flags: treat it as flagged
+        if (lod - floorf(lod) > 0.995f) tirr.w = 1.0f;
+        tlut = make_tap(NoV, rough, float(p.lut_res));
+        ql = ldg_quad(p.q_lut + 2 * size_t(tlut.idx));
       }
     }
 
@@ -274,14 +296,28 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     if (p.has_ibl) {
       RGB irr, pre;
       float2 sb;
-      if (ACCEL) {
+      if (IBL == IBL_RECORDS) {
         irr = quad_bilinear_rgb(qi, taps.irr_tx, taps.irr_ty);
         pre = quad_bilinear_rgb(q0, taps.p0_tx, taps.p0_ty);
         const RGB pr1 = quad_bilinear_rgb(q1, taps.p1_tx, taps.p1_ty);
         pre.r = lerpf(pre.r, pr1.r, taps.lod_f); pre.g = lerpf(pre.g, pr1.g, taps.lod_f); pre.b = lerpf(pre.b, pr1.b, taps.lod_f);
-        const float ax = __uint_as_float(ql.w[0]), ay = __uint_as_float(ql.w[1]), cx = __uint_as_float(ql.w[4]), cy = __uint_as_float(ql.w[5]);
-        sb.x = lerpf(lerpf(ax, __uint_as_float(ql.w[2]), taps.lut_tx), lerpf(cx, __uint_as_float(ql.w[6]), taps.lut_tx), taps.lut_ty);
-        sb.y = lerpf(lerpf(ay, __uint_as_float(ql.w[3]), taps.lut_tx), lerpf(cy, __uint_as_float(ql.w[7]), taps.lut_tx), taps.lut_ty);
+        sb = quad_bilinear_lut(ql, taps.lut_tx, taps.lut_ty);
+      } else if (IBL == IBL_TEX) {
+        irr = RGB{tirr.x, tirr.y, tirr.z};
+        pre = RGB{tpre.x, tpre.y, tpre.z};
+        if (tpre.w > 0.0f || tirr.w > 0.0f) {
+          // a flagged texel took part in the fetch: the unit's 8-bit weights are not accurate enough for
+          // this footprint's contrast (around the sun), so redo both taps with fp32 weights from the records
+          taps = make_ibl_taps(p, N, Rv, NoV, rough);
+          q0 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p0));
+          q1 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p1));
+          qi = ldg_quad(p.q_irr + 2 * size_t(taps.i_irr));
+          irr = quad_bilinear_rgb(qi, taps.irr_tx, taps.irr_ty);
+          pre = quad_bilinear_rgb(q0, taps.p0_tx, taps.p0_ty);
+          const RGB pr1 = quad_bilinear_rgb(q1, taps.p1_tx, taps.p1_ty);
+          pre.r = lerpf(pre.r, pr1.r, taps.lod_f); pre.g = lerpf(pre.g, pr1.g, taps.lod_f); pre.b = lerpf(pre.b, pr1.b, taps.lod_f);
+        }
+        sb = quad_bilinear_lut(ql, tlut.tx, tlut.ty);
       } else {
         irr = cube_sample(p.irr, N, 0.0f);
         pre = cube_sample(p.pref, Rv, rough * float(p.pref.nmips - 1));
@@ -414,6 +450,12 @@ extern "C" int pbrcu_cluster_lights(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, cons
   return launch_check("cluster_lights_kernel");
 }
 
+extern "C" int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on) {
+  PBRCU_REQUIRE(ctx, "ctx is NULL");
+  ctx->shade_tex = on != 0;
+  return PBRCU_OK;
+}
+
 extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
                                    const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
                                    const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch, pbrcu_stream s) {
@@ -452,6 +494,7 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
       PBRCU_REQUIRE(a->pref_res == ibl->pref_res && a->pref_mips == ibl->pref_mips && a->irr_res == ibl->irr_res && a->lut_res == ibl->lut_res,
                     "ibl->accel was built for textures of another shape");
       p.q_pref = a->pref; p.q_irr = a->irr; p.q_lut = a->lut;
+      p.t_pref = a->pref_tex.tex; p.t_irr = a->irr_tex.tex;
     }
   }
   p.ntx = (p.x1 + kTile - 1) / kTile - p.tx0;
@@ -459,8 +502,11 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
   PBRCU_REQUIRE(uint64_t(p.ntiles) * p.ntx < (1ull << 32), "rect too large");  // 16x16 tiles: beyond 100k x 100k pixels
   p.ntx_magic = p.ntx == 1 ? 0u : uint32_t(((1ull << 32) + p.ntx - 1) / p.ntx);  // 0: one tile per row
   // persistent grid: kShadeCtasPerSm CTAs per SM walk the tiles round-robin
-  const uint32_t grid = min(p.ntiles, uint32_t(ctx->sm_count) * kShadeCtasPerSm);
-  if (p.q_pref) shade_ggx_kernel<true><<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
-  else shade_ggx_kernel<false><<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(p);
+  const bool tex = p.q_pref && ctx->shade_tex;
+  const uint32_t grid = min(p.ntiles, uint32_t(ctx->sm_count) * (tex ? kShadeCtasPerSmTex : kShadeCtasPerSm));
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (tex) shade_ggx_kernel<IBL_TEX><<<grid, kShadeThreads, 0, st>>>(p);
+  else if (p.q_pref) shade_ggx_kernel<IBL_RECORDS><<<grid, kShadeThreads, 0, st>>>(p);
+  else shade_ggx_kernel<IBL_PLAIN><<<grid, kShadeThreads, 0, st>>>(p);
   return launch_check("shade_ggx_kernel");
 }

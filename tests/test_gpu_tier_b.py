@@ -166,15 +166,60 @@ def test_shade_matches_oracle(pbr, dev, oracle, w, h, nl, use_ibl):
     peak = float(max(f16(want).max(), 1.0))
     assert_hdr_parity(got, want, peak=peak, rel_tol=REL, what=f"shade {w}x{h} nl={nl}")
     assert (got[g["bg"]] == 0).all()
-    if use_ibl:  # the footprint-record path (one 256-bit load per bilinear tap) must be bit-identical
+    if use_ibl:
         ibl2 = make_ibl_struct(pbr, host, bufs, dev, accel=True)
-        assert dev.lib.ibl_accel_bytes(ibl2.accel) == 32 * (oracle.chain_texels(host["pref_res"], host["pref_mips"]) + host["irr"].size // 4 + host["lut"].size // 2)
+        n_cube = oracle.chain_texels(host["pref_res"], host["pref_mips"]) + host["irr"].size // 4
+        # 32-byte footprint records of the three maps + the flagged RGBA16F texture copies of the two cubes
+        assert dev.lib.ibl_accel_bytes(ibl2.accel) == 32 * (n_cube + host["lut"].size // 2) + 8 * n_cube
         out2 = dev.alloc(w * h * 8)
+        # opt-in: texture-unit fetches (8-bit weights), fp32-weight records where the contrast flag is set
+        dev.lib.shade_set_texture_unit(dev.ctx, 1)
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr if ld else None, nl, None, C.byref(ibl2), pbr.WHOLE, out2.ptr, w * 8, None)
+        dev.sync()
+        dev.lib.shade_set_texture_unit(dev.ctx, 0)
+        assert_hdr_parity(out2.download((h, w, 4), np.uint16), want, peak=peak, rel_tol=REL, what=f"shade (texture unit) {w}x{h} nl={nl}")
+        # default: one 256-bit footprint-record load per bilinear tap, bit-identical to the plain path
         dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr if ld else None, nl, None, C.byref(ibl2), pbr.WHOLE, out2.ptr, w * 8, None)
         dev.sync()
         got2 = out2.download((h, w, 4), np.uint16)
-        assert np.array_equal(got2, got), f"accel path differs from the plain path in {np.count_nonzero(got2 != got)} values"
+        assert np.array_equal(got2, got), f"record path differs from the plain path in {np.count_nonzero(got2 != got)} values"
         dev.lib.ibl_accel_free(dev.ctx, ibl2.accel)
+
+
+def test_shade_texture_unit_on_sharp_environment(pbr, dev, oracle):
+    """K3's texture-unit path with a hard-edged 5e3 sun in the environment (the worst case for the unit's 8-bit
+    weights): the contrast flags must route the affected pixels to the fp32-weight records."""
+    res, nmips, ns, ires, lres = 128, 8, 256, 32, 128
+    env = synth_environment(512, 256, 3, sun=5.0e3)
+    src = dev.upload(env)
+    n = oracle.chain_texels(res, nmips)
+    chain_d = dev.alloc(n * 8)
+    dev.lib.ibl_equirect_to_cube(dev.ctx, src.ptr, 512, 256, res, chain_d.ptr, None)
+    dev.lib.ibl_cube_mipgen(dev.ctx, chain_d.ptr, res, nmips, None)
+    pref_d = dev.alloc(n * 8)
+    dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, pref_d.ptr, 0, nmips - 1, 0, 1, None)
+    irr_d = dev.alloc(6 * ires * ires * 8)
+    dev.lib.ibl_irradiance(dev.ctx, chain_d.ptr, res, nmips, ires, ns, irr_d.ptr, None)
+    lut_d = dev.alloc(lres * lres * 8)
+    dev.lib.ibl_brdf_lut(dev.ctx, lres, ns, lut_d.ptr, None)
+    dev.sync()
+    host = dict(irr=irr_d.download((6, ires, ires, 4), np.uint16), pref=pref_d.download((n, 4), np.uint16),
+                pref_res=res, pref_mips=nmips, lut=lut_d.download((lres, lres, 2), np.float32))
+    w, h = 320, 180
+    g = synth_gbuffer(w, h, seed=11, tier_b=True)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    ibl = make_ibl_struct(pbr, host, (irr_d, pref_d, lut_d), dev, accel=True)
+    cam = (0.5, -1.0, 12.0)
+    out = dev.alloc(w * h * 8)
+    dev.lib.shade_set_texture_unit(dev.ctx, 1)
+    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), None, 0, None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
+    dev.sync()
+    dev.lib.shade_set_texture_unit(dev.ctx, 0)
+    got = out.download((h, w, 4), np.uint16)
+    _, want = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, synth_lights(0, seed=1), host)
+    assert f16(want).max() > 50.0, "the sun should be visible in some reflections"
+    assert_hdr_parity(got, want, peak=float(f16(want).max()), rel_tol=REL, what="shade (texture unit), sharp environment")
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
 
 
 def test_shade_tiled_lights_equal_brute_force(pbr, dev, oracle):
