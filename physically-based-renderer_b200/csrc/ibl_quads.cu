@@ -10,6 +10,7 @@ namespace pbrcu {
 constexpr float kShadeTexRelRange = 0.12f;
 
 // faces of one level: n = 6*res*res records (n_faces*res*res in general)
+template <bool CUBE>
 __global__ void __launch_bounds__(256) build_quads8_kernel(const uint2* __restrict__ src, uint4* __restrict__ dst, int res, size_t n) {
   for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
     const int x = int(i % res);
@@ -19,8 +20,13 @@ __global__ void __launch_bounds__(256) build_quads8_kernel(const uint2* __restri
     const uint2* f = src + face * size_t(res) * res;
     const uint2 t00 = __ldg(f + size_t(y) * res + x), t10 = __ldg(f + size_t(y) * res + x1);
     const uint2 t01 = __ldg(f + size_t(y1) * res + x), t11 = __ldg(f + size_t(y1) * res + x1);
-    dst[2 * i] = make_uint4(t00.x, t00.y, t10.x, t10.y);
-    dst[2 * i + 1] = make_uint4(t01.x, t01.y, t11.x, t11.y);
+    if (CUBE) {  // {rg00, rg10, rg01, rg11}, {b00|b10, b01|b11, 0, 0}
+      dst[2 * i] = make_uint4(t00.x, t10.x, t01.x, t11.x);
+      dst[2 * i + 1] = make_uint4((t00.y & 0xFFFFu) | (t10.y << 16), (t01.y & 0xFFFFu) | (t11.y << 16), 0u, 0u);
+    } else {
+      dst[2 * i] = make_uint4(t00.x, t00.y, t10.x, t10.y);
+      dst[2 * i + 1] = make_uint4(t01.x, t01.y, t11.x, t11.y);
+    }
   }
 }
 
@@ -28,7 +34,8 @@ static int build_level(const uint2* src, uint4* dst, int res, int faces, int sms
   const size_t n = size_t(faces) * res * res;
   const size_t want = (n + 255) / 256;
   const unsigned blocks = unsigned(want < size_t(sms) * 16 ? want : size_t(sms) * 16);
-  build_quads8_kernel<<<blocks, 256, 0, st>>>(src, dst, res, n);
+  if (faces == 6) build_quads8_kernel<true><<<blocks, 256, 0, st>>>(src, dst, res, n);
+  else build_quads8_kernel<false><<<blocks, 256, 0, st>>>(src, dst, res, n);
   return launch_check("build_quads8_kernel");
 }
 
@@ -78,7 +85,7 @@ extern "C" int pbrcu_ibl_accel_build(pbrcu_ctx* ctx, const pbrcu_ibl* ibl, pbrcu
       return rc;
     }
   }
-  // the LUT's float2 texels are 8 bytes like an RGBA16F texel: the same gather builds its records
+  // the LUT's float2 texels are 8 bytes like an RGBA16F texel: the same gather builds its records (plain copy of the four)
   if ((rc = build_level(static_cast<const uint2*>(ibl->irradiance), a->irr, int(ibl->irr_res), 6, ctx->sm_count, st)) ||
       (rc = build_level(reinterpret_cast<const uint2*>(ibl->lut), a->lut, int(ibl->lut_res), 1, ctx->sm_count, st))) {
     pbrcu_ibl_accel_free(ctx, a);

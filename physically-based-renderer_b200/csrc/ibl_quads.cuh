@@ -1,7 +1,10 @@
 // ibl_quads.cuh -- "footprint record" layout of the IBL textures for the GGX shading kernel (K3).
-// Record of texel (x, y) of a face = the four texels {(x,y), (x+1,y), (x,y+1), (x+1,y+1)} with x+1 / y+1
-// clamped to the face edge, 4 x RGBA16F = 32 bytes (LUT: 4 x float2 = 32 bytes).  A bilinear tap with
-// clamp-to-edge is then one 256-bit load: with fx = max(u*res - 0.5, 0) the footprint origin is
+// Record of texel (x, y) of a face = the four texels t00 = (x,y), t10 = (x+1,y), t01 = (x,y+1), t11 = (x+1,y+1)
+// with x+1 / y+1 clamped to the face edge, one 32-byte sector.  Cube maps (RGBA16F, alpha unused) store
+// {rg00, rg10, rg01, rg11, b00|b10, b01|b11, 0, 0} so that the 24 bytes a tap needs are six registers with
+// the halves already where the filter wants them (a plain copy of the four texels made ptxas repack the
+// blue halves right after the load, i.e. before the light loop that should cover the load's latency);
+// the LUT stores its 4 x float2.  A bilinear tap with clamp-to-edge is then one sector: with fx = max(u*res - 0.5, 0) the footprint origin is
 // floor(fx) in [0, res-1] and the weights frac(fx) are 0 where the oracle's clamp makes both taps equal,
 // so the result is bit-identical to cube.cuh's four-load face_bilinear.
 #pragma once
@@ -20,7 +23,8 @@ struct pbrcu_ibl_accel {
 
 namespace pbrcu {
 
-struct Quad8 { uint32_t w[8]; };
+struct Quad8 { uint32_t w[8]; };  // LUT record
+struct Quad6 { uint32_t w[6]; };  // cube-map record (the 24 bytes in use)
 
 // one 256-bit load; the records are re-read by neighbouring pixels, so let them allocate in L1
 __device__ __forceinline__ Quad8 ldg_quad(const uint4* p) {
@@ -28,6 +32,14 @@ __device__ __forceinline__ Quad8 ldg_quad(const uint4* p) {
   asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=r"(q.w[0]), "=r"(q.w[1]), "=r"(q.w[2]), "=r"(q.w[3]), "=r"(q.w[4]), "=r"(q.w[5]), "=r"(q.w[6]), "=r"(q.w[7])
                : "l"(p));
+  return q;
+}
+
+// the 24 bytes of a cube-map record: same sector, a 128-bit and a 64-bit load
+__device__ __forceinline__ Quad6 ldg_rec(const uint4* p) {
+  Quad6 q;
+  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q.w[0]), "=r"(q.w[1]), "=r"(q.w[2]), "=r"(q.w[3]) : "l"(p));
+  asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2+16];" : "=r"(q.w[4]), "=r"(q.w[5]) : "l"(p));
   return q;
 }
 
@@ -66,22 +78,22 @@ __device__ __forceinline__ Tap make_tap(float u, float v, float resf) {
   return t;
 }
 
-// bilinear of the RGB channels of one record: lerp(lerp(t00,t10,tx), lerp(t01,t11,tx), ty), lerp(a,b,t) = fma(t,b-a,a)
-__device__ __forceinline__ RGB quad_bilinear_rgb(const Quad8& q, float tx, float ty) {
+// bilinear of the RGB channels of one cube-map record: lerp(lerp(t00,t10,tx), lerp(t01,t11,tx), ty), lerp(a,b,t) = fma(t,b-a,a)
+__device__ __forceinline__ RGB quad_bilinear_rgb(const Quad6& q, float tx, float ty) {
   RGB o;
   {
-    const float a = h_lo(q.w[0]), c = h_lo(q.w[4]);
-    const float top = fmaf(tx, hsub_lo(q.w[2], a), a), bot = fmaf(tx, hsub_lo(q.w[6], c), c);
+    const float a = h_lo(q.w[0]), c = h_lo(q.w[2]);
+    const float top = fmaf(tx, hsub_lo(q.w[1], a), a), bot = fmaf(tx, hsub_lo(q.w[3], c), c);
     o.r = fmaf(ty, bot - top, top);
   }
   {
-    const float a = h_hi(q.w[0]), c = h_hi(q.w[4]);
-    const float top = fmaf(tx, hsub_hi(q.w[2], a), a), bot = fmaf(tx, hsub_hi(q.w[6], c), c);
+    const float a = h_hi(q.w[0]), c = h_hi(q.w[2]);
+    const float top = fmaf(tx, hsub_hi(q.w[1], a), a), bot = fmaf(tx, hsub_hi(q.w[3], c), c);
     o.g = fmaf(ty, bot - top, top);
   }
   {
-    const float a = h_lo(q.w[1]), c = h_lo(q.w[5]);
-    const float top = fmaf(tx, hsub_lo(q.w[3], a), a), bot = fmaf(tx, hsub_lo(q.w[7], c), c);
+    const float a = h_lo(q.w[4]), c = h_lo(q.w[5]);
+    const float top = fmaf(tx, hsub_hi(q.w[4], a), a), bot = fmaf(tx, hsub_hi(q.w[5], c), c);
     o.b = fmaf(ty, bot - top, top);
   }
   return o;

@@ -3,18 +3,23 @@
 // K3c the per-tile light lists.  No reference counterpart; definition:
 // glTF 2.0 Appendix B + KHR_lights_punctual + Karis 2013 (restated for the CPU checker as pbro_shade_pixel).
 //
-// Persistent CTAs (4 per SM) walk the 16x16 pixel tiles of the rect.  The five G-buffer planes of the
+// The light loop evaluates TWO lights per iteration as packed f32x2 instructions (f32x2.cuh: light 2j in
+// the low lane, light 2j+1 in the high lane, the pixel's own quantities as scalar-broadcast operands) --
+// the kernel is bound by issue slots, not by the FMA pipe, and a packed instruction does two lights' worth
+// per slot.  Persistent CTAs (3 per SM) walk the 16x16 pixel tiles of the rect.  The five G-buffer planes of the
 // NEXT tile are staged into shared memory with cp.async while the current tile is shaded, so the DRAM
 // latency of the streaming reads never sits on a warp's critical path; the tile's light list is staged
 // in shared memory; the IBL footprint records of a pixel are prefetched into L1 before its light loop.
+#include "f32x2.cuh"
 #include "ibl_quads.cuh"
 
 namespace pbrcu {
 
 constexpr int kTile = PBRCU_TILE;
-constexpr int kShadeThreads = kTile * kTile;
-constexpr int kShadeCtasPerSm = 3;  // 85 registers: the four IBL records stay in registers across the light loop
-constexpr int kShadeCtasPerSmTex = 4;  // texture-unit mode: 8 result registers instead of 24 record registers -> 64 registers
+constexpr int kHalfRows = kTile / 2;
+constexpr int kShadeThreads = kTile * kHalfRows;  // a CTA iteration shades half a tile (16 x 8 pixels): finer register granularity
+constexpr int kClusterThreads = kTile * kTile;    // K3c: one thread per pixel of a tile
+constexpr int kShadeCtasPerSm = 5;  // <= 102 registers: the four IBL records stay in registers across the light loop
 constexpr int kMaxLights = 1024;   // API limit for max_per_tile
 constexpr int kLightChunk = 128;   // lights staged in shared memory at a time
 constexpr float kInvPi = 0.31830988618379067154f;
@@ -113,10 +118,21 @@ struct TileStage {
   uint32_t orm[kShadeThreads];
 };
 
-__device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, uint32_t tile) {
+// work item = half a tile: item >> 1 = tile of the rect (row-major), item & 1 = upper / lower 8 rows
+struct ItemPos { uint32_t tx, ty, x, y; };
+__device__ __forceinline__ ItemPos item_pos(const ShadeParams& p, uint32_t item) {
+  const uint32_t tile = item >> 1;
   const uint32_t trow = p.ntx_magic ? __umulhi(tile, p.ntx_magic) : tile;
-  const uint32_t ty = p.ty0 + trow, tx = p.tx0 + (tile - trow * p.ntx);
-  const uint32_t x = tx * kTile + (threadIdx.x % kTile), y = ty * kTile + (threadIdx.x / kTile);
+  ItemPos q;
+  q.ty = p.ty0 + trow; q.tx = p.tx0 + (tile - trow * p.ntx);
+  q.x = q.tx * kTile + (threadIdx.x % kTile);
+  q.y = q.ty * kTile + (item & 1u) * kHalfRows + (threadIdx.x / kTile);
+  return q;
+}
+
+__device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, uint32_t item) {
+  const ItemPos q = item_pos(p, item);
+  const uint32_t x = q.x, y = q.y;
   if (x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1) {
     const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8;
     cp_async8(&st.px[1][threadIdx.x], p.nrm + o8);
@@ -128,38 +144,46 @@ __device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, 
 }
 
 template <int IBL>
-__global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerSmTex : kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
-  __shared__ float4 s_pos[kLightChunk];   // {position, 1/range^2 (0 = unlimited)}
-  __shared__ float4 s_col[kLightChunk];   // {colour * intensity}
+__global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
+  // staged lights, two per entry (lane 0 = light 2j, lane 1 = light 2j+1):
+  // s_lp[j] = {{x0,x1,y0,y1}, {z0,z1,w0,w1}} with w = 1/range^2 (0 = unlimited); s_lc[j] = {{r0,r1,g0,g1}, {b0,b1,-,-}}
+  // with rgb = colour * intensity.  An odd count is padded with a null light (colour 0: it adds exactly 0).
+  __shared__ float4 s_lp[kLightChunk];
+  __shared__ float4 s_lc[kLightChunk];
   __shared__ TileStage s_tile[2];
 
   auto stage_lights = [&](const uint16_t* idx, uint32_t base, uint32_t cnt) {
-    if (threadIdx.x < cnt) {
-      const uint32_t li = idx ? uint32_t(__ldg(idx + base + threadIdx.x)) : base + threadIdx.x;
-      const float4 a = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * li);
-      const float4 b = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * li + 1);
-      s_pos[threadIdx.x] = make_float4(a.x, a.y, a.z, a.w > 0.0f ? __fdividef(1.0f, a.w * a.w) : 0.0f);
-      s_col[threadIdx.x] = make_float4(b.x * b.w, b.y * b.w, b.z * b.w, 0.0f);
+    if (threadIdx.x < ((cnt + 1) & ~1u)) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+      if (threadIdx.x < cnt) {
+        const uint32_t li = idx ? uint32_t(__ldg(idx + base + threadIdx.x)) : base + threadIdx.x;
+        a = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * li);
+        b = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * li + 1);
+      }
+      float* lp = reinterpret_cast<float*>(s_lp + (threadIdx.x & ~1u)) + (threadIdx.x & 1u);
+      float* lc = reinterpret_cast<float*>(s_lc + (threadIdx.x & ~1u)) + (threadIdx.x & 1u);
+      lp[0] = a.x; lp[2] = a.y; lp[4] = a.z; lp[6] = a.w > 0.0f ? __fdividef(1.0f, a.w * a.w) : 0.0f;
+      lc[0] = b.x * b.w; lc[2] = b.y * b.w; lc[4] = b.z * b.w;
     }
   };
   // without tile lists and with few lights, every tile uses the same staged list: stage it once
   const bool one_list = p.tile_counts == nullptr && p.n_lights <= uint32_t(kLightChunk);
   if (one_list) stage_lights(nullptr, 0, p.n_lights);
 
-  uint32_t tile = blockIdx.x;
+  const uint32_t nitems = 2 * p.ntiles;
+  uint32_t tile = blockIdx.x;  // work item (half tile)
   int stage = 0;
-  if (tile < p.ntiles) stage_tile(p, s_tile[0], tile);
+  if (tile < nitems) stage_tile(p, s_tile[0], tile);
   cp_async_commit();
   if (one_list) __syncthreads();
 
-  for (; tile < p.ntiles; tile += gridDim.x, stage ^= 1) {
-    if (tile + gridDim.x < p.ntiles) stage_tile(p, s_tile[stage ^ 1], tile + gridDim.x);  // next tile in flight
+  for (; tile < nitems; tile += gridDim.x, stage ^= 1) {
+    if (tile + gridDim.x < nitems) stage_tile(p, s_tile[stage ^ 1], tile + gridDim.x);  // next item in flight
     cp_async_commit();
     cp_async_wait<1>();  // this tile's group has landed (each thread reads only its own slots)
 
-    const uint32_t trow = p.ntx_magic ? __umulhi(tile, p.ntx_magic) : tile;
-    const uint32_t ty = p.ty0 + trow, tx = p.tx0 + (tile - trow * p.ntx);
-    const uint32_t x = tx * kTile + (threadIdx.x % kTile), y = ty * kTile + (threadIdx.x / kTile);
+    const ItemPos ip = item_pos(p, tile);
+    const uint32_t tx = ip.tx, ty = ip.ty, x = ip.x, y = ip.y;
     const bool inside = x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1;
 
     // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
@@ -208,7 +232,8 @@ __global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerS
     // the light loop, whose ~400 instructions cover their L2 / DRAM latency (a prefetch into L1 does not
     // survive: 24 warps x 32 lanes x 4 incoherent 128-byte lines exceed the L1) ----
     IblTaps taps;
-    Quad8 qi, q0, q1, ql;
+    Quad6 qi, q0, q1;
+    Quad8 ql;
     float4 tpre = make_float4(0.f, 0.f, 0.f, 0.f), tirr = tpre;
     Tap tlut;
     float3 Rv = make_float3(0.f, 0.f, 0.f);
@@ -216,9 +241,9 @@ __global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerS
       Rv = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
       if (IBL == IBL_RECORDS) {
         taps = make_ibl_taps(p, N, Rv, NoV, rough);
-        q0 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p0));
-        q1 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p1));
-        qi = ldg_quad(p.q_irr + 2 * size_t(taps.i_irr));
+        q0 = ldg_rec(p.q_pref + 2 * size_t(taps.i_p0));
+        q1 = ldg_rec(p.q_pref + 2 * size_t(taps.i_p1));
+        qi = ldg_rec(p.q_irr + 2 * size_t(taps.i_irr));
         ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
       }
       if (IBL == IBL_TEX) {
@@ -241,7 +266,8 @@ __global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerS
       nl = min(__ldg(p.tile_counts + t), p.max_per_tile);
       idx = p.tile_indices + size_t(t) * p.max_per_tile;
     }
-    float dr = 0.f, dg = 0.f, db = 0.f;  // summed separately, in light order, like the oracle
+    f2 dr2 = dup(0.f), dg2 = dr2, db2 = dr2;  // per lane: the even / the odd lights of the list, in list order
+    const f2 one = dup(1.0f);
     for (uint32_t base = 0; base < nl; base += kLightChunk) {
       const uint32_t cnt = min(nl - base, uint32_t(kLightChunk));
       if (!one_list) {
@@ -250,41 +276,43 @@ __global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerS
         __syncthreads();
       }
       if (!lit) continue;
-      for (uint32_t i = 0; i < cnt; ++i) {
-        const float4 lp = s_pos[i];
-        const float dx = lp.x - P.x, dy = lp.y - P.y, dz = lp.z - P.z;
-        const float d2 = fmaxf(dx * dx + dy * dy + dz * dz, 1e-8f);
-        const float invd = rsq(d2);
-        const float NoL = sat((N.x * dx + N.y * dy + N.z * dz) * invd);
-        const float q = d2 * lp.w;                          // (d/range)^2; 0 for unlimited range
-        const float att = invd * invd * sat(1.0f - q * q);  // inverse square * clamp(1 - (d/range)^4, 0, 1)
-        const float w = att * NoL;
-        if (w > 0.0f) {
-          const float hx = fmaf(dx, invd, V.x), hy = fmaf(dy, invd, V.y), hz = fmaf(dz, invd, V.z);  // V + L
-          const float hh = fmaxf(hx * hx + hy * hy + hz * hz, 1e-12f);  // V = -L: grazing back-facing pixel
-          const float hinv = rsq(hh);
+      for (uint32_t j = 0; 2 * j < cnt; ++j) {
+        const float4 l0 = s_lp[2 * j], l1 = s_lp[2 * j + 1];
+        const f2 dx = sub2(pk(l0.x, l0.y), dup(P.x)), dy = sub2(pk(l0.z, l0.w), dup(P.y)), dz = sub2(pk(l1.x, l1.y), dup(P.z));
+        const f2 d2 = max2(fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))), 1e-8f);
+        const f2 invd = map2(d2, rsq);
+        const f2 NoL = sat2(mul2(fma2(dup(N.z), dz, fma2(dup(N.y), dy, mul2(dup(N.x), dx))), invd));
+        const f2 qq = mul2(d2, pk(l1.z, l1.w));               // (d/range)^2; 0 for unlimited range
+        const f2 win = sat2(sub2(one, mul2(qq, qq)));         // clamp(1 - (d/range)^4, 0, 1)
+        const f2 w = mul2(mul2(mul2(invd, invd), win), NoL);  // inverse square * window * N.L
+        if (lo(w) > 0.0f || hi(w) > 0.0f) {
+          const f2 hx = fma2(dx, invd, dup(V.x)), hy = fma2(dy, invd, dup(V.y)), hz = fma2(dz, invd, dup(V.z));  // V + L
+          const f2 hh = max2(fma2(hz, hz, fma2(hy, hy, mul2(hx, hx))), 1e-12f);  // V = -L: grazing back-facing pixel
+          const f2 nhinv = map2(hh, [](float x) { return -rsq(x); });
           // |V| = |L| = 1: V.h = 1 + V.L = |h|^2 / 2, so V.H = |h| / 2 (in [0, 1] by construction)
-          const float VoH = 0.5f * hh * hinv;
-          // 1 - NoH^2 without cancellation: s = |H - N|^2 = 2 - 2 N.H  =>  u = 1 - (N.H)^2 = s (1 - s/4)
+          const f2 VoH = mul2(mul2(hh, nhinv), dup(-0.5f));
+          // 1 - NoH^2 without cancellation: s = |N - H|^2 = 2 - 2 N.H  =>  u = 1 - (N.H)^2 = s (1 - s/4)
           // (what the oracle takes from |N x H|^2).  D's denominator NoH^2 (a2 - 1) + 1 with
           // NoH = max(N.H, 0) is then u (1 - a2) + a2, or just u where N.H < 0, i.e. s > 2.
-          const float ex = fmaf(hx, hinv, -N.x), ey = fmaf(hy, hinv, -N.y), ez = fmaf(hz, hinv, -N.z);
-          const float sq = ex * ex + ey * ey + ez * ez;
-          const float u = fmaf(sq * sq, -0.25f, sq);
-          const float dd = sq > 2.0f ? u : fmaf(u, oma2, a2);
-          const float vl = NoL * NoL * oma2 + a2;
-          const float den = NoL * visV + NoV * (vl * rsq(vl));
-          const float dv = a2h * rcp(dd * dd * den);  // D * Vis = a2/(pi dd^2) * 0.5/den
-          const float t = 1.0f - VoH, t2 = t * t, fc = t2 * t2 * t;
-          const float Fr = fmaf(omF0r, fc, F0r), Fg = fmaf(omF0g, fc, F0g), Fb = fmaf(omF0b, fc, F0b);
-          const float4 lc = s_col[i];
+          const f2 ex = fma2(hx, nhinv, dup(N.x)), ey = fma2(hy, nhinv, dup(N.y)), ez = fma2(hz, nhinv, dup(N.z));
+          const f2 sq = fma2(ez, ez, fma2(ey, ey, mul2(ex, ex)));
+          const f2 u = fma2(mul2(sq, sq), dup(-0.25f), sq);
+          const f2 ddn = fma2(u, dup(oma2), dup(a2));
+          const f2 dd = pk(lo(sq) > 2.0f ? lo(u) : lo(ddn), hi(sq) > 2.0f ? hi(u) : hi(ddn));
+          const f2 vl = fma2(mul2(NoL, NoL), dup(oma2), dup(a2));
+          const f2 den = fma2(dup(NoV), mul2(vl, map2(vl, rsq)), mul2(NoL, dup(visV)));
+          const f2 dv = mul2(dup(a2h), map2(mul2(mul2(dd, dd), den), rcp));  // D * Vis = a2/(pi dd^2) * 0.5/den
+          const f2 t = sub2(one, VoH), t2 = mul2(t, t), fc = mul2(mul2(t2, t2), t);
+          const f2 Fr = fma2(dup(omF0r), fc, dup(F0r)), Fg = fma2(dup(omF0g), fc, dup(F0g)), Fb = fma2(dup(omF0b), fc, dup(F0b));
+          const float4 c0 = s_lc[2 * j], c1 = s_lc[2 * j + 1];
           // (1 - F) c_diff/pi + F D Vis = c_diff/pi + F (D Vis - c_diff/pi)
-          dr = fmaf(fmaf(Fr, dv - cdpr, cdpr), lc.x * w, dr);
-          dg = fmaf(fmaf(Fg, dv - cdpg, cdpg), lc.y * w, dg);
-          db = fmaf(fmaf(Fb, dv - cdpb, cdpb), lc.z * w, db);
+          dr2 = fma2(fma2(Fr, sub2(dv, dup(cdpr)), dup(cdpr)), mul2(pk(c0.x, c0.y), w), dr2);
+          dg2 = fma2(fma2(Fg, sub2(dv, dup(cdpg)), dup(cdpg)), mul2(pk(c0.z, c0.w), w), dg2);
+          db2 = fma2(fma2(Fb, sub2(dv, dup(cdpb)), dup(cdpb)), mul2(pk(c1.x, c1.y), w), db2);
         }
       }
     }
+    const float dr = lo(dr2) + hi(dr2), dg = lo(dg2) + hi(dg2), db = lo(db2) + hi(db2);
     if (!inside) continue;
     uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8;
     if (!lit) {
@@ -309,9 +337,9 @@ __global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerS
           // a flagged texel took part in the fetch: the unit's 8-bit weights are not accurate enough for
           // this footprint's contrast (around the sun), so redo both taps with fp32 weights from the records
           taps = make_ibl_taps(p, N, Rv, NoV, rough);
-          q0 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p0));
-          q1 = ldg_quad(p.q_pref + 2 * size_t(taps.i_p1));
-          qi = ldg_quad(p.q_irr + 2 * size_t(taps.i_irr));
+          q0 = ldg_rec(p.q_pref + 2 * size_t(taps.i_p0));
+          q1 = ldg_rec(p.q_pref + 2 * size_t(taps.i_p1));
+          qi = ldg_rec(p.q_irr + 2 * size_t(taps.i_irr));
           irr = quad_bilinear_rgb(qi, taps.irr_tx, taps.irr_ty);
           pre = quad_bilinear_rgb(q0, taps.p0_tx, taps.p0_ty);
           const RGB pr1 = quad_bilinear_rgb(q1, taps.p1_tx, taps.p1_ty);
@@ -336,13 +364,13 @@ __global__ void __launch_bounds__(kShadeThreads, IBL == IBL_TEX ? kShadeCtasPerS
 
 // ---- K3c: per 16x16 tile, world-space AABB of the tile's non-cleared positions, then every light
 // whose range sphere meets it, in ascending light index (so K3 sums in the oracle's order).
-__global__ void __launch_bounds__(kShadeThreads) cluster_lights_kernel(
+__global__ void __launch_bounds__(kClusterThreads) cluster_lights_kernel(
     const uint8_t* pos, const uint8_t* nrm, size_t pitch8, uint32_t width, uint32_t height,
     const pbrcu_light* lights, uint32_t n_lights, uint32_t* counts, uint16_t* indices, uint32_t tiles_x,
     uint32_t max_per_tile) {
-  __shared__ float s_min[3][kShadeThreads / 32], s_max[3][kShadeThreads / 32];
+  __shared__ float s_min[3][kClusterThreads / 32], s_max[3][kClusterThreads / 32];
   __shared__ float s_box[6];
-  __shared__ uint32_t s_warp_cnt[kShadeThreads / 32];
+  __shared__ uint32_t s_warp_cnt[kClusterThreads / 32];
   __shared__ uint32_t s_base;
   const uint32_t tile = blockIdx.y * tiles_x + blockIdx.x;
   const uint32_t x = blockIdx.x * kTile + threadIdx.x % kTile, y = blockIdx.y * kTile + threadIdx.x / kTile;
@@ -370,13 +398,13 @@ __global__ void __launch_bounds__(kShadeThreads) cluster_lights_kernel(
   __syncthreads();
   if (threadIdx.x < 3) {
     float a = s_min[threadIdx.x][0], b = s_max[threadIdx.x][0];
-    for (int w = 1; w < kShadeThreads / 32; ++w) { a = fminf(a, s_min[threadIdx.x][w]); b = fmaxf(b, s_max[threadIdx.x][w]); }
+    for (int w = 1; w < kClusterThreads / 32; ++w) { a = fminf(a, s_min[threadIdx.x][w]); b = fmaxf(b, s_max[threadIdx.x][w]); }
     s_box[threadIdx.x] = a; s_box[3 + threadIdx.x] = b;
   }
   if (threadIdx.x == 0) s_base = 0;
   __syncthreads();
   const bool empty = s_box[0] > s_box[3];
-  for (uint32_t base = 0; base < n_lights; base += kShadeThreads) {
+  for (uint32_t base = 0; base < n_lights; base += kClusterThreads) {
     const uint32_t i = base + threadIdx.x;
     bool hit = false;
     if (i < n_lights && !empty) {
@@ -402,7 +430,7 @@ __global__ void __launch_bounds__(kShadeThreads) cluster_lights_kernel(
     __syncthreads();
     if (threadIdx.x == 0) {
       uint32_t tot = 0;
-      for (int w = 0; w < kShadeThreads / 32; ++w) tot += s_warp_cnt[w];
+      for (int w = 0; w < kClusterThreads / 32; ++w) tot += s_warp_cnt[w];
       s_base += tot;
     }
     __syncthreads();
@@ -444,7 +472,7 @@ extern "C" int pbrcu_cluster_lights(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, cons
   PBRCU_REQUIRE(n_lights <= 65535 && (n_lights == 0 || lights_dev), "n_lights out of range or lights NULL");
   PBRCU_REQUIRE(tiles->tiles_x == (g->width + kTile - 1) / kTile && tiles->tiles_y == (g->height + kTile - 1) / kTile, "tile grid does not match the gbuffer");
   dim3 grid(tiles->tiles_x, tiles->tiles_y);
-  cluster_lights_kernel<<<grid, kShadeThreads, 0, static_cast<cudaStream_t>(s)>>>(
+  cluster_lights_kernel<<<grid, kClusterThreads, 0, static_cast<cudaStream_t>(s)>>>(
       static_cast<const uint8_t*>(g->positions), static_cast<const uint8_t*>(g->normals), g->pitch8, g->width, g->height,
       lights_dev, n_lights, tiles->counts, tiles->indices, tiles->tiles_x, tiles->max_per_tile);
   return launch_check("cluster_lights_kernel");
@@ -499,11 +527,11 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
   }
   p.ntx = (p.x1 + kTile - 1) / kTile - p.tx0;
   p.ntiles = p.ntx * ((p.y1 + kTile - 1) / kTile - p.ty0);
-  PBRCU_REQUIRE(uint64_t(p.ntiles) * p.ntx < (1ull << 32), "rect too large");  // 16x16 tiles: beyond 100k x 100k pixels
+  PBRCU_REQUIRE(uint64_t(p.ntiles) * p.ntx < (1ull << 31), "rect too large");  // 16x16 tiles: beyond 100k x 100k pixels
   p.ntx_magic = p.ntx == 1 ? 0u : uint32_t(((1ull << 32) + p.ntx - 1) / p.ntx);  // 0: one tile per row
-  // persistent grid: kShadeCtasPerSm CTAs per SM walk the tiles round-robin
+  // persistent grid: kShadeCtasPerSm CTAs per SM walk the half-tile work items round-robin
   const bool tex = p.q_pref && ctx->shade_tex;
-  const uint32_t grid = min(p.ntiles, uint32_t(ctx->sm_count) * (tex ? kShadeCtasPerSmTex : kShadeCtasPerSm));
+  const uint32_t grid = min(2 * p.ntiles, uint32_t(ctx->sm_count) * kShadeCtasPerSm);
   cudaStream_t st = static_cast<cudaStream_t>(s);
   if (tex) shade_ggx_kernel<IBL_TEX><<<grid, kShadeThreads, 0, st>>>(p);
   else if (p.q_pref) shade_ggx_kernel<IBL_RECORDS><<<grid, kShadeThreads, 0, st>>>(p);

@@ -243,7 +243,10 @@ def test_shade_tiled_lights_equal_brute_force(pbr, dev, oracle):
     dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr, nl, None, C.byref(ibl), pbr.WHOLE, o2.ptr, w * 8, None)
     dev.sync()
     tiled, brute = o1.download((h, w, 4), np.uint16), o2.download((h, w, 4), np.uint16)
-    assert np.array_equal(tiled, brute), "tiled light lists changed the result"
+    # K3 sums the even and the odd entries of a light list in separate lanes, so culling a light changes the
+    # association of the fp32 sum (not its terms): equal up to fp32 rounding, i.e. at most 1 fp16 ulp apart
+    assert (np.abs(tiled.astype(np.int32) - brute.astype(np.int32)) <= 1).all(), "tiled light lists changed the result"
+    assert np.mean(tiled != brute) < 0.02
     cnt = pbr.DeviceBuffer.__new__(pbr.DeviceBuffer); cnt.dev, cnt.nbytes, cnt.ptr = dev, tiles.tiles_x * tiles.tiles_y * 4, tiles.counts
     counts = cnt.download((tiles.tiles_y, tiles.tiles_x), np.uint32)
     assert counts.mean() < 0.6 * nl, "clustering culled nothing"
