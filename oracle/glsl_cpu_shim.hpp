@@ -210,6 +210,7 @@ struct Plane {
   int width = 0, height = 0;
   std::size_t pitch = 0;  // bytes
   Fmt fmt = Fmt::RGBA16F;
+  bool repeat = false;    // material textures: all-zero VkSamplerCreateInfo (gltf/Asset.cpp:116-117) = nearest + repeat
 };
 inline vec4 fetch(Plane const& p, int x, int y) {
   auto const* row = static_cast<unsigned char const*>(p.data) + std::size_t(y) * p.pitch;
@@ -245,6 +246,11 @@ struct sampler2D {
 inline vec4 texture(sampler2D const& s, vec2 uv) {
   int x = int(std::floor(uv.x * float(s.plane.width)));
   int y = int(std::floor(uv.y * float(s.plane.height)));
+  if (s.plane.repeat) {
+    x %= s.plane.width; if (x < 0) x += s.plane.width;
+    y %= s.plane.height; if (y < 0) y += s.plane.height;
+    return fetch(s.plane, x, y);
+  }
   x = x < 0 ? 0 : (x >= s.plane.width ? s.plane.width - 1 : x);   // clamp-to-edge
   y = y < 0 ? 0 : (y >= s.plane.height ? s.plane.height - 1 : y);
   return fetch(s.plane, x, y);
@@ -284,3 +290,5 @@ using namespace glsl;
 // `layout(set=0,binding=0) uniform SceneUBO { Camera cam; };` -> static thread_local anonymous union
 #define SceneUBO union
 #define MaterialUBO union
+// `layout(push_constant) uniform PC { mat4x4 model; mat3x3 normalModel; } pc;` -> a thread-local struct variable
+#define PC struct

@@ -99,6 +99,27 @@ void pbro_shade_image(const void* positions, const void* normals, const void* al
                       int nlights, const pbro_ibl* ibl, float* out_f32, void* out_f16,
                       size_t out_pitch, int nthreads);
 
+/* ---- geometry pass (pbr_oracle_raster.c): vertex.glsl / fragment.glsl + the fixed-function rasteriser ---- */
+typedef struct { const void* texels; int width, height; size_t pitch; } pbro_texture; /* R8G8B8A8_UNORM */
+typedef struct {
+  const void* vertices;         /* MeshVertex: pos3 nrm3 tan4 uv2, 48 bytes (MeshVertex.hpp:14-19) */
+  const uint16_t* indices;
+  uint32_t first_index, index_count;
+  int32_t vertex_offset;
+  float model[16];              /* ModelPushConstant.model, column-major */
+  float normal_model[12];       /* ModelPushConstant.normalModel: three vec4 columns */
+  float color[4];               /* MaterialData.color */
+  pbro_texture color_tex, normal_tex;
+  float occlusion, roughness, metallic, emissive[3]; /* Tier B planes (no reference counterpart) */
+} pbro_draw;
+void pbro_geom_vertex(const float model[16], const float normal_model[12], const float view[16], const float proj[16],
+                      const float vertex[12], float clip[4], float attrs[14]);
+void pbro_geom_fragment(const float attrs[14], const float color[4], const pbro_texture* color_tex, const pbro_texture* normal_tex,
+                        float out_pos[4], float out_nrm[4], float out_alb[4]);
+void pbro_geometry_pass(const pbro_draw* draws, int n_draws, const float view[16], const float proj[16], int W, int H,
+                        uint16_t* positions, uint16_t* normals, uint16_t* albedo, float* depth, uint8_t* orm, uint16_t* emissive,
+                        uint32_t* prim_id);
+
 int pbro_max_threads(void);
 
 #ifdef __cplusplus

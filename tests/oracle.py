@@ -27,10 +27,22 @@ class Ibl(C.Structure):
                 ("lut", vp), ("lut_res", ci)]
 
 
+class Texture(C.Structure):
+    _fields_ = [("texels", vp), ("width", ci), ("height", ci), ("pitch", sz)]
+
+
+class Draw(C.Structure):
+    """pbro_draw: one drawIndexed of the geometry pass (PbrRenderSystem.cpp:441-461)."""
+    _fields_ = [("vertices", vp), ("indices", vp), ("first_index", C.c_uint32), ("index_count", C.c_uint32),
+                ("vertex_offset", C.c_int32), ("model", cf * 16), ("normal_model", cf * 12), ("color", cf * 4),
+                ("color_tex", Texture), ("normal_tex", Texture), ("occlusion", cf), ("roughness", cf), ("metallic", cf),
+                ("emissive", cf * 3)]
+
+
 def build_oracle(force: bool = False) -> Path:
     if force or not ORACLE_SO.exists() or any(
             p.stat().st_mtime > ORACLE_SO.stat().st_mtime
-            for p in [ORACLE_DIR / n for n in ("pbr_oracle.c", "pbr_oracle_ibl.c", "pbr_oracle.h", "pbr_detmath.h")]):
+            for p in [ORACLE_DIR / n for n in ("pbr_oracle.c", "pbr_oracle_ibl.c", "pbr_oracle_raster.c", "pbr_oracle.h", "pbr_detmath.h")]):
         subprocess.run(["make", "-C", str(ORACLE_DIR), "oracle"], check=True, capture_output=True)
     return ORACLE_SO
 
@@ -82,9 +94,40 @@ class Oracle:
         L.pbro_cube_dir_to_face_uv.argtypes = [vp, vp, vp, vp]
         L.pbro_brdf_lut_texel.argtypes = [ci, ci, ci, ci, vp]
         L.pbro_tonemap_pixel.argtypes = [vp, vp]
+        L.pbro_geom_vertex.argtypes = [vp] * 7
+        L.pbro_geom_fragment.argtypes = [vp, vp, C.POINTER(Texture), C.POINTER(Texture), vp, vp, vp]
+        L.pbro_geometry_pass.argtypes = [C.POINTER(Draw), ci, vp, vp, ci, ci, vp, vp, vp, vp, vp, vp, vp]
 
     def max_threads(self) -> int:
         return self.lib.pbro_max_threads()
+
+    # ---- geometry pass ----
+    def geom_vertex(self, model, normal_model, view, proj, vertex):
+        clip, attrs = np.zeros(4, np.float32), np.zeros(14, np.float32)
+        a = [np.ascontiguousarray(v, np.float32) for v in (model, normal_model, view, proj, vertex)]
+        self.lib.pbro_geom_vertex(_p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]), _p(clip), _p(attrs))
+        return clip, attrs
+
+    def geom_fragment(self, attrs, color, color_tex, normal_tex):
+        o = [np.zeros(4, np.float32) for _ in range(3)]
+        ct, nt = _texture(color_tex), _texture(normal_tex)
+        self.lib.pbro_geom_fragment(_p(np.ascontiguousarray(attrs, np.float32)), _p(np.ascontiguousarray(color, np.float32)),
+                                    C.byref(ct), C.byref(nt), _p(o[0]), _p(o[1]), _p(o[2]))
+        return o
+
+    def geometry_pass(self, draws, view, proj, W, H, extended=False):
+        """draws: list of dicts (see make_draw).  Returns the planes the reference's geometry pass writes."""
+        arr = (Draw * max(1, len(draws)))()
+        for i, d in enumerate(draws):
+            fill_draw(arr[i], d, lambda a: a.ctypes.data)
+        out = dict(pos=np.zeros((H, W, 4), np.uint16), nrm=np.zeros((H, W, 4), np.uint16), alb=np.zeros((H, W, 4), np.uint16),
+                   depth=np.zeros((H, W), np.float32), prim=np.zeros((H, W), np.uint32))
+        if extended:
+            out.update(orm=np.zeros((H, W, 4), np.uint8), emi=np.zeros((H, W, 4), np.uint16))
+        self.lib.pbro_geometry_pass(arr, len(draws), _p(np.ascontiguousarray(view, np.float32)), _p(np.ascontiguousarray(proj, np.float32)),
+                                    W, H, _p(out["pos"]), _p(out["nrm"]), _p(out["alb"]), _p(out["depth"]),
+                                    _p(out["orm"]) if extended else None, _p(out["emi"]) if extended else None, _p(out["prim"]))
+        return out
 
     # ---- Tier A ----
     def lighting(self, pos, nrm, alb, cam, rect=None, nthreads=0):
@@ -190,6 +233,24 @@ class RefShaders:
         self.lib.pbr_ref_gamma_correct.argtypes = [vp, cf, vp]
         self.lib.pbr_ref_aces_tonemap.argtypes = [vp, vp]
         self.lib.pbr_ref_fullscreen_vertex.argtypes = [ci, vp]
+        self.lib.pbr_ref_geom_vertex.argtypes = [vp] * 7
+        self.lib.pbr_ref_geom_fragment.argtypes = [vp, vp, vp, ci, ci, sz, vp, ci, ci, sz, vp, vp, vp]
+
+    def geom_vertex(self, model, normal_model, view, proj, vertex):
+        """assets/shaders/geometry_pass/vertex.glsl::main, compiled for the CPU."""
+        clip, attrs = np.zeros(4, np.float32), np.zeros(14, np.float32)
+        a = [np.ascontiguousarray(v, np.float32) for v in (model, normal_model, view, proj, vertex)]
+        self.lib.pbr_ref_geom_vertex(_p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]), _p(clip), _p(attrs))
+        return clip, attrs
+
+    def geom_fragment(self, attrs, color, color_tex, normal_tex):
+        """assets/shaders/geometry_pass/fragment.glsl::main, compiled for the CPU."""
+        o = [np.zeros(4, np.float32) for _ in range(3)]
+        self.lib.pbr_ref_geom_fragment(_p(np.ascontiguousarray(attrs, np.float32)), _p(np.ascontiguousarray(color, np.float32)),
+                                       _p(color_tex), color_tex.shape[1], color_tex.shape[0], color_tex.strides[0],
+                                       _p(normal_tex), normal_tex.shape[1], normal_tex.shape[0], normal_tex.strides[0],
+                                       _p(o[0]), _p(o[1]), _p(o[2]))
+        return o
 
     def lighting(self, pos, nrm, alb, cam, nthreads=0):
         H, W = pos.shape[:2]
@@ -226,6 +287,137 @@ class RefShaders:
         out = np.zeros(6, np.float32)
         self.lib.pbr_ref_fullscreen_vertex(i, _p(out))
         return out
+
+
+def _texture(img: np.ndarray) -> Texture:
+    assert img.dtype == np.uint8 and img.ndim == 3 and img.shape[2] == 4 and img.flags.c_contiguous
+    return Texture(img.ctypes.data, img.shape[1], img.shape[0], img.strides[0])
+
+
+def fill_draw(dst, d: dict, addr):
+    """Fills a pbro_draw / pbrcu_draw-shaped ctypes struct from a draw dict; `addr(x)` maps the dict's arrays
+    (numpy on the host, device buffers on the GPU) to addresses."""
+    dst.vertices, dst.indices = addr(d["vertices"]), addr(d["indices"])
+    dst.first_index, dst.index_count, dst.vertex_offset = d["first_index"], d["index_count"], d["vertex_offset"]
+    dst.model[:] = np.asarray(d["model"], np.float32).reshape(-1).tolist()
+    dst.normal_model[:] = np.asarray(d["normal_model"], np.float32).reshape(-1).tolist()
+    dst.color[:] = [float(c) for c in d["color"]]
+    for name in ("color_tex", "normal_tex"):
+        t, img = getattr(dst, name), d[name]
+        t.texels, t.width, t.height, t.pitch = addr(img), d[name + "_shape"][1], d[name + "_shape"][0], d[name + "_shape"][1] * 4
+    dst.occlusion, dst.roughness, dst.metallic = d.get("occlusion", 1.0), d.get("roughness", 1.0), d.get("metallic", 1.0)
+    dst.emissive[:] = [float(c) for c in d.get("emissive", (0.0, 0.0, 0.0))]
+
+
+# ---- column-major 4x4 maths the way glm builds them (CameraData.hpp:23-32, ModelPushConstant.hpp:33-46); float64
+# here, rounded to fp32 once: these are INPUTS of the geometry pass, identical for the oracle and the device ----
+def look_at_rh(eye, center, up=(0.0, -1.0, 0.0)):
+    eye, center, up = (np.asarray(v, np.float64) for v in (eye, center, up))
+    f = center - eye; f /= np.linalg.norm(f)
+    s = np.cross(f, up); s /= np.linalg.norm(s)
+    u = np.cross(s, f)
+    m = np.eye(4)
+    m[0, :3], m[1, :3], m[2, :3] = s, u, -f
+    m[0, 3], m[1, 3], m[2, 3] = -s @ eye, -u @ eye, f @ eye
+    return m  # row-major maths matrix; use .T.reshape(-1) for column-major storage
+
+
+def perspective_rh_no(fovy, aspect, near=0.01, far=1024.0):
+    t = np.tan(fovy / 2)
+    m = np.zeros((4, 4))
+    m[0, 0], m[1, 1] = 1 / (aspect * t), 1 / t
+    m[2, 2], m[3, 2], m[2, 3] = -(far + near) / (far - near), -1.0, -(2 * far * near) / (far - near)
+    return m
+
+
+def col_major(m):
+    return np.ascontiguousarray(np.asarray(m, np.float64).T.reshape(-1), np.float32)
+
+
+def model_push_constant(translation=(0, 0, 0), scale=(1, 1, 1), rot_axis=(0, 1, 0), rot_angle=0.0):
+    """(model[16], normalModel[12]) like makeModelPushConstant: T * R * S and mat3(transpose(inverse(model)))
+    padded to three vec4 columns."""
+    a = np.asarray(rot_axis, np.float64); a /= np.linalg.norm(a)
+    c, s = np.cos(rot_angle), np.sin(rot_angle)
+    K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    R = np.eye(3) + s * K + (1 - c) * K @ K
+    M = np.eye(4)
+    M[:3, :3] = R @ np.diag(np.asarray(scale, np.float64))
+    M[:3, 3] = translation
+    nm = np.linalg.inv(M).T[:3, :3]
+    nm4 = np.zeros((3, 4)); nm4[:, :3] = nm.T  # three columns, each padded to a vec4
+    return col_major(M), np.ascontiguousarray(nm4.reshape(-1), np.float32)
+
+
+def make_draw(vertices, indices, model=None, color=(1, 1, 1, 1), color_tex=None, normal_tex=None, first_index=0, index_count=None,
+              vertex_offset=0, **pbr):
+    if model is None:
+        model = model_push_constant()
+    if color_tex is None:
+        color_tex = np.full((1, 1, 4), 255, np.uint8)
+    if normal_tex is None:
+        normal_tex = np.array([[[128, 128, 255, 255]]], np.uint8)
+    vertices = np.ascontiguousarray(vertices, np.float32).reshape(-1, 12)
+    indices = np.ascontiguousarray(indices, np.uint16).reshape(-1)
+    d = dict(vertices=vertices, indices=indices, first_index=first_index, index_count=len(indices) - first_index if index_count is None else index_count,
+             vertex_offset=vertex_offset, model=model[0], normal_model=model[1], color=color,
+             color_tex=np.ascontiguousarray(color_tex), normal_tex=np.ascontiguousarray(normal_tex))
+    d["color_tex_shape"], d["normal_tex_shape"] = d["color_tex"].shape, d["normal_tex"].shape
+    d.update(pbr)
+    return d
+
+
+def mesh_vertex(pos, nrm=(0, 0, 1), tan=(1, 0, 0, 1), uv=(0, 0)):
+    return [*pos, *nrm, *tan, *uv]
+
+
+def uv_sphere(radius=1.0, stacks=16, slices=32):
+    """UV sphere as MeshVertex rows + uint16 triangle indices, outward normals, clockwise front faces in the
+    reference's framebuffer convention (y down), tangents along +longitude."""
+    v = []
+    for i in range(stacks + 1):
+        th = np.pi * i / stacks
+        for j in range(slices + 1):
+            ph = 2 * np.pi * j / slices
+            n = np.array([np.sin(th) * np.cos(ph), np.cos(th), np.sin(th) * np.sin(ph)])
+            t = np.array([-np.sin(ph), 0.0, np.cos(ph)])
+            v.append(mesh_vertex(radius * n, n, (*t, 1.0), (j / slices * 4, i / stacks * 2)))
+    idx = []
+    for i in range(stacks):
+        for j in range(slices):
+            a, b = i * (slices + 1) + j, (i + 1) * (slices + 1) + j
+            idx += [a, a + 1, b, a + 1, b + 1, b]
+    return np.array(v, np.float32), np.array(idx, np.uint16)
+
+
+def checker_texture(w, h, seed, normal_map=False):
+    rng = np.random.default_rng(seed)
+    img = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    if normal_map:  # perturbed +Z normals: xy in [96,160], z high
+        img[..., 0:2] = rng.integers(96, 161, (h, w, 2))
+        img[..., 2] = rng.integers(200, 256, (h, w))
+    img[..., 3] = 255
+    return img
+
+
+def raster_scene(seed=1, n_spheres=6):
+    """A small seeded scene for the geometry pass: textured spheres over a ground quad."""
+    rng = np.random.default_rng(seed)
+    sv, si = uv_sphere(1.0, 12, 24)
+    draws = []
+    for k in range(n_spheres):
+        m = model_push_constant(translation=rng.uniform(-4, 4, 3), scale=rng.uniform(0.5, 1.5, 3), rot_axis=rng.standard_normal(3),
+                                rot_angle=rng.uniform(0, 6.28))
+        draws.append(make_draw(sv, si, m, color=rng.uniform(0.3, 1.0, 4), color_tex=checker_texture(16, 8, seed + k),
+                               normal_tex=checker_texture(8, 8, seed + 100 + k, normal_map=True),
+                               occlusion=float(rng.uniform(0.5, 1)), roughness=float(rng.uniform(0.05, 1)), metallic=float(rng.integers(0, 2)),
+                               emissive=tuple(rng.uniform(0, 0.5, 3))))
+    g = 30.0
+    quad = np.array([mesh_vertex((-g, 2.0, -g), (0, -1, 0), (1, 0, 0, 1), (0, 0)), mesh_vertex((g, 2.0, -g), (0, -1, 0), (1, 0, 0, 1), (8, 0)),
+                     mesh_vertex((g, 2.0, g), (0, -1, 0), (1, 0, 0, 1), (8, 8)), mesh_vertex((-g, 2.0, g), (0, -1, 0), (1, 0, 0, 1), (0, 8))], np.float32)
+    draws.append(make_draw(quad, [0, 1, 2, 0, 2, 3], color=(0.8, 0.8, 0.8, 1.0), color_tex=checker_texture(32, 32, seed + 50)))
+    draws.append(make_draw(quad, [0, 2, 1, 0, 3, 2], color=(0.8, 0.8, 0.8, 1.0), color_tex=checker_texture(32, 32, seed + 50)))  # both windings: one is culled
+    return draws
 
 
 # ---- seeded synthetic inputs shared by tests, smoke and bench's cpu legs --------------------------
