@@ -217,6 +217,40 @@ int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t 
 int pbrcu_ibl_irradiance(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
                          uint32_t res, uint32_t nsamples, void* out_dev, pbrcu_stream s);
 
+/* ---- K10: the geometry pass (fills the G-buffer) -------------------------------------------------
+ * Replaces PbrRenderSystem::recordGeometryPass (src/pbr_engine/engine/pbr/PbrRenderSystem.cpp:367-465):
+ * clears the planes (colour 0, depth 1.0), then for every draw runs vertex.glsl:25-37, the fixed-function
+ * rasteriser (triangle list, uint16 indices + vertexOffset, back-face culling with front = CLOCKWISE, depth test
+ * LESS with depth write, viewport = G-buffer extent; PbrRenderSystem.cpp:176-187, core/PipelineBuilder.hpp:92-107)
+ * and fragment.glsl:19-31 (nearest + repeat sampling of R8G8B8A8_UNORM textures, gltf/Asset.cpp:116-117,
+ * image/LoadImage.cpp:27).  Coverage, depth and the three colour planes are bit-exact vs the CPU checker. */
+typedef struct {
+  const void* texels; /* device, R8G8B8A8_UNORM, row-major */
+  uint32_t width, height;
+  size_t pitch; /* bytes */
+} pbrcu_texture;
+typedef struct {
+  float color[4];                      /* MaterialData.color (Material.hpp:14-16) */
+  pbrcu_texture color_tex, normal_tex; /* both required, like the reference's loader (gltf/Asset.cpp:142-157) */
+  /* Tier B (no reference counterpart): constants written to the ORM / emissive planes when the G-buffer has them */
+  float occlusion, roughness, metallic, emissive[3];
+} pbrcu_material;
+typedef struct {
+  const void* vertices;    /* device; MeshVertex {vec3 position, vec3 normal, vec4 tangent, vec2 texCoords} = 48 bytes
+                              (MeshVertex.hpp:14-19) */
+  const uint16_t* indices; /* device */
+  uint32_t first_index, index_count; /* drawIndexed(indexCount, 1, firstIndex, vertexOffset, 0), PbrRenderSystem.cpp:458-459 */
+  int32_t vertex_offset;
+  float model[16];        /* ModelPushConstant.model, column-major (ModelPushConstant.hpp:13-17) */
+  float normal_model[12]; /* ModelPushConstant.normalModel: three vec4 columns */
+  pbrcu_material material;
+} pbrcu_draw;
+/* view / proj: CameraData.view / .proj, column-major (CameraData.hpp:14-18).  draws: HOST array (read before the call
+ * returns).  prim_id_dev (optional): width*height uint32, the winning triangle's sequence number over all draws, or
+ * 0xFFFFFFFF.  Scratch (visibility buffer, piece set-ups) lives in the context and grows on demand. */
+int pbrcu_geometry_pass(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float view[16], const float proj[16],
+                        const pbrcu_draw* draws, uint32_t n_draws, uint32_t* prim_id_dev, pbrcu_stream s);
+
 /* ---- synthetic inputs for benchmarks (generated on the device; never timed) ------------------ */
 /* kind 0 = gbuf_noise (every texel a hit, no coherence), 1 = gbuf_spheres (ray-cast spheres + plane,
  * ~25 % cleared background).  Fills every plane the G-buffer has. */

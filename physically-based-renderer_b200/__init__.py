@@ -54,6 +54,21 @@ class Ibl(C.Structure):
                 ("lut", C.c_void_p), ("lut_res", C.c_uint32), ("accel", C.c_void_p)]
 
 
+class Texture(C.Structure):
+    _fields_ = [("texels", C.c_void_p), ("width", C.c_uint32), ("height", C.c_uint32), ("pitch", C.c_size_t)]
+
+
+class Material(C.Structure):
+    _fields_ = [("color", C.c_float * 4), ("color_tex", Texture), ("normal_tex", Texture), ("occlusion", C.c_float),
+                ("roughness", C.c_float), ("metallic", C.c_float), ("emissive", C.c_float * 3)]
+
+
+class Draw(C.Structure):
+    """pbrcu_draw: one drawIndexed of the geometry pass."""
+    _fields_ = [("vertices", C.c_void_p), ("indices", C.c_void_p), ("first_index", C.c_uint32), ("index_count", C.c_uint32),
+                ("vertex_offset", C.c_int32), ("model", C.c_float * 16), ("normal_model", C.c_float * 12), ("material", Material)]
+
+
 class LightTiles(C.Structure):
     _fields_ = [("counts", C.c_void_p), ("indices", C.c_void_p),
                 ("tiles_x", C.c_uint32), ("tiles_y", C.c_uint32), ("max_per_tile", C.c_uint32)]
@@ -115,6 +130,7 @@ _SIGNATURES = {
     "pbrcu_ibl_cube_mipgen": (_i, [_vp, _vp, _u32, _u32, _vp]),
     "pbrcu_ibl_set_exact_filtering": (_i, [_vp, _i]),
     "pbrcu_shade_set_texture_unit": (_i, [_vp, _i]),
+    "pbrcu_geometry_pass": (_i, [_vp, C.POINTER(GBuffer), _vp, _vp, C.POINTER(Draw), C.c_uint32, _vp, _vp]),
     "pbrcu_ibl_prefilter_ggx": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, _vp]),
     "pbrcu_ibl_irradiance": (_i, [_vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
     "pbrcu_synth_gbuffer": (_i, [_vp, _PG, _i, _u64, _f3, _f3, _vp]),

@@ -73,6 +73,7 @@ extern "C" void pbrcu_ctx_destroy(pbrcu_ctx* ctx) {
   }
   if (ctx->pipe_start) cudaEventDestroy(ctx->pipe_start);
   pbrcu::cube_tex_destroy(&ctx->cube);
+  if (ctx->raster_scratch) cudaFree(ctx->raster_scratch);
   if (ctx->cube_stage) cudaFree(ctx->cube_stage);
   if (ctx->cube_mm) cudaFree(ctx->cube_mm);
   delete ctx;

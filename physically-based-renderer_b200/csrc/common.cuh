@@ -37,6 +37,8 @@ struct pbrcu_ctx {
   void *cube_stage, *cube_mm;  // staging copy with contrast flags in alpha; per-texel 3x3 min/max
   size_t cube_stage_bytes, cube_mm_bytes;
   bool exact_ibl_filter;  // K6/K7: software fp32-weight filtering instead of the texture unit
+  void* raster_scratch;  // K10: visibility buffer, piece set-ups, chunk queue, draw table (grown on demand)
+  size_t raster_bytes;
   bool shade_tex;         // K3: texture-unit fetches of the prefiltered / irradiance cubes (pbrcu_shade_set_texture_unit)
 };
 
