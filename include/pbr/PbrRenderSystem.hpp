@@ -9,15 +9,20 @@
 // CUDA kernel enqueued on the command buffer's stream:
 //   ShadingModel::BlinnPhong  (default) = assets/shaders/pbr/lighting.glsl, bit-for-bit the reference
 //   ShadingModel::MetallicRoughness     = GGX + point lights + IBL (Tier B, no reference counterpart)
-// The geometry pass runs when the scene holds mesh nodes; a scene without meshes shades whatever the
-// caller put into the G-buffer (the deferred hot path on its own).
+// The geometry pass (K10, a CUDA visibility-buffer rasteriser behind pbrcu_geometry_pass) runs when the scene
+// holds mesh nodes; a scene without meshes shades whatever the caller put into the G-buffer (the deferred hot
+// path on its own).
 #pragma once
 #include "pbr/Environment.hpp"
 #include "pbr/GBuffer.hpp"
+#include "pbr/ModelPushConstant.hpp"
 #include "pbr/Scene.hpp"
 
+#include <cstring>
 #include <memory>
 #include <stdexcept>
+#include <string>
+#include <vector>
 
 namespace pbr {
 enum class ShadingModel { BlinnPhong, MetallicRoughness };
@@ -57,12 +62,52 @@ public:
   }
 
 private:
-  auto recordGeometryPass(vk::CommandBuffer, Scene const& scene, GBuffer const&) -> void {
-    for (auto const& node : scene.iterateAllNodes())
-      if (node.getMesh())
-        throw std::runtime_error(
-            "pbr::PbrRenderSystem::render: the CUDA geometry pass (rasteriser, SURVEY 8(f) next-1) is not "
-            "built yet; shade a caller-filled G-buffer with a scene that holds no mesh nodes");
+  // PbrRenderSystem.cpp:367-465: clear, then one drawIndexed per primitive of every mesh node in iterateAllNodes()
+  // order, model / normal matrices from the node's own transform (makeModelPushConstant, :446-449).
+  // Runs when the scene holds mesh nodes; a scene without meshes keeps the caller-filled G-buffer.
+  auto recordGeometryPass(vk::CommandBuffer cmdBuffer, Scene const& scene, GBuffer const& gBuffer) -> void {
+    std::vector<pbrcu_draw> draws;
+    bool anyMesh = false;
+    for (auto const& node : scene.iterateAllNodes()) {
+      auto const& mesh = node.getMesh();
+      if (!mesh) continue;
+      anyMesh = true;
+      auto const transform = node.getTransform();
+      auto const pushConst = makeModelPushConstant(transform.position, transform.rotation, transform.scale);
+      for (auto const& primitive : mesh->getPrimitives()) {
+        if (!primitive.material) throw std::runtime_error("pbr::PbrRenderSystem::render: primitive without a material");
+        pbrcu_draw d {};
+        d.vertices = mesh->getVertexBuffer().get();
+        d.indices = static_cast<std::uint16_t const*>(mesh->getIndexBuffer().get());
+        d.first_index = primitive.firstIndex;
+        d.index_count = primitive.indexCount;
+        d.vertex_offset = static_cast<std::int32_t>(primitive.firstVertex);
+        static_assert(sizeof(pushConst.model) == sizeof(d.model) && sizeof(pushConst.normalModel) == sizeof(d.normal_model));
+        std::memcpy(d.model, &pushConst.model, sizeof(d.model));
+        std::memcpy(d.normal_model, &pushConst.normalModel, sizeof(d.normal_model));
+        auto const color = primitive.material->getMaterialData().color;
+        d.material.color[0] = color.x; d.material.color[1] = color.y; d.material.color[2] = color.z; d.material.color[3] = color.w;
+        auto const texture = [](std::shared_ptr<Image2D> const& img, char const* what) {
+          if (!img || img->getFormat() != vk::Format::eR8G8B8A8Unorm)
+            throw std::runtime_error(std::string("pbr::PbrRenderSystem::render: material needs an R8G8B8A8_UNORM ") + what + " texture");
+          return pbrcu_texture {img->getImage().data, img->getExtent().width, img->getExtent().height, img->getImage().pitch};
+        };
+        d.material.color_tex = texture(primitive.material->getColorTexture(), "colour");
+        d.material.normal_tex = texture(primitive.material->getNormalTexture(), "normal");
+        auto const mr = primitive.material->getMetallicRoughness();
+        d.material.occlusion = mr.occlusion; d.material.roughness = mr.roughness; d.material.metallic = mr.metallic;
+        d.material.emissive[0] = mr.emissive.x; d.material.emissive[1] = mr.emissive.y; d.material.emissive[2] = mr.emissive.z;
+        draws.push_back(d);
+      }
+    }
+    if (!anyMesh) return;
+    auto const camera = scene.findCamera();
+    if (!camera) draws.clear();  // no camera bound: the pass still clears the attachments
+    CameraData const cam = camera ? camera.value()->get() : CameraData {};
+    auto const g = gBuffer.raw();
+    core::check(pbrcu_geometry_pass(_gpu->getContext(), &g, reinterpret_cast<float const*>(&cam.view), reinterpret_cast<float const*>(&cam.proj), draws.data(),
+                                    static_cast<std::uint32_t>(draws.size()), nullptr, cmdBuffer.stream()),
+                "PbrRenderSystem: geometry pass");
   }
 
   auto recordLightingPass(vk::CommandBuffer cmdBuffer, Scene const& scene, GBuffer const& gBuffer,
