@@ -288,7 +288,72 @@ def extra_configs(scene, torch, dist, world, rank):
     out["config4_256_views_1080p"] = {"mpix_s": round(NV * WV * HV * 3 / (ms * 1e-3) / 1e6, 1), "ms_per_pass": round(ms / 3, 3),
                                       "views_per_rank": v1 - v0, "scaling": "strong (view blocks, no exchange)",
                                       "what": "pbrcu_shade_ggx_ibl per view, 4 point lights + IBL, one launch per view"}
+    out["geometry_pass_1080p"] = geometry_bench(scene, torch, dist, world, rank)
     return out
+
+
+def geometry_bench(scene, torch, dist, world, rank):
+    """K10 (pbrcu_geometry_pass, the CUDA visibility-buffer rasteriser that FILLS the G-buffer): 64 textured,
+    normal-mapped spheres of 9216 triangles each + two large quads = 589,828 triangles at 1920x1080, one camera per
+    step on an orbit; then the same frame end to end: geometry pass -> GGX shading (4 lights + IBL) -> the HDR image."""
+    pbr, lib, ctx = scene.pbr, scene.dev.lib, scene.dev.ctx
+    from oracle import checker_texture, col_major, look_at_rh, mesh_vertex, model_push_constant, perspective_rh_no, uv_sphere
+    W, H = 1920, 1080
+    rng = np.random.default_rng(7)
+
+    def dev_of(a):
+        t = scene.buf(a.nbytes)
+        t.copy_(torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)))
+        return t
+
+    sv, si = uv_sphere(1.0, 48, 96)
+    g = 40.0
+    quad = np.array([mesh_vertex((-g, 3.0, -g), (0, -1, 0), (1, 0, 0, 1), (0, 0)), mesh_vertex((g, 3.0, -g), (0, -1, 0), (1, 0, 0, 1), (16, 0)),
+                     mesh_vertex((g, 3.0, g), (0, -1, 0), (1, 0, 0, 1), (16, 16)), mesh_vertex((-g, 3.0, g), (0, -1, 0), (1, 0, 0, 1), (0, 16))], np.float32)
+    qi = np.array([0, 1, 2, 0, 2, 3, 0, 2, 1, 0, 3, 2], np.uint16)
+    vb, ib, qvb, qib = dev_of(sv), dev_of(si), dev_of(quad), dev_of(qi)
+    ctex, ntex, flat = dev_of(checker_texture(64, 64, 1)), dev_of(checker_texture(32, 32, 2, normal_map=True)), dev_of(np.array([[[128, 128, 255, 255]]], np.uint8))
+    n_draws = 65
+    draws = (pbr.Draw * n_draws)()
+
+    def fill(d, vbuf, ibuf, nidx, model, color, ct, cshape, nt, nshape, rough, metal):
+        d.vertices, d.indices, d.first_index, d.index_count, d.vertex_offset = vbuf.data_ptr(), ibuf.data_ptr(), 0, nidx, 0
+        d.model[:] = model[0].tolist(); d.normal_model[:] = model[1].tolist()
+        m = d.material
+        m.color[:] = [float(c) for c in color]
+        m.color_tex.texels, m.color_tex.width, m.color_tex.height, m.color_tex.pitch = ct.data_ptr(), cshape[1], cshape[0], cshape[1] * 4
+        m.normal_tex.texels, m.normal_tex.width, m.normal_tex.height, m.normal_tex.pitch = nt.data_ptr(), nshape[1], nshape[0], nshape[1] * 4
+        m.occlusion, m.roughness, m.metallic = 1.0, rough, metal
+
+    for k in range(64):
+        fill(draws[k], vb, ib, len(si), model_push_constant(rng.uniform(-8, 8, 3), rng.uniform(0.5, 1.5, 3), rng.standard_normal(3), rng.uniform(0, 6.28)),
+             rng.uniform(0.3, 1.0, 4), ctex, (64, 64), ntex, (32, 32), float(rng.uniform(0.05, 1.0)), float(rng.integers(0, 2)))
+    fill(draws[64], qvb, qib, len(qi), model_push_constant(), (0.8, 0.8, 0.8, 1.0), ctex, (64, 64), flat, (1, 1), 0.6, 0.0)
+    n_tris = 64 * (len(si) // 3) + len(qi) // 3
+    gb = pbr.GBuffer()
+    gb.width, gb.height, gb.pitch8, gb.pitch4 = W, H, W * 8, W * 4
+    planes = {k: scene.buf(W * H * (4 if k in ("depth", "orm") else 8)) for k in ("positions", "normals", "albedo", "depth", "orm", "emissive")}
+    for k, t in planes.items():
+        setattr(gb, k, t.data_ptr())
+    hdr = scene.buf(W * H * 8)
+    proj = col_major(perspective_rh_no(np.pi / 2, W / H))
+    cams = [(12.0 * np.cos(a), -2.0, 12.0 * np.sin(a)) for a in np.linspace(0, 2 * np.pi, 16, endpoint=False)]
+    views = [col_major(look_at_rh(c, (0, 0, 0))) for c in cams]
+
+    def geo(i):
+        lib.geometry_pass(ctx, C.byref(gb), views[i % 16].ctypes.data, proj.ctypes.data, draws, n_draws, None, scene.stream())
+
+    def frame(i):
+        geo(i)
+        lib.shade_ggx_ibl(ctx, C.byref(gb), pbr.f3(*cams[i % 16]), scene.lights.data_ptr(), N_LIGHTS, None, C.byref(scene.ibl), pbr.WHOLE, hdr.data_ptr(), W * 8, scene.stream())
+
+    ms_geo = timed(torch, dist, geo, 16, 4) / 16
+    ms_frame = timed(torch, dist, frame, 16, 4) / 16
+    covered = float((planes["normals"].view(torch.int16).view(-1, 4)[:, :3] != 0).any(dim=1).float().mean())
+    return {"triangles": n_tris, "draws": n_draws, "ms_geometry_pass": round(ms_geo, 4), "mtri_s": round(n_tris / (ms_geo * 1e-3) / 1e6, 1),
+            "ms_frame_geometry_plus_ggx_shading": round(ms_frame, 4), "frame_mpix_s": round(W * H / (ms_frame * 1e-3) / 1e6, 1),
+            "covered_fraction_last_view": round(covered, 3),
+            "what": "pbrcu_geometry_pass (setup, cover, chunk queue, resolve) per view; then + pbrcu_shade_ggx_ibl on the rasterised G-buffer"}
 
 
 def timed(torch, dist, fn, steps, warmup):

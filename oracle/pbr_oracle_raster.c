@@ -21,8 +21,9 @@
  *       bounds the fixed-point coordinates);
  *     - framebuffer coordinates are snapped to 1/256 pixel (RNE); coverage = exact 64-bit edge functions at
  *       pixel centres with the top-left rule;
+ *     - perspective divide by one reciprocal per vertex: iw = 1 / w, ndc = clip * iw;
  *     - barycentrics l_i = float(E_i) / float(2A); z_fb = (l0 z0 + l1 z1) + l2 z2; perspective-correct attributes
- *       a = ((p0 a0 + p1 a1) + p2 a2) / ((p0 + p1) + p2), p_i = l_i / w_i;
+ *       a = ((p0 a0 + p1 a1) + p2 a2) * (1 / ((p0 + p1) + p2)), p_i = l_i * iw_i;
  *     - every fp32 step is ONE correctly rounded operation in the order written here (compile with
  *       -ffp-contract=off); the device kernels use __fmul_rn/__fadd_rn/__fdiv_rn/__fsqrt_rn in the same order, so
  *       coverage, depth and all three colour planes are BIT-EXACT between this file and csrc/raster.cu.
@@ -154,11 +155,11 @@ static int setup_tri(const rvert* a, const rvert* b, const rvert* c, int W, int 
   for (int i = 0; i < 3; ++i)
     if (!(v[i]->clip[3] > 0.0f)) return 0;  /* w <= 0 survives the clip planes only at the degenerate point x = y = z = w = 0 */
   for (int i = 0; i < 3; ++i) {
-    const float iw = 1.0f / v[i]->clip[3];
-    const float xn = v[i]->clip[0] / v[i]->clip[3], yn = v[i]->clip[1] / v[i]->clip[3];
+    const float iw = 1.0f / v[i]->clip[3];   /* one reciprocal per vertex; the perspective divide multiplies by it */
+    const float xn = v[i]->clip[0] * iw, yn = v[i]->clip[1] * iw;
     const float xf = ((float)W * 0.5f) * xn + (float)W * 0.5f, yf = ((float)H * 0.5f) * yn + (float)H * 0.5f;
     t->X[i] = (int64_t)lrintf(xf * (float)RAST_SUB); t->Y[i] = (int64_t)lrintf(yf * (float)RAST_SUB);
-    t->z[i] = v[i]->clip[2] / v[i]->clip[3];
+    t->z[i] = v[i]->clip[2] * iw;
     t->iw[i] = iw;
     t->v[i] = v[i];
   }
@@ -231,9 +232,9 @@ void pbro_geometry_pass(const pbro_draw* draws, int n_draws, const float view[16
             depth[o] = z;
             if (prim_id) prim_id[o] = seq;
             const float p0 = l0 * t.iw[0], p1 = l1 * t.iw[1], p2 = l2 * t.iw[2];
-            const float den = (p0 + p1) + p2;
+            const float inv = 1.0f / ((p0 + p1) + p2);
             float at[14];
-            for (int i = 0; i < 14; ++i) at[i] = ((p0 * t.v[0]->a[i] + p1 * t.v[1]->a[i]) + p2 * t.v[2]->a[i]) / den;
+            for (int i = 0; i < 14; ++i) at[i] = ((p0 * t.v[0]->a[i] + p1 * t.v[1]->a[i]) + p2 * t.v[2]->a[i]) * inv;
             float op[4], on[4], oa[4];
             pbro_geom_fragment(at, d->color, &d->color_tex, &d->normal_tex, op, on, oa);
             for (int c = 0; c < 4; ++c) {
