@@ -293,7 +293,33 @@ def extra_configs(scene, torch, dist, world, rank):
                                       "views_per_rank": v1 - v0, "scaling": "strong (view blocks, no exchange)",
                                       "what": "pbrcu_shade_ggx_ibl per view, 4 point lights + IBL, one launch per view"}
     out["geometry_pass_1080p"] = geometry_bench(scene, torch, dist, world, rank)
+    out["config2_prefilter_sharded"] = prefilter_sharded(scene, torch, dist, world, rank)
     return out
+
+
+def prefilter_sharded(scene, torch, dist, world, rank):
+    """BASELINE configs[2]'s prefilter (2048^2, 12 mips, 1024 spp) over the ranks: every rank convolves its row
+    block of every level (pbrcu_ibl_prefilter_ggx shard/nshards) from its own replica of the source chain, then
+    the finished chain is all-gathered over NCCL so every GPU can shade with it.  Strong
+    scaling; the gather is inside the timed region, and the gathered chain is checked against the unsharded one."""
+    from pbr_b200.partition import gather_chain
+    lib, ctx = scene.dev.lib, scene.dev.ctx
+    dst = scene.buf(scene.pref.numel())
+
+    def conv(_):
+        lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, dst.data_ptr(), 0, CUBE_MIPS - 1, rank, world, scene.stream())
+
+    def step(i):
+        conv(i)
+        gather_chain(dst, CUBE_RES, CUBE_MIPS, world, rank, dist if world > 1 else None)
+
+    ms_conv = timed(torch, dist, conv, 3, 2) / 3
+    dst.zero_()
+    ms = timed(torch, dist, step, 3, 2) / 3
+    same = bool(torch.equal(dst, scene.pref))
+    return {"ms_prefilter_and_gather": round(ms, 3), "ms_prefilter_shard_only": round(ms_conv, 3), "shards": world,
+            "gathered_chain_equals_unsharded": same, "gather_bytes_per_rank": int(dst.numel() * (world - 1) // world),
+            "scaling": "strong (row blocks of every level; NCCL all-gather of the finished chain)"}
 
 
 def geometry_bench(scene, torch, dist, world, rank):

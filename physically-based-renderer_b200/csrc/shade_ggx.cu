@@ -130,8 +130,7 @@ __device__ __forceinline__ ItemPos item_pos(const ShadeParams& p, uint32_t item)
   return q;
 }
 
-__device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, uint32_t item) {
-  const ItemPos q = item_pos(p, item);
+__device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, const ItemPos& q) {
   const uint32_t x = q.x, y = q.y;
   if (x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1) {
     const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8;
@@ -143,7 +142,8 @@ __device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, 
   }
 }
 
-template <int IBL>
+// ONE_LIST: no tile lists and at most kLightChunk lights -- every item uses the same list, staged once per CTA.
+template <int IBL, bool ONE_LIST>
 __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
   // staged lights, two per entry (lane 0 = light 2j, lane 1 = light 2j+1):
   // s_lp[j] = {{x0,x1,y0,y1}, {z0,z1,w0,w1}} with w = 1/range^2 (0 = unlimited); s_lc[j] = {{r0,r1,g0,g1}, {b0,b1,-,-}}
@@ -151,7 +151,6 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
   __shared__ float4 s_lp[kLightChunk];
   __shared__ float4 s_lc[kLightChunk];
   __shared__ TileStage s_tile[2];
-
   auto stage_lights = [&](const uint16_t* idx, uint32_t base, uint32_t cnt) {
     if (threadIdx.x < ((cnt + 1) & ~1u)) {
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
@@ -166,23 +165,25 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
       lc[0] = b.x * b.w; lc[2] = b.y * b.w; lc[4] = b.z * b.w;
     }
   };
-  // without tile lists and with few lights, every tile uses the same staged list: stage it once
-  const bool one_list = p.tile_counts == nullptr && p.n_lights <= uint32_t(kLightChunk);
-  if (one_list) stage_lights(nullptr, 0, p.n_lights);
+  if (ONE_LIST) stage_lights(nullptr, 0, p.n_lights);
 
   const uint32_t nitems = 2 * p.ntiles;
   uint32_t tile = blockIdx.x;  // work item (half tile)
   int stage = 0;
-  if (tile < nitems) stage_tile(p, s_tile[0], tile);
+  ItemPos next = item_pos(p, tile);
+  if (tile < nitems) stage_tile(p, s_tile[0], next);
   cp_async_commit();
-  if (one_list) __syncthreads();
+  if (ONE_LIST) __syncthreads();
 
   for (; tile < nitems; tile += gridDim.x, stage ^= 1) {
-    if (tile + gridDim.x < nitems) stage_tile(p, s_tile[stage ^ 1], tile + gridDim.x);  // next item in flight
+    const ItemPos ip = next;
+    if (tile + gridDim.x < nitems) {  // next item in flight
+      next = item_pos(p, tile + gridDim.x);
+      stage_tile(p, s_tile[stage ^ 1], next);
+    }
     cp_async_commit();
     cp_async_wait<1>();  // this tile's group has landed (each thread reads only its own slots)
 
-    const ItemPos ip = item_pos(p, tile);
     const uint32_t tx = ip.tx, ty = ip.ty, x = ip.x, y = ip.y;
     const bool inside = x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1;
 
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     // ---- direct lighting: KHR_lights_punctual point lights, Cook-Torrance GGX / Smith / Schlick ----
     uint32_t nl = p.n_lights;
     const uint16_t* idx = nullptr;
-    if (p.tile_counts != nullptr) {
+    if (!ONE_LIST && p.tile_counts != nullptr) {
       const uint32_t t = ty * p.tiles_x + tx;
       nl = min(__ldg(p.tile_counts + t), p.max_per_tile);
       idx = p.tile_indices + size_t(t) * p.max_per_tile;
@@ -269,8 +270,8 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     f2 dr2 = dup(0.f), dg2 = dr2, db2 = dr2;  // per lane: the even / the odd lights of the list, in list order
     const f2 one = dup(1.0f);
     for (uint32_t base = 0; base < nl; base += kLightChunk) {
-      const uint32_t cnt = min(nl - base, uint32_t(kLightChunk));
-      if (!one_list) {
+      const uint32_t cnt = ONE_LIST ? nl : min(nl - base, uint32_t(kLightChunk));
+      if (!ONE_LIST) {
         __syncthreads();  // everyone is done with the previous chunk / tile
         stage_lights(idx, base, cnt);
         __syncthreads();
@@ -484,6 +485,12 @@ extern "C" int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on) {
   return PBRCU_OK;
 }
 
+template <int IBL>
+static void launch_shade(const ShadeParams& p, bool one_list, uint32_t grid, cudaStream_t st) {
+  if (one_list) shade_ggx_kernel<IBL, true><<<grid, kShadeThreads, 0, st>>>(p);
+  else shade_ggx_kernel<IBL, false><<<grid, kShadeThreads, 0, st>>>(p);
+}
+
 extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
                                    const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
                                    const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch, pbrcu_stream s) {
@@ -533,8 +540,9 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
   const bool tex = p.q_pref && ctx->shade_tex;
   const uint32_t grid = min(2 * p.ntiles, uint32_t(ctx->sm_count) * kShadeCtasPerSm);
   cudaStream_t st = static_cast<cudaStream_t>(s);
-  if (tex) shade_ggx_kernel<IBL_TEX><<<grid, kShadeThreads, 0, st>>>(p);
-  else if (p.q_pref) shade_ggx_kernel<IBL_RECORDS><<<grid, kShadeThreads, 0, st>>>(p);
-  else shade_ggx_kernel<IBL_PLAIN><<<grid, kShadeThreads, 0, st>>>(p);
+  const bool one_list = p.tile_counts == nullptr && p.n_lights <= uint32_t(kLightChunk);
+  if (tex) launch_shade<IBL_TEX>(p, one_list, grid, st);
+  else if (p.q_pref) launch_shade<IBL_RECORDS>(p, one_list, grid, st);
+  else launch_shade<IBL_PLAIN>(p, one_list, grid, st);
   return launch_check("shade_ggx_kernel");
 }

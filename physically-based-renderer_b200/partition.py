@@ -51,3 +51,39 @@ def _gather_list(tensor, bands, y0, y1, dist):
     dist.all_gather(parts, tensor[y0:y1].contiguous())
     for (b, e), p in zip(bands, parts):
         tensor[b:e] = p
+
+
+def chain_blocks(base_res: int, nmips: int, world: int, rank: int, texel_bytes: int = 8):
+    """Per-level (byte_offset, byte_length) of the rows of a cube mip chain that `rank` owns when the
+    prefilter is sharded (pbrcu_ibl_prefilter_ggx shard/nshards: level l has 6*res_l rows of res_l texels,
+    cut with split_range).  Level order and offsets are those of pbrcu_cube_chain_texels."""
+    out, off = [], 0
+    for m in range(nmips):
+        res = max(base_res >> m, 1)
+        b, e = split_range(6 * res, world, rank)
+        out.append((off + b * res * texel_bytes, (e - b) * res * texel_bytes))
+        off += 6 * res * res * texel_bytes
+    return out
+
+
+def gather_chain(chain, base_res: int, nmips: int, world: int, rank: int, dist=None, texel_bytes: int = 8):
+    """All-gathers a sharded prefilter result: `chain` is the full-size flat uint8 tensor in which this rank
+    has written only its chain_blocks; on return every rank holds the whole chain.  Levels whose rows divide
+    evenly go through ONE in-place all-gather each (NCCL: all_gather_into_tensor), the tiny tail levels
+    through per-owner broadcasts."""
+    if dist is None or world == 1:
+        return chain
+    blocks = [chain_blocks(base_res, nmips, world, r, texel_bytes) for r in range(world)]
+    for m in range(nmips):
+        lens = {blocks[r][m][1] for r in range(world)}
+        off0 = blocks[0][m][0]
+        if len(lens) == 1 and chain.is_cuda and hasattr(dist, "all_gather_into_tensor"):
+            n = blocks[0][m][1]
+            o, _ = blocks[rank][m]
+            dist.all_gather_into_tensor(chain[off0:off0 + n * world], chain[o:o + n])
+        else:
+            for r in range(world):
+                o, n = blocks[r][m]
+                if n:
+                    dist.broadcast(chain[o:o + n], src=r)
+    return chain

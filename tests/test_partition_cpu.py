@@ -21,6 +21,17 @@ def test_partitions_cover_exactly(pbr):
     assert P.view_block(256, 8, 7) == (224, 256)
     with pytest.raises(ValueError):
         P.split_range(10, 2, 2)
+    # prefilter shards: per level, the ranks' row blocks tile the level exactly
+    for world in (1, 2, 3, 8):
+        per_rank = [P.chain_blocks(2048, 12, world, r) for r in range(world)]
+        off = 0
+        for m in range(12):
+            res = 2048 >> m
+            assert per_rank[0][m][0] == off
+            for r in range(world - 1):
+                assert per_rank[r][m][0] + per_rank[r][m][1] == per_rank[r + 1][m][0]
+            off += 6 * res * res * 8
+            assert per_rank[-1][m][0] + per_rank[-1][m][1] == off
 
 
 def _worker(rank, world, port, height, q):
@@ -34,9 +45,18 @@ def _worker(rank, world, port, height, q):
     full = torch.arange(height * 32, dtype=torch.int32).reshape(height, 8, 4)
     frame[y0:y1] = full[y0:y1]  # "shade" only the rows this rank owns
     pbr.partition.gather_rows(frame, y0, y1, world, height, dist)
+    # the sharded prefilter's chain gather: every rank fills only its row blocks of every level
+    res, mips = 8, 4
+    nbytes = sum(6 * (res >> m) ** 2 * 8 for m in range(mips))
+    want = (torch.arange(nbytes, dtype=torch.int64) * 7 % 251).to(torch.uint8)
+    chain = torch.zeros(nbytes, dtype=torch.uint8)
+    for o, n in pbr.partition.chain_blocks(res, mips, world, rank):
+        chain[o:o + n] = want[o:o + n]
+    pbr.partition.gather_chain(chain, res, mips, world, rank, dist)
+    ok_chain = bool(torch.equal(chain, want))
     t = torch.tensor([float(rank + 1)])
     dist.all_reduce(t, op=dist.ReduceOp.MAX)  # the max-over-ranks timing reduction of bench.py
-    q.put((rank, bool(torch.equal(frame, full)), float(t.item())))
+    q.put((rank, bool(torch.equal(frame, full)) and ok_chain, float(t.item())))
     dist.destroy_process_group()
 
 
