@@ -348,6 +348,7 @@ def geometry_bench(scene, torch, dist, world, rank):
 
     def fill(d, vbuf, ibuf, nidx, model, color, ct, cshape, nt, nshape, rough, metal):
         d.vertices, d.indices, d.first_index, d.index_count, d.vertex_offset = vbuf.data_ptr(), ibuf.data_ptr(), 0, nidx, 0
+        d.vertex_count = vbuf.numel() // 48
         d.model[:] = model[0].tolist(); d.normal_model[:] = model[1].tolist()
         m = d.material
         m.color[:] = [float(c) for c in color]

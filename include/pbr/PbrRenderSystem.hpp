@@ -82,6 +82,7 @@ private:
         d.first_index = primitive.firstIndex;
         d.index_count = primitive.indexCount;
         d.vertex_offset = static_cast<std::int32_t>(primitive.firstVertex);
+        d.vertex_count = primitive.vertexCount;
         static_assert(sizeof(pushConst.model) == sizeof(d.model) && sizeof(pushConst.normalModel) == sizeof(d.normal_model));
         std::memcpy(d.model, &pushConst.model, sizeof(d.model));
         std::memcpy(d.normal_model, &pushConst.normalModel, sizeof(d.normal_model));

@@ -241,6 +241,10 @@ typedef struct {
   const uint16_t* indices; /* device */
   uint32_t first_index, index_count; /* drawIndexed(indexCount, 1, firstIndex, vertexOffset, 0), PbrRenderSystem.cpp:458-459 */
   int32_t vertex_offset;
+  uint32_t vertex_count;  /* PrimitiveSpan.vertexCount (Mesh.hpp): vertices this draw may address, counted from
+                             vertex_offset -- every index of the draw must be < vertex_count.  The vertex stage then runs
+                             once per vertex (post-transform cache in the context's scratch).  0 = unknown: the vertex
+                             stage is re-run per triangle and per pixel instead (same results, slower) */
   float model[16];        /* ModelPushConstant.model, column-major (ModelPushConstant.hpp:13-17) */
   float normal_model[12]; /* ModelPushConstant.normalModel: three vec4 columns */
   pbrcu_material material;

@@ -66,7 +66,7 @@ class Material(C.Structure):
 class Draw(C.Structure):
     """pbrcu_draw: one drawIndexed of the geometry pass."""
     _fields_ = [("vertices", C.c_void_p), ("indices", C.c_void_p), ("first_index", C.c_uint32), ("index_count", C.c_uint32),
-                ("vertex_offset", C.c_int32), ("model", C.c_float * 16), ("normal_model", C.c_float * 12), ("material", Material)]
+                ("vertex_offset", C.c_int32), ("vertex_count", C.c_uint32), ("model", C.c_float * 16), ("normal_model", C.c_float * 12), ("material", Material)]
 
 
 class LightTiles(C.Structure):

@@ -15,6 +15,9 @@ GOLDEN = Path(__file__).resolve().parent / "golden" / "raster_golden.npz"
 EMPTY = 0xFFFFFFFF
 
 
+CACHE = True  # state vertex_count (the post-transform vertex cache); test_uncached_path_is_identical flips it
+
+
 def upload_draws(pbr, dev, draws):
     """Device copies of the draws' buffers + the pbrcu_draw array; returns (array, keepalive)."""
     arr = (pbr.Draw * max(1, len(draws)))()
@@ -25,6 +28,7 @@ def upload_draws(pbr, dev, draws):
         a = arr[i]
         a.vertices, a.indices = bufs["vertices"].ptr, bufs["indices"].ptr
         a.first_index, a.index_count, a.vertex_offset = d["first_index"], d["index_count"], d["vertex_offset"]
+        a.vertex_count = len(d["vertices"]) - d["vertex_offset"] if CACHE else 0
         a.model[:] = np.asarray(d["model"], np.float32).tolist()
         a.normal_model[:] = np.asarray(d["normal_model"], np.float32).tolist()
         m = a.material
@@ -169,3 +173,38 @@ def test_geometry_pass_argument_errors(pbr, dev):
     arr[0].vertices, arr[0].indices, arr[0].index_count = v.ptr, i.ptr, 3
     with pytest.raises(pbr.PbrcuError):  # the reference's materials always carry both textures
         dev.lib.geometry_pass(dev.ctx, C.byref(gb), view.ctypes.data, proj.ctypes.data, arr, 1, None, None)
+
+
+def test_uncached_path_is_identical(pbr, dev, oracle, monkeypatch):
+    """vertex_count = 0 (the caller does not know how many vertices a draw addresses): the vertex stage runs per
+    triangle and per pixel instead of once per vertex -- same bits; also a mix of cached and uncached draws."""
+    import sys
+    me = sys.modules[__name__]
+    view, proj = camera((0.5, -1.5, -6.0), (0, 0, 0), aspect=16 / 9)  # close enough that the ground plane is clipped
+    draws = raster_scene(1)
+    want = oracle.geometry_pass(draws, view, proj, 200, 112, extended=True)
+    cached = device_pass(pbr, dev, draws, view, proj, 200, 112)
+    assert_same(cached, want, "cached")
+    monkeypatch.setattr(me, "CACHE", False)
+    assert_same(device_pass(pbr, dev, draws, view, proj, 200, 112), want, "uncached")
+    monkeypatch.setattr(me, "CACHE", True)
+    orig = me.upload_draws
+
+    def mixed(pbr_, dev_, ds):
+        arr, keep = orig(pbr_, dev_, ds)
+        for i in range(0, len(ds), 2):
+            arr[i].vertex_count = 0
+        return arr, keep
+
+    monkeypatch.setattr(me, "upload_draws", mixed)
+    assert_same(device_pass(pbr, dev, draws, view, proj, 200, 112), want, "mixed")
+
+
+def test_clip_cache_overflow_falls_back(pbr, dev, oracle, monkeypatch):
+    """More clipped triangles than parked-polygon slots (forced: capacity 1): the rest re-clip per pixel, same bits."""
+    view, proj = camera((0.5, -1.5, -6.0), (0, 0, 0), aspect=16 / 9)
+    draws = raster_scene(1)
+    want = oracle.geometry_pass(draws, view, proj, 200, 112, extended=True)
+    for cap in ("1", "0"):
+        monkeypatch.setenv("PBRCU_RASTER_CLIP_CAP", cap)
+        assert_same(device_pass(pbr, dev, draws, view, proj, 200, 112), want, f"clip cap {cap}")
