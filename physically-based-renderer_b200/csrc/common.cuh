@@ -39,7 +39,6 @@ struct pbrcu_ctx {
   bool exact_ibl_filter;  // K6/K7: software fp32-weight filtering instead of the texture unit
   void* raster_scratch;  // K10: visibility buffer, piece set-ups, chunk queue, draw table (grown on demand)
   size_t raster_bytes;
-  bool raster_table_ready;
   bool shade_tex;         // K3: texture-unit fetches of the prefiltered / irradiance cubes (pbrcu_shade_set_texture_unit)
 };
 
