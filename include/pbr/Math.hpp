@@ -169,5 +169,39 @@ inline mat4 perspectiveRH_NO(float fovy, float aspect, float zNear, float zFar) 
   r[3][2] = -(2.0f * zFar * zNear) / (zFar - zNear);
   return r;
 }
+// ---- what the viewer's CameraController and frame loop use (src/gltf_viewer/CameraController.hpp, App.cpp:301-308) ----
+constexpr vec2 operator-(vec2 a, vec2 b) { return {a.x - b.x, a.y - b.y}; }
+constexpr vec3& operator+=(vec3& a, vec3 b) { a = a + b; return a; }
+template <class T> constexpr T half_pi();
+template <> constexpr float half_pi<float>() { return 1.5707963267948966192313216916397514420985846996875529104874722961f; }
+// x (1 - a) + y a, component-wise
+constexpr vec3 mix(vec3 x, vec3 y, float a) { return x * (1.0f - a) + y * a; }
+constexpr quat operator*(quat p, quat q) {
+  return {p.w * q.w - p.x * q.x - p.y * q.y - p.z * q.z, p.w * q.x + p.x * q.w + p.y * q.z - p.z * q.y,
+          p.w * q.y + p.y * q.w + p.z * q.x - p.x * q.z, p.w * q.z + p.z * q.w + p.x * q.y - p.y * q.x};
+}
+// q * angleAxis(angle, normalised v): the axis is re-normalised only when its length is off by more than 0.001
+inline quat rotate(quat q, float angle, vec3 v) {
+  vec3 tmp = v;
+  const float len = length(tmp);
+  if (std::fabs(len - 1.0f) > 0.001f) tmp = tmp * (1.0f / len);
+  const float s = std::sin(angle * 0.5f);
+  return q * quat {std::cos(angle * 0.5f), tmp.x * s, tmp.y * s, tmp.z * s};
+}
+// m * (rotation by angle about normalize(v)), Rodrigues form
+inline mat4 rotate(mat4 const& m, float angle, vec3 v) {
+  const float c = std::cos(angle), s = std::sin(angle);
+  const vec3 axis = normalize(v), temp = axis * (1.0f - c);
+  mat4 rot;
+  rot[0][0] = c + temp.x * axis.x; rot[0][1] = temp.x * axis.y + s * axis.z; rot[0][2] = temp.x * axis.z - s * axis.y;
+  rot[1][0] = temp.y * axis.x - s * axis.z; rot[1][1] = c + temp.y * axis.y; rot[1][2] = temp.y * axis.z + s * axis.x;
+  rot[2][0] = temp.z * axis.x + s * axis.y; rot[2][1] = temp.z * axis.y - s * axis.x; rot[2][2] = c + temp.z * axis.z;
+  mat4 r;
+  r[0] = m[0] * rot[0][0] + m[1] * rot[0][1] + m[2] * rot[0][2];
+  r[1] = m[0] * rot[1][0] + m[1] * rot[1][1] + m[2] * rot[1][2];
+  r[2] = m[0] * rot[2][0] + m[1] * rot[2][1] + m[2] * rot[2][2];
+  r[3] = m[3];
+  return r;
+}
 }  // namespace glm
 #endif
