@@ -128,8 +128,10 @@ template <int MODE, bool TEX>
 static int launch_conv(const pbrcu_ctx* ctx, ConvParams p, cudaStream_t s) {
   const int rows = p.row_end - p.row_begin;
   if (rows <= 0) return PBRCU_OK;
-  // lanes per texel: enough threads to fill 148 SMs x 1024 threads, at most a warp
-  const size_t texels = size_t(rows) * p.res;
+  // lanes per texel: enough threads to fill 148 SMs x 1024 threads, at most a warp.  Chosen from the WHOLE level,
+  // not from this launch's rows: G fixes the order in which a texel's samples are summed, and a shard of the
+  // level must produce the same bits as the unsharded run
+  const size_t texels = size_t(6) * p.res * p.res;
   int G = 1;
   while (G < 32 && texels * G < size_t(ctx->sm_count) * 1024) G *= 2;
   const int per_block = kConvThreads / G;

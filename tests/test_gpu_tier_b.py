@@ -253,3 +253,25 @@ def test_shade_tiled_lights_equal_brute_force(pbr, dev, oracle):
     _, want = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, lights, host)
     assert_hdr_parity(tiled, want, peak=float(max(f16(want).max(), 1.0)), rel_tol=REL, what="tiled shade")
     dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
+
+
+@pytest.mark.parametrize("exact", [0, 1])
+def test_prefilter_shards_are_bit_identical_to_the_whole(dev, oracle, exact):
+    """Multi-GPU partition of K7 (row blocks of every level): at a size where the levels use DIFFERENT numbers of lanes
+    per texel, 2 and 8 shards must reproduce the unsharded chain bit for bit (the lane count is taken from the whole
+    level, so a texel's samples are summed in the same order whoever computes it)."""
+    res, nmips, ns = 256, 9, 256
+    _, chain_d, chain = make_env_chain(dev, oracle, res, nmips, seed=3)
+    dev.lib.ibl_set_exact_filtering(dev.ctx, exact)
+    whole = dev.alloc(chain.nbytes)
+    dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, whole.ptr, 0, nmips - 1, 0, 1, None)
+    dev.sync()
+    want = whole.download(chain.shape, np.uint16)
+    for nshards in (2, 8):
+        part = dev.alloc(chain.nbytes); part.zero()
+        for s in range(nshards):
+            dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, part.ptr, 0, nmips - 1, s, nshards, None)
+        dev.sync()
+        got = part.download(chain.shape, np.uint16)
+        assert np.array_equal(got, want), f"{nshards} shards: {np.count_nonzero(got != want)} values differ"
+    dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
