@@ -232,7 +232,7 @@ def extra_configs(scene, torch, dist, world, rank):
         K3 with 4 lights + IBL per view (no exchange: views are independent)."""
     pbr, dev, lib, ctx = scene.pbr, scene.dev, scene.dev.lib, scene.dev.ctx
     from oracle import synth_lights
-    from pbr_b200.partition import row_band, view_block
+    from pbr_b200.partition import band_views, row_band, view_block
     out = {}
     # ---- config[3]: 8K, 256 clustered lights, row bands ----
     W8, H8, NL = 7680, 4320, 256
@@ -249,49 +249,60 @@ def extra_configs(scene, torch, dist, world, rank):
     tiles = pbr.LightTiles()
     lib.light_tiles_alloc(ctx, W8, H8, NL, C.byref(tiles))
     y0, y1 = row_band(H8, world, rank, align=16)
-    band = pbr.Rect(0, y0, W8, y1 - y0)
+    band = band_views(pbr, g, tiles, y0, y1)  # this rank's rows of the G-buffer and of the tile lists (pointer arithmetic only)
 
     def step8k(_):
-        # clustering covers the whole frame on every rank (it is 2 % of the step); shading only the band
-        lib.cluster_lights(ctx, C.byref(g), lights.data_ptr(), NL, C.byref(tiles), scene.stream())
+        # each rank clusters and shades only its own band (per-band clustering == whole-frame clustering: tiles are 16-aligned)
         if y1 > y0:
-            lib.shade_ggx_ibl(ctx, C.byref(g), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(tiles), C.byref(scene.ibl), band, hdr.data_ptr(), W8 * 8, scene.stream())
+            lib.cluster_lights(ctx, C.byref(band.gbuffer), lights.data_ptr(), NL, C.byref(band.tiles), scene.stream())
+            lib.shade_ggx_ibl(ctx, C.byref(band.gbuffer), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(band.tiles), C.byref(scene.ibl), pbr.WHOLE,
+                              hdr.data_ptr() + y0 * W8 * 8, W8 * 8, scene.stream())
 
     ms = timed(torch, dist, step8k, 5, 3)
-    # tile counts live in library-owned memory: copy them out through the C ABI
-    host_counts = np.empty(tiles.tiles_x * tiles.tiles_y, np.uint32)
-    lib.memcpy_d2h(host_counts.ctypes.data, tiles.counts, host_counts.nbytes, scene.stream())
+    # tile counts live in library-owned memory: copy this rank's out through the C ABI
+    host_counts = np.empty(max(band.tiles.tiles_x * band.tiles.tiles_y, 1), np.uint32)
+    lib.memcpy_d2h(host_counts.ctypes.data, band.tiles.counts, band.tiles.tiles_x * band.tiles.tiles_y * 4, scene.stream())
     torch.cuda.synchronize()
     out["config3_8k_256_lights"] = {"mpix_s": round(W8 * H8 * 5 / (ms * 1e-3) / 1e6, 1), "ms_per_frame": round(ms / 5, 4),
                                     "rows_per_rank": y1 - y0, "mean_lights_per_tile": round(float(host_counts.mean()), 2),
                                     "max_lights_per_tile": int(host_counts.max()), "scaling": "strong (row bands, no exchange)",
-                                    "what": "pbrcu_cluster_lights (whole frame) + pbrcu_shade_ggx_ibl (band), 256 point lights range U[2,6], IBL"}
+                                    "what": "pbrcu_cluster_lights + pbrcu_shade_ggx_ibl on the rank's row band, 256 point lights range U[2,6], IBL"}
     lib.light_tiles_free(ctx, C.byref(tiles))
     # ---- config[4]: 256 views x 1080p, view blocks ----
     WV, HV, NV = 1920, 1080, 256
     v0, v1 = view_block(NV, world, rank)
-    views = []
-    for v in range(v0, v1):
+    nv = v1 - v0
+    # one allocation per plane with the rank's views back to back (view stride = one view): the batched entry shades
+    # them all in ONE launch
+    stride8, stride4 = WV * HV * 8, WV * HV * 4
+    planes = {k2: scene.buf(max(nv, 1) * (stride4 if k2 == "orm" else stride8)) for k2 in ("positions", "normals", "albedo", "orm", "emissive")}
+    outs = scene.buf(max(nv, 1) * stride8)
+    cams = np.zeros((max(nv, 1), 3), np.float32)
+    g0 = pbr.GBuffer()
+    g0.width, g0.height, g0.pitch8, g0.pitch4 = WV, HV, WV * 8, WV * 4
+    for k2, t in planes.items():
+        setattr(g0, k2, t.data_ptr())
+    for i, v in enumerate(range(v0, v1)):
         ring, k = divmod(v, NV // 2)
         ang = 2 * np.pi * k / (NV // 2)
-        cam = (12.0 * np.cos(ang), -1.0 - 4.0 * ring, 12.0 * np.sin(ang))
+        cams[i] = (12.0 * np.cos(ang), -1.0 - 4.0 * ring, 12.0 * np.sin(ang))
         gv = pbr.GBuffer()
         gv.width, gv.height, gv.pitch8, gv.pitch4 = WV, HV, WV * 8, WV * 4
-        pl = {k2: scene.buf(WV * HV * (4 if k2 == "orm" else 8)) for k2 in ("positions", "normals", "albedo", "orm", "emissive")}
-        for k2, t in pl.items():
-            setattr(gv, k2, t.data_ptr())
-        lib.synth_gbuffer(ctx, C.byref(gv), 1, SEED + 50, pbr.f3(*cam), pbr.f3(0, 0, 0), None)  # one scene, many cameras
-        views.append((gv, pl, cam, scene.buf(WV * HV * 8)))
+        for k2, t in planes.items():
+            setattr(gv, k2, t.data_ptr() + i * (stride4 if k2 == "orm" else stride8))
+        lib.synth_gbuffer(ctx, C.byref(gv), 1, SEED + 50, pbr.f3(*cams[i]), pbr.f3(0, 0, 0), None)  # one scene, many cameras
     torch.cuda.synchronize()
+    cam_ptr = cams.ctypes.data_as(C.POINTER(C.c_float))
 
     def step_views(_):
-        for gv, _pl, cam, o in views:
-            lib.shade_ggx_ibl(ctx, C.byref(gv), pbr.f3(*cam), scene.lights.data_ptr(), N_LIGHTS, None, C.byref(scene.ibl), pbr.WHOLE, o.data_ptr(), WV * 8, scene.stream())
+        if nv:
+            lib.shade_ggx_ibl_batched(ctx, C.byref(g0), stride8, stride4, nv, cam_ptr, scene.lights.data_ptr(), N_LIGHTS, C.byref(scene.ibl), outs.data_ptr(), WV * 8,
+                                      stride8, scene.stream())
 
     ms = timed(torch, dist, step_views, 3, 3)
     out["config4_256_views_1080p"] = {"mpix_s": round(NV * WV * HV * 3 / (ms * 1e-3) / 1e6, 1), "ms_per_pass": round(ms / 3, 3),
-                                      "views_per_rank": v1 - v0, "scaling": "strong (view blocks, no exchange)",
-                                      "what": "pbrcu_shade_ggx_ibl per view, 4 point lights + IBL, one launch per view"}
+                                      "views_per_rank": nv, "scaling": "strong (view blocks, no exchange)",
+                                      "what": "pbrcu_shade_ggx_ibl_batched: the rank's views in one launch, 4 point lights + IBL"}
     out["geometry_pass_1080p"] = geometry_bench(scene, torch, dist, world, rank)
     out["config2_prefilter_sharded"] = prefilter_sharded(scene, torch, dist, world, rank)
     return out

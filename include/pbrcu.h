@@ -174,6 +174,14 @@ int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host, const voi
 int pbrcu_ibl_accel_build(pbrcu_ctx* ctx, const pbrcu_ibl* ibl, pbrcu_ibl_accel** out, pbrcu_stream s);
 int pbrcu_ibl_accel_free(pbrcu_ctx* ctx, pbrcu_ibl_accel* accel);
 size_t pbrcu_ibl_accel_bytes(const pbrcu_ibl_accel* accel);
+/* K3 batched multi-view (BASELINE config 5): n_views extended G-buffers of identical shape laid out view_stride8 /
+ * view_stride4 bytes apart starting at g0's planes, one camera per view (host array, n_views*3), the same lights
+ * (at most 128, no tile lists) and IBL for all; view v's frame lands out_view_stride bytes after view v-1's.
+ * One launch: the persistent CTAs stride over the work items of all views. */
+int pbrcu_shade_ggx_ibl_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
+                                uint32_t n_views, const float* cam_pos_xyz, const pbrcu_light* lights_dev,
+                                uint32_t n_lights, const pbrcu_ibl* ibl, void* out_rgba16f, size_t out_pitch,
+                                size_t out_view_stride, pbrcu_stream s);
 /* K3c: per 16x16 tile, the lights whose range sphere meets the tile's world-space position AABB */
 int pbrcu_light_tiles_alloc(pbrcu_ctx* ctx, uint32_t width, uint32_t height, uint32_t max_per_tile,
                             pbrcu_light_tiles* out);

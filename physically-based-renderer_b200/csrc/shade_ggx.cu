@@ -10,6 +10,8 @@
 // NEXT tile are staged into shared memory with cp.async while the current tile is shaded, so the DRAM
 // latency of the streaming reads never sits on a warp's critical path; the tile's light list is staged
 // in shared memory; the IBL footprint records of a pixel are prefetched into L1 before its light loop.
+#include <algorithm>
+
 #include "f32x2.cuh"
 #include "ibl_quads.cuh"
 
@@ -44,6 +46,18 @@ struct ShadeParams {
   uint32_t lut_res;
   const uint4 *q_pref, *q_irr, *q_lut;  // footprint records (pbrcu_ibl_accel); NULL: plain textures
   cudaTextureObject_t t_pref, t_irr;    // flagged hardware textures of the same maps (IBL_TEX)
+  // batched multi-view (LIST_ONE_BATCHED): view v reads its planes view_stride8 / view_stride4 bytes after view
+  // v - 1's, its camera from cams[3 v ..], and writes out_view_stride bytes after view v - 1's output
+  uint32_t n_views;
+  size_t view_stride8, view_stride4, out_view_stride;
+  const float* cams;
+};
+
+// how a work item gets its light list
+enum : int {
+  LIST_TILED = 0,        // per-tile lists (K3c) or more than kLightChunk lights: staged per item, in chunks
+  LIST_ONE = 1,          // no tile lists and at most kLightChunk lights: one list, staged once per CTA
+  LIST_ONE_BATCHED = 2   // LIST_ONE over n_views G-buffers of one shape in a single launch
 };
 
 // how the ambient term samples the three IBL textures
@@ -119,7 +133,7 @@ struct TileStage {
 };
 
 // work item = half a tile: item >> 1 = tile of the rect (row-major), item & 1 = upper / lower 8 rows
-struct ItemPos { uint32_t tx, ty, x, y; };
+struct ItemPos { uint32_t tx, ty, x, y, view; };
 __device__ __forceinline__ ItemPos item_pos(const ShadeParams& p, uint32_t item) {
   const uint32_t tile = item >> 1;
   const uint32_t trow = p.ntx_magic ? __umulhi(tile, p.ntx_magic) : tile;
@@ -127,24 +141,26 @@ __device__ __forceinline__ ItemPos item_pos(const ShadeParams& p, uint32_t item)
   q.ty = p.ty0 + trow; q.tx = p.tx0 + (tile - trow * p.ntx);
   q.x = q.tx * kTile + (threadIdx.x % kTile);
   q.y = q.ty * kTile + (item & 1u) * kHalfRows + (threadIdx.x / kTile);
+  q.view = 0;
   return q;
 }
 
+template <bool BATCHED>
 __device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, const ItemPos& q) {
   const uint32_t x = q.x, y = q.y;
   if (x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1) {
-    const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8;
+    const size_t o8 = size_t(y) * p.pitch8 + size_t(x) * 8 + (BATCHED ? size_t(q.view) * p.view_stride8 : 0);
     cp_async8(&st.px[1][threadIdx.x], p.nrm + o8);
     cp_async8(&st.px[0][threadIdx.x], p.pos + o8);
     cp_async8(&st.px[2][threadIdx.x], p.alb + o8);
     cp_async8(&st.px[3][threadIdx.x], p.emi + o8);
-    cp_async4(&st.orm[threadIdx.x], p.orm + size_t(y) * p.pitch4 + size_t(x) * 4);
+    cp_async4(&st.orm[threadIdx.x], p.orm + size_t(y) * p.pitch4 + size_t(x) * 4 + (BATCHED ? size_t(q.view) * p.view_stride4 : 0));
   }
 }
 
-// ONE_LIST: no tile lists and at most kLightChunk lights -- every item uses the same list, staged once per CTA.
-template <int IBL, bool ONE_LIST>
+template <int IBL, int LISTS>
 __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
+  constexpr bool ONE_LIST = LISTS != LIST_TILED, BATCHED = LISTS == LIST_ONE_BATCHED;
   // staged lights, two per entry (lane 0 = light 2j, lane 1 = light 2j+1):
   // s_lp[j] = {{x0,x1,y0,y1}, {z0,z1,w0,w1}} with w = 1/range^2 (0 = unlimited); s_lc[j] = {{r0,r1,g0,g1}, {b0,b1,-,-}}
   // with rgb = colour * intensity.  An odd count is padded with a null light (colour 0: it adds exactly 0).
@@ -167,19 +183,31 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
   };
   if (ONE_LIST) stage_lights(nullptr, 0, p.n_lights);
 
-  const uint32_t nitems = 2 * p.ntiles;
-  uint32_t tile = blockIdx.x;  // work item (half tile)
+  const uint32_t nitems = 2 * p.ntiles;  // per view
+  uint32_t tile = blockIdx.x, view = 0;  // work item (half tile) of `view`
+  // BATCHED: the CTAs stride over the items of all views; (view, tile) is kept normalised without a division
+  auto carry = [&](uint32_t& t, uint32_t& v) {
+    if (BATCHED)
+      while (t >= nitems && v < p.n_views) { t -= nitems; ++v; }
+  };
+  auto live = [&](uint32_t t, uint32_t v) { return BATCHED ? v < p.n_views : t < nitems; };
+  carry(tile, view);
   int stage = 0;
   ItemPos next = item_pos(p, tile);
-  if (tile < nitems) stage_tile(p, s_tile[0], next);
+  next.view = view;
+  if (live(tile, view)) stage_tile<BATCHED>(p, s_tile[0], next);
   cp_async_commit();
   if (ONE_LIST) __syncthreads();
 
-  for (; tile < nitems; tile += gridDim.x, stage ^= 1) {
+  uint32_t ntile = tile, nview = view;
+  for (; live(tile, view); tile = ntile, view = nview, stage ^= 1) {
     const ItemPos ip = next;
-    if (tile + gridDim.x < nitems) {  // next item in flight
-      next = item_pos(p, tile + gridDim.x);
-      stage_tile(p, s_tile[stage ^ 1], next);
+    ntile = tile + gridDim.x; nview = view;
+    carry(ntile, nview);
+    if (live(ntile, nview)) {  // next item in flight
+      next = item_pos(p, ntile);
+      next.view = nview;
+      stage_tile<BATCHED>(p, s_tile[stage ^ 1], next);
     }
     cp_async_commit();
     cp_async_wait<1>();  // this tile's group has landed (each thread reads only its own slots)
@@ -205,7 +233,9 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
         P = make_float3(pxy.x, pxy.y, pzw.x);
         const float ninv = rsq(nxy.x * nxy.x + nxy.y * nxy.y + nzw.x * nzw.x);
         N = make_float3(nxy.x * ninv, nxy.y * ninv, nzw.x * ninv);
-        const float vx = p.cx - P.x, vy = p.cy - P.y, vz = p.cz - P.z;
+        float cx = p.cx, cy = p.cy, cz = p.cz;
+        if (BATCHED) { cx = __ldg(p.cams + 3 * ip.view); cy = __ldg(p.cams + 3 * ip.view + 1); cz = __ldg(p.cams + 3 * ip.view + 2); }
+        const float vx = cx - P.x, vy = cy - P.y, vz = cz - P.z;
         const float vinv = rsq(vx * vx + vy * vy + vz * vz);
         V = make_float3(vx * vinv, vy * vinv, vz * vinv);
         NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
@@ -315,7 +345,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     }
     const float dr = lo(dr2) + hi(dr2), dg = lo(dg2) + hi(dg2), db = lo(db2) + hi(db2);
     if (!inside) continue;
-    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8;
+    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
     if (!lit) {
       stg_stream8(outp, make_uint2(0u, 0u));
       continue;
@@ -365,28 +395,33 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
 
 // ---- K3c: per 16x16 tile, world-space AABB of the tile's non-cleared positions, then every light
 // whose range sphere meets it, in ascending light index (so K3 sums in the oracle's order).
+// One WARP per tile (eight tiles per CTA): the 256 pixels are read as eight fully coalesced 2-row slabs, the box is
+// reduced with shuffles and the lights are compacted 32 at a time with a ballot -- no block barriers at all.
 __global__ void __launch_bounds__(kClusterThreads) cluster_lights_kernel(
     const uint8_t* pos, const uint8_t* nrm, size_t pitch8, uint32_t width, uint32_t height,
-    const pbrcu_light* lights, uint32_t n_lights, uint32_t* counts, uint16_t* indices, uint32_t tiles_x,
+    const pbrcu_light* lights, uint32_t n_lights, uint32_t* counts, uint16_t* indices, uint32_t tiles_x, uint32_t n_tiles,
     uint32_t max_per_tile) {
-  __shared__ float s_min[3][kClusterThreads / 32], s_max[3][kClusterThreads / 32];
-  __shared__ float s_box[6];
-  __shared__ uint32_t s_warp_cnt[kClusterThreads / 32];
-  __shared__ uint32_t s_base;
-  const uint32_t tile = blockIdx.y * tiles_x + blockIdx.x;
-  const uint32_t x = blockIdx.x * kTile + threadIdx.x % kTile, y = blockIdx.y * kTile + threadIdx.x / kTile;
+  const uint32_t tile = (blockIdx.x * kClusterThreads + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (tile >= n_tiles) return;
+  const uint32_t ty = tile / tiles_x, tx = tile - ty * tiles_x;
+  const uint32_t x = tx * kTile + (lane & 15u);
   float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
-  if (x < width && y < height) {
-    const size_t o8 = size_t(y) * pitch8 + size_t(x) * 8;
-    const uint2 tn = __ldg(reinterpret_cast<const uint2*>(nrm + o8));
-    const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
-    if (!(nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f)) {
-      const uint2 tp = __ldg(reinterpret_cast<const uint2*>(pos + o8));
-      const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
-      mn[0] = mx[0] = pxy.x; mn[1] = mx[1] = pxy.y; mn[2] = mx[2] = pzw.x;
+#pragma unroll
+  for (int k = 0; k < kTile / 2; ++k) {
+    const uint32_t y = ty * kTile + 2 * k + (lane >> 4);
+    if (x < width && y < height) {
+      const size_t o8 = size_t(y) * pitch8 + size_t(x) * 8;
+      const uint2 tn = __ldg(reinterpret_cast<const uint2*>(nrm + o8));
+      const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
+      if (!(nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f)) {
+        const uint2 tp = __ldg(reinterpret_cast<const uint2*>(pos + o8));
+        const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
+        mn[0] = fminf(mn[0], pxy.x); mx[0] = fmaxf(mx[0], pxy.x);
+        mn[1] = fminf(mn[1], pxy.y); mx[1] = fmaxf(mx[1], pxy.y);
+        mn[2] = fminf(mn[2], pzw.x); mx[2] = fmaxf(mx[2], pzw.x);
+      }
     }
   }
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
 #pragma unroll
@@ -394,19 +429,11 @@ __global__ void __launch_bounds__(kClusterThreads) cluster_lights_kernel(
       mn[c] = fminf(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], off));
       mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], off));
     }
-    if (lane == 0) { s_min[c][warp] = mn[c]; s_max[c][warp] = mx[c]; }
   }
-  __syncthreads();
-  if (threadIdx.x < 3) {
-    float a = s_min[threadIdx.x][0], b = s_max[threadIdx.x][0];
-    for (int w = 1; w < kClusterThreads / 32; ++w) { a = fminf(a, s_min[threadIdx.x][w]); b = fmaxf(b, s_max[threadIdx.x][w]); }
-    s_box[threadIdx.x] = a; s_box[3 + threadIdx.x] = b;
-  }
-  if (threadIdx.x == 0) s_base = 0;
-  __syncthreads();
-  const bool empty = s_box[0] > s_box[3];
-  for (uint32_t base = 0; base < n_lights; base += kClusterThreads) {
-    const uint32_t i = base + threadIdx.x;
+  const bool empty = mn[0] > mx[0];
+  uint32_t total = 0;
+  for (uint32_t base = 0; base < n_lights; base += 32) {
+    const uint32_t i = base + lane;
     bool hit = false;
     if (i < n_lights && !empty) {
       const float4 la = __ldg(reinterpret_cast<const float4*>(lights) + 2 * i);
@@ -414,29 +441,18 @@ __global__ void __launch_bounds__(kClusterThreads) cluster_lights_kernel(
       else {
         // fp16 positions are exact in fp32; widen the sphere by 1 ulp-ish so K3's window (which is
         // exactly 0 at d >= range) can never see a light this test dropped
-        const float ddx = fmaxf(fmaxf(s_box[0] - la.x, la.x - s_box[3]), 0.0f);
-        const float ddy = fmaxf(fmaxf(s_box[1] - la.y, la.y - s_box[4]), 0.0f);
-        const float ddz = fmaxf(fmaxf(s_box[2] - la.z, la.z - s_box[5]), 0.0f);
+        const float ddx = fmaxf(fmaxf(mn[0] - la.x, la.x - mx[0]), 0.0f);
+        const float ddy = fmaxf(fmaxf(mn[1] - la.y, la.y - mx[1]), 0.0f);
+        const float ddz = fmaxf(fmaxf(mn[2] - la.z, la.z - mx[2]), 0.0f);
         hit = ddx * ddx + ddy * ddy + ddz * ddz <= la.w * la.w * 1.0001f;
       }
     }
-    // ordered compaction: ballot within the warp, prefix over the 8 warps
-    const uint32_t ballot = __ballot_sync(0xffffffffu, hit);
-    if (lane == 0) s_warp_cnt[warp] = __popc(ballot);
-    __syncthreads();
-    uint32_t before = s_base;
-    for (int w = 0; w < warp; ++w) before += s_warp_cnt[w];
-    const uint32_t slot = before + __popc(ballot & ((1u << lane) - 1u));
+    const uint32_t ballot = __ballot_sync(0xffffffffu, hit);  // ordered compaction
+    const uint32_t slot = total + __popc(ballot & ((1u << lane) - 1u));
     if (hit && slot < max_per_tile) indices[size_t(tile) * max_per_tile + slot] = uint16_t(i);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t tot = 0;
-      for (int w = 0; w < kClusterThreads / 32; ++w) tot += s_warp_cnt[w];
-      s_base += tot;
-    }
-    __syncthreads();
+    total += __popc(ballot);
   }
-  if (threadIdx.x == 0) counts[tile] = min(s_base, max_per_tile);
+  if (lane == 0) counts[tile] = min(total, max_per_tile);
 }
 
 }  // namespace pbrcu
@@ -472,10 +488,10 @@ extern "C" int pbrcu_cluster_lights(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, cons
   PBRCU_REQUIRE(g->positions && g->normals, "gbuffer plane is NULL");
   PBRCU_REQUIRE(n_lights <= 65535 && (n_lights == 0 || lights_dev), "n_lights out of range or lights NULL");
   PBRCU_REQUIRE(tiles->tiles_x == (g->width + kTile - 1) / kTile && tiles->tiles_y == (g->height + kTile - 1) / kTile, "tile grid does not match the gbuffer");
-  dim3 grid(tiles->tiles_x, tiles->tiles_y);
-  cluster_lights_kernel<<<grid, kClusterThreads, 0, static_cast<cudaStream_t>(s)>>>(
+  const uint32_t n_tiles = tiles->tiles_x * tiles->tiles_y;
+  cluster_lights_kernel<<<(n_tiles + kClusterThreads / 32 - 1) / (kClusterThreads / 32), kClusterThreads, 0, static_cast<cudaStream_t>(s)>>>(
       static_cast<const uint8_t*>(g->positions), static_cast<const uint8_t*>(g->normals), g->pitch8, g->width, g->height,
-      lights_dev, n_lights, tiles->counts, tiles->indices, tiles->tiles_x, tiles->max_per_tile);
+      lights_dev, n_lights, tiles->counts, tiles->indices, tiles->tiles_x, n_tiles, tiles->max_per_tile);
   return launch_check("cluster_lights_kernel");
 }
 
@@ -486,14 +502,16 @@ extern "C" int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on) {
 }
 
 template <int IBL>
-static void launch_shade(const ShadeParams& p, bool one_list, uint32_t grid, cudaStream_t st) {
-  if (one_list) shade_ggx_kernel<IBL, true><<<grid, kShadeThreads, 0, st>>>(p);
-  else shade_ggx_kernel<IBL, false><<<grid, kShadeThreads, 0, st>>>(p);
+static void launch_shade(const ShadeParams& p, int lists, uint32_t grid, cudaStream_t st) {
+  if (lists == LIST_ONE_BATCHED) shade_ggx_kernel<IBL, LIST_ONE_BATCHED><<<grid, kShadeThreads, 0, st>>>(p);
+  else if (lists == LIST_ONE) shade_ggx_kernel<IBL, LIST_ONE><<<grid, kShadeThreads, 0, st>>>(p);
+  else shade_ggx_kernel<IBL, LIST_TILED><<<grid, kShadeThreads, 0, st>>>(p);
 }
 
-extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
-                                   const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
-                                   const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch, pbrcu_stream s) {
+// argument checks and kernel parameters shared by the single-view and the batched entry; n_views > 1 = batched
+static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_dev, uint32_t n_lights,
+                        const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch,
+                        uint32_t n_views, size_t view_stride8, size_t view_stride4, size_t out_view_stride, pbrcu_stream s) {
   PBRCU_REQUIRE(ctx && g && cam_pos && out_rgba16f, "NULL argument");
   PBRCU_REQUIRE(g->positions && g->normals && g->albedo && g->orm && g->emissive, "gbuffer plane is NULL (K3 needs the tier-1 planes)");
   PBRCU_REQUIRE(g->pitch8 >= size_t(g->width) * 8 && g->pitch8 % 8 == 0 && g->pitch4 >= size_t(g->width) * 4 && g->pitch4 % 4 == 0, "bad gbuffer pitch");
@@ -510,6 +528,8 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
   p.x0 = rect.x0; p.y0 = rect.y0; p.x1 = rect.x0 + rect.w; p.y1 = rect.y0 + rect.h;
   p.tx0 = rect.x0 / kTile; p.ty0 = rect.y0 / kTile;
   p.cx = cam_pos[0]; p.cy = cam_pos[1]; p.cz = cam_pos[2];
+  p.n_views = n_views; p.view_stride8 = view_stride8; p.view_stride4 = view_stride4; p.out_view_stride = out_view_stride;
+  p.cams = ctx->cams_dev;
   p.lights = lights_dev; p.n_lights = n_lights;
   if (tiles) {
     PBRCU_REQUIRE(tiles->counts && tiles->indices, "light tiles not allocated");
@@ -538,11 +558,40 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
   p.ntx_magic = p.ntx == 1 ? 0u : uint32_t(((1ull << 32) + p.ntx - 1) / p.ntx);  // 0: one tile per row
   // persistent grid: kShadeCtasPerSm CTAs per SM walk the half-tile work items round-robin
   const bool tex = p.q_pref && ctx->shade_tex;
-  const uint32_t grid = min(2 * p.ntiles, uint32_t(ctx->sm_count) * kShadeCtasPerSm);
+  const uint32_t grid = uint32_t(std::min<uint64_t>(uint64_t(2) * p.ntiles * n_views, uint64_t(ctx->sm_count) * kShadeCtasPerSm));
   cudaStream_t st = static_cast<cudaStream_t>(s);
   const bool one_list = p.tile_counts == nullptr && p.n_lights <= uint32_t(kLightChunk);
-  if (tex) launch_shade<IBL_TEX>(p, one_list, grid, st);
-  else if (p.q_pref) launch_shade<IBL_RECORDS>(p, one_list, grid, st);
-  else launch_shade<IBL_PLAIN>(p, one_list, grid, st);
+  PBRCU_REQUIRE(n_views == 1 || one_list, "batched shading takes no tile lists and at most 128 lights");
+  const int lists = n_views > 1 ? LIST_ONE_BATCHED : one_list ? LIST_ONE : LIST_TILED;
+  if (tex) launch_shade<IBL_TEX>(p, lists, grid, st);
+  else if (p.q_pref) launch_shade<IBL_RECORDS>(p, lists, grid, st);
+  else launch_shade<IBL_PLAIN>(p, lists, grid, st);
   return launch_check("shade_ggx_kernel");
+}
+
+extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                                   const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
+                                   const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch, pbrcu_stream s) {
+  return shade_common(ctx, g, cam_pos, lights_dev, n_lights, tiles, ibl, rect, out_rgba16f, out_pitch, 1, 0, 0, 0, s);
+}
+
+extern "C" int pbrcu_shade_ggx_ibl_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
+                                           uint32_t n_views, const float* cam_pos_xyz, const pbrcu_light* lights_dev, uint32_t n_lights,
+                                           const pbrcu_ibl* ibl, void* out_rgba16f, size_t out_pitch, size_t out_view_stride, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && g0 && cam_pos_xyz && out_rgba16f, "NULL argument");
+  PBRCU_REQUIRE(n_views >= 1 && n_views <= 65535, "n_views must be in [1, 65535]");
+  PBRCU_REQUIRE(view_stride8 >= g0->pitch8 * g0->height && view_stride4 >= g0->pitch4 * g0->height && out_view_stride >= out_pitch * g0->height,
+                "view stride smaller than one view");
+  PBRCU_REQUIRE(view_stride8 % 8 == 0 && view_stride4 % 4 == 0 && out_view_stride % 8 == 0, "view strides must keep texels aligned");
+  if (n_views == 1)
+    return shade_common(ctx, g0, cam_pos_xyz, lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, 0, 0, 0}, out_rgba16f, out_pitch, 1, 0, 0, 0, s);
+  if (ctx->cams_cap < n_views) {
+    if (ctx->cams_dev) PBRCU_CUDA(cudaFree(ctx->cams_dev));
+    ctx->cams_dev = nullptr; ctx->cams_cap = 0;
+    PBRCU_CUDA(cudaMalloc(&ctx->cams_dev, size_t(n_views) * 3 * sizeof(float)));
+    ctx->cams_cap = n_views;
+  }
+  PBRCU_CUDA(cudaMemcpyAsync(ctx->cams_dev, cam_pos_xyz, size_t(n_views) * 3 * sizeof(float), cudaMemcpyHostToDevice, static_cast<cudaStream_t>(s)));
+  return shade_common(ctx, g0, cam_pos_xyz, lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, 0, 0, 0}, out_rgba16f, out_pitch, n_views, view_stride8,
+                      view_stride4, out_view_stride, s);
 }

@@ -87,3 +87,30 @@ def gather_chain(chain, base_res: int, nmips: int, world: int, rank: int, dist=N
                 if n:
                     dist.broadcast(chain[o:o + n], src=r)
     return chain
+
+
+class BandViews:
+    """Sub-views of a G-buffer and of its light-tile lists restricted to rows [y0, y1) (y0 a multiple of 16):
+    plain pointer arithmetic on the C structs, so a rank can cluster and shade ONLY its band with the ordinary
+    entry points (pbrcu_cluster_lights / pbrcu_shade_ggx_ibl) and still write the whole-frame buffers in place."""
+
+    def __init__(self, gbuffer, tiles, out_offset_rows):
+        self.gbuffer, self.tiles, self.out_offset_rows = gbuffer, tiles, out_offset_rows
+
+
+def band_views(pbr, g, tiles, y0: int, y1: int, tile: int = 16) -> BandViews:
+    if y0 % tile != 0:
+        raise ValueError("a band must start on a light-tile boundary")
+    gv = pbr.GBuffer()
+    gv.width, gv.height, gv.pitch8, gv.pitch4 = g.width, max(y1 - y0, 0), g.pitch8, g.pitch4
+    for name, pitch in (("positions", g.pitch8), ("normals", g.pitch8), ("albedo", g.pitch8), ("emissive", g.pitch8), ("orm", g.pitch4), ("depth", g.pitch4)):
+        p = getattr(g, name)
+        setattr(gv, name, (p + y0 * pitch) if p else None)
+    tv = None
+    if tiles is not None:
+        tv = pbr.LightTiles()
+        ty0 = y0 // tile
+        tv.tiles_x, tv.tiles_y, tv.max_per_tile = tiles.tiles_x, (max(y1 - y0, 0) + tile - 1) // tile, tiles.max_per_tile
+        tv.counts = tiles.counts + ty0 * tiles.tiles_x * 4
+        tv.indices = tiles.indices + ty0 * tiles.tiles_x * tiles.max_per_tile * 2
+    return BandViews(gv, tv, y0)

@@ -275,3 +275,74 @@ def test_prefilter_shards_are_bit_identical_to_the_whole(dev, oracle, exact):
         got = part.download(chain.shape, np.uint16)
         assert np.array_equal(got, want), f"{nshards} shards: {np.count_nonzero(got != want)} values differ"
     dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+
+
+def test_shade_batched_views_equal_single_launches(pbr, dev, oracle):
+    """pbrcu_shade_ggx_ibl_batched (config 5: many views of one shape in ONE launch) writes exactly the frames the
+    per-view calls write -- also when the grid has more CTAs than one view has work items, and for a single view."""
+    host, bufs = build_ibl(dev, oracle)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    lights = synth_lights(5, seed=9)  # odd count: the padded null light
+    ld = dev.upload(lights)
+    for (w, h, nv) in ((64, 32, 7), (333, 61, 3), (48, 16, 1)):
+        gs = [synth_gbuffer(w, h, seed=300 + v, tier_b=True) for v in range(nv)]
+        stack = lambda k, dt: np.ascontiguousarray(np.stack([g[k] for g in gs])).view(dt)
+        planes = dict(positions=dev.upload(stack("pos", np.uint16)), normals=dev.upload(stack("nrm", np.uint16)), albedo=dev.upload(stack("alb", np.uint16)),
+                      orm=dev.upload(stack("orm", np.uint8)), emissive=dev.upload(stack("emi", np.uint16)))
+        gb = pbr.GBuffer()
+        gb.width, gb.height, gb.pitch8, gb.pitch4 = w, h, w * 8, w * 4
+        for k, b in planes.items():
+            setattr(gb, k, b.ptr)
+        cams = np.array([[12 * np.cos(v), -1.0 - v, 12 * np.sin(v)] for v in range(nv)], np.float32)
+        out = dev.alloc(nv * w * h * 8); out.zero()
+        dev.lib.shade_ggx_ibl_batched(dev.ctx, C.byref(gb), w * h * 8, w * h * 4, nv, cams.ctypes.data_as(C.POINTER(C.c_float)), ld.ptr, 5, C.byref(ibl), out.ptr, w * 8,
+                                      w * h * 8, None)
+        dev.sync()
+        got = out.download((nv, h, w, 4), np.uint16)
+        one = dev.alloc(w * h * 8)
+        for v in range(nv):
+            gv = pbr.GBuffer()
+            gv.width, gv.height, gv.pitch8, gv.pitch4 = w, h, w * 8, w * 4
+            for k, b in planes.items():
+                setattr(gv, k, b.ptr + v * w * h * (4 if k == "orm" else 8))
+            dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gv), pbr.f3(*cams[v]), ld.ptr, 5, None, C.byref(ibl), pbr.WHOLE, one.ptr, w * 8, None)
+            dev.sync()
+            assert np.array_equal(got[v], one.download((h, w, 4), np.uint16)), f"{w}x{h} view {v} of {nv}"
+        _, want = oracle.shade(gs[-1]["pos"], gs[-1]["nrm"], gs[-1]["alb"], gs[-1]["orm"], gs[-1]["emi"], cams[-1], lights, host)
+        assert_hdr_parity(got[-1], want, peak=float(max(f16(want).max(), 1.0)), rel_tol=REL, what="batched shade, last view")
+    with pytest.raises(pbr.PbrcuError):  # a view stride smaller than one view
+        dev.lib.shade_ggx_ibl_batched(dev.ctx, C.byref(gb), 8, 4, 2, cams.ctypes.data_as(C.POINTER(C.c_float)), ld.ptr, 5, C.byref(ibl), out.ptr, w * 8, w * h * 8, None)
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+
+
+def test_cluster_lights_on_a_row_band_equals_the_whole_frame(pbr, dev, oracle):
+    """Multi-GPU config 4: a rank clusters ONLY its 16-aligned row band, through sub-views of the G-buffer and of the
+    tile lists (no extra entry point) -- same counts and indices as the whole-frame clustering has for those tiles."""
+    w, h, nl = 200, 120, 256
+    g = synth_gbuffer(w, h, seed=78, tier_b=True)
+    yy, xx = np.mgrid[0:h, 0:w]
+    g["pos"][..., 0] = (xx / w * 16 - 8); g["pos"][..., 1] = (yy / h * 16 - 8); g["pos"][..., 2] = np.cos(xx * 0.07) * 2
+    g["pos"][g["bg"]] = 0
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    ld = dev.upload(synth_lights(nl, seed=5, ranged=True))
+    whole, part = pbr.LightTiles(), pbr.LightTiles()
+    dev.lib.light_tiles_alloc(dev.ctx, w, h, 64, C.byref(whole))
+    dev.lib.light_tiles_alloc(dev.ctx, w, h, 64, C.byref(part))
+    dev.lib.cluster_lights(dev.ctx, C.byref(gb), ld.ptr, nl, C.byref(whole), None)
+
+    def fetch(t):
+        c = pbr.DeviceBuffer.__new__(pbr.DeviceBuffer); c.dev, c.nbytes, c.ptr = dev, t.tiles_x * t.tiles_y * 4, t.counts
+        i = pbr.DeviceBuffer.__new__(pbr.DeviceBuffer); i.dev, i.nbytes, i.ptr = dev, t.tiles_x * t.tiles_y * t.max_per_tile * 2, t.indices
+        return c.download((t.tiles_y, t.tiles_x), np.uint32), i.download((t.tiles_y, t.tiles_x, t.max_per_tile), np.uint16)
+
+    for rank in range(3):
+        y0, y1 = pbr.partition.row_band(h, 3, rank, align=16)
+        band = pbr.partition.band_views(pbr, gb, part, y0, y1)
+        dev.lib.cluster_lights(dev.ctx, C.byref(band.gbuffer), ld.ptr, nl, C.byref(band.tiles), None)
+    dev.sync()
+    (cw, iw), (cp, ip) = fetch(whole), fetch(part)
+    assert np.array_equal(cw, cp) and cw.max() > 0
+    for ty in range(whole.tiles_y):
+        for tx in range(whole.tiles_x):
+            assert np.array_equal(iw[ty, tx, :cw[ty, tx]], ip[ty, tx, :cw[ty, tx]])
+    dev.lib.light_tiles_free(dev.ctx, C.byref(whole)); dev.lib.light_tiles_free(dev.ctx, C.byref(part))
