@@ -42,7 +42,7 @@ B_PER_PX_K1 = 32   # 24 read + 8 written
 # dram__bytes_read.sum + dram__bytes_write.sum of one shade_ggx_kernel launch on this workload, from the committed
 # `ncu --set full` capture (profiles/r01_k3_shade_ggx_ncu_details.txt): 519.3 MB + 60.7 MB; the 215 MB above the
 # algorithmic 365 MB are the IBL footprint records and write-allocate traffic
-K3_DRAM_TRAFFIC_BYTES = 579.9e6
+K3_DRAM_TRAFFIC_BYTES = 585.7e6
 ENV_W, ENV_H = 4096, 2048
 CUBE_RES, CUBE_MIPS, IBL_SAMPLES, IRR_RES, LUT_RES = 2048, 12, 1024, 64, 512
 CAM = (0.0, -1.0, -12.0)
