@@ -72,6 +72,8 @@ extern "C" void pbrcu_ctx_destroy(pbrcu_ctx* ctx) {
     if (ctx->pipe_done[i]) cudaEventDestroy(ctx->pipe_done[i]);
   }
   if (ctx->pipe_start) cudaEventDestroy(ctx->pipe_start);
+  for (auto& e : ctx->band_ready)
+    if (e) cudaEventDestroy(e);
   pbrcu::cube_tex_destroy(&ctx->cube);
   if (ctx->raster_scratch) cudaFree(ctx->raster_scratch);
   if (ctx->cube_stage) cudaFree(ctx->cube_stage);
@@ -289,6 +291,7 @@ static int ensure_pipe(pbrcu_ctx* ctx) {
     PBRCU_CUDA(cudaEventCreateWithFlags(&ctx->pipe_done[i], cudaEventDisableTiming));
   }
   PBRCU_CUDA(cudaEventCreateWithFlags(&ctx->pipe_start, cudaEventDisableTiming));
+  for (auto& e : ctx->band_ready) PBRCU_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   return PBRCU_OK;
 }
 
@@ -301,6 +304,7 @@ extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host
   PBRCU_REQUIRE(width > 0 && height > 0, "empty extent");
   PBRCU_REQUIRE(n_lights == 0 || lights_host, "lights_host is NULL");
   if (n_bands == 0) n_bands = 8;
+  if (n_bands > 64) n_bands = 64;
   if (n_bands > height) n_bands = height;
   cudaStream_t st = static_cast<cudaStream_t>(s);
   const size_t p8 = size_t(width) * 8, p4 = size_t(width) * 4;
@@ -323,20 +327,25 @@ extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host
   g.orm = ctx->stage[3]; g.emissive = ctx->stage[4];
   g.width = width; g.height = height; g.pitch8 = p8; g.pitch4 = p4;
   const void* src[5] = {positions_host, normals_host, albedo_host, orm_host, emissive_host};
+  // pipe[0] carries every host-to-device copy, band after band; pipe[1] shades a band as soon as its planes are in and
+  // sends the result back.  Copies-in thus run back to back at the full PCIe rate (issued on two streams they would
+  // share it and every band would arrive late), copies-out overlap them on the other direction of the link.
+  cudaStream_t in = ctx->pipe[0], work = ctx->pipe[1];
   for (uint32_t b = 0; b < n_bands; ++b) {
-    cudaStream_t ps = ctx->pipe[b & 1];
     const uint32_t y0 = uint32_t(uint64_t(height) * b / n_bands), y1 = uint32_t(uint64_t(height) * (b + 1) / n_bands);
     if (y1 == y0) continue;
     for (int i = 0; i < 5; ++i) {
       const size_t pitch = (i == 3) ? p4 : p8;
       PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(ctx->stage[i]) + y0 * pitch, static_cast<const uint8_t*>(src[i]) + y0 * pitch,
-                                 size_t(y1 - y0) * pitch, cudaMemcpyHostToDevice, ps));
+                                 size_t(y1 - y0) * pitch, cudaMemcpyHostToDevice, in));
     }
+    PBRCU_CUDA(cudaEventRecord(ctx->band_ready[b], in));
+    PBRCU_CUDA(cudaStreamWaitEvent(work, ctx->band_ready[b], 0));
     if ((rc = pbrcu_shade_ggx_ibl(ctx, &g, cam_pos, ctx->lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, y0, width, y1 - y0},
-                                  ctx->stage[5], p8, ps)))
+                                  ctx->stage[5], p8, work)))
       return rc;
     PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(hdr_out_host) + y0 * p8, static_cast<uint8_t*>(ctx->stage[5]) + y0 * p8,
-                               size_t(y1 - y0) * p8, cudaMemcpyDeviceToHost, ps));
+                               size_t(y1 - y0) * p8, cudaMemcpyDeviceToHost, work));
   }
   for (int i = 0; i < 2; ++i) {
     PBRCU_CUDA(cudaEventRecord(ctx->pipe_done[i], ctx->pipe[i]));

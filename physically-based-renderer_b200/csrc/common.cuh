@@ -26,6 +26,7 @@ struct pbrcu_ctx {
   cudaStream_t pipe[2];
   cudaEvent_t pipe_done[2];
   cudaEvent_t pipe_start;
+  cudaEvent_t band_ready[64];  // band b's planes have arrived (recorded on the copy-in stream)
   pbrcu_light* lights_dev;
   uint32_t lights_cap;
   // per-view camera positions for the batched multi-view launch (grown on demand)
