@@ -1,17 +1,19 @@
-// pbr/image/Decode.hpp -- PNG -> tightly packed R8G8B8A8 on the host.
+// pbr/image/Decode.hpp -- PNG and JPEG -> tightly packed R8G8B8A8 on the host.
 // The reference decodes textures with the vendored stb_image (src/pbr_engine/image/pbr/image/LoadImage.cpp:58-73:
-// stbi_load / stbi_load_from_memory with req_comp = 4); this is an own decoder of the PNG subset of that call,
-// written from the PNG (ISO/IEC 15948) and DEFLATE (RFC 1951) specifications, with stb's conversion rules to
-// 8-bit RGBA where the specification leaves a choice:
+// stbi_load / stbi_load_from_memory with req_comp = 4); decode() is an own implementation of that call for the two
+// containers glTF allows (PNG here, JPEG in DecodeJpeg.hpp).  The PNG decoder is written from the PNG (ISO/IEC 15948)
+// and DEFLATE (RFC 1951) specifications, with stb's conversion rules to 8-bit RGBA where the specification leaves a choice:
 //   * 16-bit samples keep their HIGH byte (stb_image.h: stbi__convert_16_to_8);
 //   * 1/2/4-bit grey samples are scaled by 0xFF / 0x55 / 0x11; palette indices are not scaled;
 //   * grey / RGB images gain alpha 255; a tRNS colour key gives alpha 0 to the matching pixels (compared at the
 //     file's bit depth); a palette's tRNS entries are per-index alpha;
 //   * gamma / colour-profile chunks are ignored, checksums (CRC-32, Adler-32) are not verified, rows are top-down.
-// Adam7-interlaced files are supported.  Other containers stb accepts (JPEG, BMP, TGA, ...) are NOT decoded:
-// decode() throws, where the reference would go on with a null pixel pointer.
+// Adam7-interlaced files are supported.  The other containers stb accepts (BMP, TGA, GIF, PSD, HDR, PIC, PNM) are NOT
+// decoded: decode() throws, where the reference would go on with a null pixel pointer.
 // CPU-only header: tests/cpp/gltf_dump.cpp pins it against the reference's own stb_image build (oracle/_ref).
 #pragma once
+#include "pbr/image/DecodeJpeg.hpp"
+
 #include <array>
 #include <cstddef>
 #include <cstdint>
@@ -266,10 +268,14 @@ struct PngHeader {
   return bytes.size() >= 8 && std::memcmp(bytes.data(), sig, 8) == 0;
 }
 
-// The counterpart of stbi_load_from_memory(buffer, size, &w, &h, &channels, 4) for PNG input.
+// The counterpart of stbi_load_from_memory(buffer, size, &w, &h, &channels, 4) for PNG and JPEG input.
 [[nodiscard]] inline auto decode(std::span<std::uint8_t const> bytes) -> DecodedImage {
   using namespace detail;
-  if (!isPng(bytes)) fail("not a PNG file (the only container this build decodes)");
+  if (jpeg::isJpeg(bytes)) {
+    auto px = jpeg::decode(bytes);
+    return {px.width, px.height, std::move(px.rgba)};
+  }
+  if (!isPng(bytes)) fail("neither a PNG nor a JPEG file (the containers this build decodes)");
   PngHeader hdr {};
   bool haveHeader = false, havePalette = false;
   std::uint8_t palette[256][4];

@@ -6,7 +6,7 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent.parent
 sys.path.insert(0, str(ROOT / "tests"))
-from test_image_decode_cpu import CASES, stb_decode  # noqa: E402
+from test_image_decode_cpu import CASES, jpeg_cases, stb_decode  # noqa: E402
 
 out = ROOT / "tests" / "golden" / "png"
 out.mkdir(parents=True, exist_ok=True)
@@ -16,4 +16,12 @@ for name, png in keep:
     assert pix is not None, name
     (out / f"{name}.png").write_bytes(png)
     (out / f"{name}.rgba").write_bytes(pix.tobytes())
+n_png = len(keep)
+jk = [c for c in jpeg_cases() if "_40x23_" in c[0] or c[0] in ("cv_411_b_rst7", "cv_440_p_rst1") or c[0] in ("pil_rgb_keep", "pil_cmyk")]
+for name, jpg in jk:
+    pix = stb_decode(jpg)
+    assert pix is not None, name
+    (out / f"{name}.jpg").write_bytes(jpg)
+    (out / f"{name}.rgba").write_bytes(pix.tobytes())
+keep = keep + jk
 print(len(keep), "golden files,", sum(f.stat().st_size for f in out.iterdir()), "bytes")

@@ -84,6 +84,65 @@ def cases():
 CASES = cases()
 
 
+def jpeg_cases():
+    """(name, jpeg bytes) written by Pillow and OpenCV: baseline and progressive, grey / 4:4:4 / 4:2:2 / 4:2:0 / 4:1:1 /
+    4:4:0 sampling, odd sizes (partial MCUs, 1-pixel images), restart intervals, optimised Huffman tables, 16-bit-free
+    quality sweep, Adobe RGB / CMYK / YCCK files."""
+    import io
+
+    import cv2
+    from PIL import Image
+    rng = np.random.default_rng(21)
+    out = []
+
+    def content(w, h, kind):
+        y, x = np.mgrid[0:h, 0:w]
+        if kind == "smooth":
+            img = np.stack([(x * 3 + y) % 256, (x + 2 * y) % 256, (x * y // 7) % 256], axis=-1)
+        elif kind == "noise":
+            img = rng.integers(0, 256, (h, w, 3))
+        else:  # edges: hard colour steps stress chroma upsampling and clamping
+            img = np.stack([((x // 5 + y // 3) % 2) * 255, ((x // 2) % 2) * 255, ((y // 4) % 2) * 200 + 30], axis=-1)
+        return img.astype(np.uint8)
+
+    def pil(img, **kw):
+        buf = io.BytesIO()
+        Image.fromarray(img).save(buf, "JPEG", **kw)
+        return buf.getvalue()
+
+    sizes = ((1, 1), (7, 5), (16, 16), (17, 33), (40, 23), (65, 49))
+    for (w, h) in sizes:
+        for kind in ("smooth", "noise", "edges"):
+            img = content(w, h, kind)
+            for sub, name in ((0, "444"), (1, "422"), (2, "420")):
+                for prog in (False, True):
+                    q = int(rng.choice([30, 75, 95, 100]))
+                    out.append((f"pil_{kind}_{w}x{h}_{name}_{'p' if prog else 'b'}_q{q}", pil(img, quality=q, subsampling=sub, progressive=prog, optimize=bool(rng.integers(0, 2)))))
+            out.append((f"pil_{kind}_{w}x{h}_grey", pil(img[..., 0], quality=85)))
+            out.append((f"pil_{kind}_{w}x{h}_grey_p", pil(img[..., 0], quality=60, progressive=True)))
+    big = content(200, 150, "smooth") // 2 + content(200, 150, "noise") // 2
+    for prog in (0, 1):
+        for rst in (0, 1, 7):
+            for samp, name in ((cv2.IMWRITE_JPEG_SAMPLING_FACTOR_411, "411"), (cv2.IMWRITE_JPEG_SAMPLING_FACTOR_440, "440"), (cv2.IMWRITE_JPEG_SAMPLING_FACTOR_420, "420")):
+                ok, enc = cv2.imencode(".jpg", big, [cv2.IMWRITE_JPEG_QUALITY, 80, cv2.IMWRITE_JPEG_PROGRESSIVE, prog, cv2.IMWRITE_JPEG_RST_INTERVAL, rst,
+                                                     cv2.IMWRITE_JPEG_SAMPLING_FACTOR, samp, cv2.IMWRITE_JPEG_OPTIMIZE, 1])
+                assert ok
+                out.append((f"cv_{name}_{'p' if prog else 'b'}_rst{rst}", enc.tobytes()))
+    # Adobe-flavoured files: RGB stored without colour transform, CMYK, YCCK
+    rgb = content(33, 21, "edges")
+    out.append(("pil_rgb_keep", pil(rgb, quality=90, keep_rgb=True)))
+    cmyk = Image.fromarray(rng.integers(0, 256, (19, 27, 4)).astype(np.uint8), "CMYK")
+    buf = io.BytesIO(); cmyk.save(buf, "JPEG", quality=90); out.append(("pil_cmyk", buf.getvalue()))
+    return out
+
+
+def jpeg_cases_or_skip():
+    try:
+        return jpeg_cases()
+    except ImportError as e:  # Pillow / OpenCV missing on this machine
+        pytest.skip(f"no JPEG encoder: {e}")
+
+
 @pytest.mark.skipif(not STB.exists(), reason="oracle/_ref/libpbr_ref_stb.so not built (needs /root/reference)")
 def test_matches_reference_stb_on_the_feature_matrix(tool, tmp_path):
     assert len(CASES) > 100
@@ -95,9 +154,23 @@ def test_matches_reference_stb_on_the_feature_matrix(tool, tmp_path):
         assert got.shape == want.shape and np.array_equal(got, want), name
 
 
+@pytest.mark.skipif(not STB.exists(), reason="oracle/_ref/libpbr_ref_stb.so not built (needs /root/reference)")
+def test_jpeg_matches_reference_stb(tool, tmp_path):
+    cases_ = jpeg_cases_or_skip()
+    assert len(cases_) > 150
+    for name, jpg in cases_:
+        want = stb_decode(jpg)
+        got, err = ours(tool, jpg, tmp_path)
+        assert want is not None, name
+        assert got is not None, f"{name}: {err}"
+        assert got.shape == want.shape, name
+        assert np.array_equal(got, want), f"{name}: {np.count_nonzero(got != want)} of {got.size} bytes differ (max {np.abs(got.astype(int) - want).max()})"
+
+
 def test_matches_committed_golden_files(tool, tmp_path):
-    files = sorted(GOLD.glob("*.png"))
+    files = sorted(GOLD.glob("*.png")) + sorted(GOLD.glob("*.jpg"))
     assert len(files) >= 10, "tests/golden/png is missing: run tests/golden/make_png_golden.py"
+    assert any(f.suffix == ".jpg" for f in files)
     for f in files:
         want = np.frombuffer(f.with_suffix(".rgba").read_bytes(), np.uint8)
         got, err = ours(tool, f.read_bytes(), tmp_path)
