@@ -39,10 +39,11 @@ class Builder:
         self.doc["accessors"].append(acc)
         return len(self.doc["accessors"]) - 1
 
-    def image(self, rgba: np.ndarray, name: str, how="view", **png_kw) -> int:
-        png = encode_rgba8(rgba, **png_kw)
+    def image(self, rgba, name: str, how="view", encoded: bytes = None, mime="image/png", **png_kw) -> int:
+        """rgba: pixels to store as PNG -- or pass `encoded` (+ mime), an already encoded PNG / JPEG file."""
+        png = encoded if encoded is not None else encode_rgba8(rgba, **png_kw)
         if how == "view":
-            entry = {"name": name, "bufferView": self._view(png), "mimeType": "image/png"}
+            entry = {"name": name, "bufferView": self._view(png), "mimeType": mime}
         elif how == "data":
             entry = {"name": name, "uri": "data:image/png;base64," + base64.b64encode(png).decode()}
         else:  # external file

@@ -38,7 +38,19 @@ def asset(tmp_path):
     quad_i = np.array([0, 1, 2, 0, 2, 3, 0, 2, 1, 0, 3, 2], np.uint16)
     tex = dict(c0=checker_texture(16, 8, 21), n0=checker_texture(8, 8, 22, normal_map=True), c1=checker_texture(32, 32, 23),
                n1=np.array([[[128, 128, 255, 255]]], np.uint8), c2=checker_texture(8, 4, 24), n2=checker_texture(4, 4, 25, normal_map=True))
-    t = {k: b.image(v, k, how="view", filters=(4, 2), level=6, interlace=(k == "c1")) for k, v in tex.items()}
+    # c2 travels as a progressive 4:2:0 JPEG: what the material sees is whatever the import path's decoder makes of it
+    # (that decoder is pinned bit-exact to the reference's stb_image in tests/test_image_decode_cpu.py)
+    import io
+    from PIL import Image
+    buf = io.BytesIO()
+    Image.fromarray(np.kron(tex["c2"][..., :3], np.ones((4, 4, 1), np.uint8))).save(buf, "JPEG", quality=80, progressive=True, subsampling=2)
+    (tmp_path / "c2.jpg").write_bytes(buf.getvalue())
+    dec = subprocess.run([str(ROOT / "tests" / "cpp" / "build" / "image_decode"), str(tmp_path / "c2.jpg"), str(tmp_path / "c2.rgba")], capture_output=True, text=True)
+    assert dec.returncode == 0, dec.stderr
+    jw, jh = map(int, dec.stdout.split())
+    tex["c2"] = np.fromfile(tmp_path / "c2.rgba", np.uint8).reshape(jh, jw, 4)
+    t = {k: (b.image(None, k, encoded=buf.getvalue(), mime="image/jpeg") if k == "c2" else b.image(v, k, how="view", filters=(4, 2), level=6, interlace=(k == "c1")))
+         for k, v in tex.items()}
     m0 = b.material("m0", (0.9, 0.6, 0.3, 1.0), t["c0"], t["n0"])
     m1 = b.material("m1", (0.5, 0.7, 0.9, 1.0), t["c1"], t["n1"])
     m2 = b.material("m2", (0.2, 0.9, 0.4, 0.5), t["c2"], t["n2"])
