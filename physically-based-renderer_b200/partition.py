@@ -114,3 +114,26 @@ def band_views(pbr, g, tiles, y0: int, y1: int, tile: int = 16) -> BandViews:
         tv.counts = tiles.counts + ty0 * tiles.tiles_x * 4
         tv.indices = tiles.indices + ty0 * tiles.tiles_x * tiles.max_per_tile * 2
     return BandViews(gv, tv, y0)
+
+
+def cost_balanced_bands(tile_row_costs, height: int, world: int, tile: int = 16) -> list[tuple[int, int]]:
+    """Row bands [y0, y1) for every rank, cut on light-tile boundaries so that each band carries about the same COST
+    instead of the same number of rows.  `tile_row_costs[r]` is the estimated shading cost of tile row r -- e.g. from the
+    previous frame's light lists, sum over the row's tiles of (fixed + lights in the tile).  Every rank computes the same
+    cuts from the same numbers, so no exchange is needed.  Bands are contiguous, cover [0, height) and may be empty."""
+    costs = [max(float(c), 0.0) for c in tile_row_costs]
+    n = len(costs)
+    if n != (height + tile - 1) // tile:
+        raise ValueError("one cost per tile row expected")
+    total = sum(costs)
+    if total <= 0.0:
+        return [row_band(height, world, r, align=tile) for r in range(world)]
+    cuts, acc, r = [0], 0.0, 0
+    for k in range(1, world):
+        target = total * k / world
+        while r < n and acc + costs[r] * 0.5 <= target:  # a row goes to the side of the cut most of it lies on
+            acc += costs[r]
+            r += 1
+        cuts.append(r)
+    cuts.append(n)
+    return [(min(cuts[k] * tile, height), min(cuts[k + 1] * tile, height)) for k in range(world)]

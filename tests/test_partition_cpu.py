@@ -34,6 +34,24 @@ def test_partitions_cover_exactly(pbr):
             assert per_rank[-1][m][0] + per_rank[-1][m][1] == off
 
 
+def test_cost_balanced_bands(pbr):
+    P = pbr.partition
+    rng = np.random.default_rng(1)
+    for height, world in ((4320, 8), (4320, 2), (1080, 4), (100, 3), (16, 8)):
+        n = (height + 15) // 16
+        costs = rng.uniform(1, 10, n) * (1 + 5 * np.exp(-((np.arange(n) - n / 2) / (n / 6 + 1)) ** 2))  # heavy middle
+        bands = P.cost_balanced_bands(costs, height, world)
+        assert len(bands) == world and bands[0][0] == 0 and bands[-1][1] == height
+        assert all(bands[i][1] == bands[i + 1][0] for i in range(world - 1)) and all(b % 16 == 0 for b, _ in bands)
+        if n >= 8 * world:
+            per = [costs[b // 16:(e + 15) // 16].sum() for b, e in bands]
+            equal = [costs[b // 16:(e + 15) // 16].sum() for b, e in (P.row_band(height, world, r, align=16) for r in range(world))]
+            assert max(per) <= max(equal) + 1e-9 and max(per) < 1.25 * sum(per) / world
+    assert P.cost_balanced_bands([0, 0, 0], 48, 2) == [P.row_band(48, 2, 0, align=16), P.row_band(48, 2, 1, align=16)]
+    with pytest.raises(ValueError):
+        P.cost_balanced_bands([1.0], 48, 2)
+
+
 def _worker(rank, world, port, height, q):
     import torch
     import torch.distributed as dist
