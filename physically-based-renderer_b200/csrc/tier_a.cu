@@ -68,7 +68,9 @@ __device__ __forceinline__ void process_single(const uint8_t* in0, const uint8_t
 
 // VEC = 2: every row start and pitch is 16-byte aligned -> 128-bit accesses of texel pairs.
 // VEC = 1: arbitrary alignment (odd x0, odd pitch): 64-bit accesses, one texel per item.
-template <int MODE, int VEC>
+// FLAT (VEC = 2 only): the image is one contiguous run of texel pairs (w = width * height, h = 1) below 2^31 texels:
+// 32-bit item arithmetic, one multiply-add per address.
+template <int MODE, int VEC, bool FLAT>
 __global__ void __launch_bounds__(kThreads) tier_a_kernel(const __grid_constant__ TierAParams p) {
   float cx = p.cx, cy = p.cy, cz = p.cz;
   const uint8_t *pos = p.pos, *nrm = p.nrm, *alb = p.alb, *hdr_in = p.hdr_in;
@@ -82,6 +84,31 @@ __global__ void __launch_bounds__(kThreads) tier_a_kernel(const __grid_constant_
     pos += o8; nrm += o8; alb += o8;
     if (hdr) hdr += size_t(v) * p.hdr_view_stride;
     if (ldr) ldr += size_t(v) * p.ldr_view_stride;
+  }
+  if (FLAT) {
+    const uint32_t npairs = p.w / 2, step = gridDim.x * kThreads * kUnroll;
+    for (uint32_t base = blockIdx.x * kThreads * kUnroll + threadIdx.x; base < npairs; base += step) {
+      uint4 a[kUnroll], b[kUnroll], c[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {  // issue every load of the iteration before any math
+        const uint32_t item = base + u * kThreads;
+        if (item < npairs) {
+          if (MODE == MODE_TONEMAP) {
+            a[u] = ldg_stream(hdr_in + size_t(item) * 16);
+          } else {
+            a[u] = ldg_stream(pos + size_t(item) * 16);
+            b[u] = ldg_stream(nrm + size_t(item) * 16);
+            c[u] = ldg_stream(alb + size_t(item) * 16);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const uint32_t item = base + u * kThreads;
+        if (item < npairs) process_pair<MODE>(hdr + size_t(item) * 16, ldr + size_t(item) * 8, a[u], b[u], c[u], cx, cy, cz);
+      }
+    }
+    return;
   }
   const uint32_t items_per_row = (VEC == 2) ? (p.w + 1) / 2 : p.w;
   const uint64_t total = uint64_t(items_per_row) * p.h;
@@ -125,6 +152,20 @@ __global__ void __launch_bounds__(kThreads) tier_a_kernel(const __grid_constant_
   }
 }
 
+// CTAs of tier_a_kernel<MODE, VEC> one SM holds (asked once per instantiation)
+template <int MODE>
+static int resident_ctas(bool vec) {
+  static int cached[2] = {0, 0};
+  int& n = cached[vec ? 1 : 0];
+  if (n == 0) {
+    int occ = 0;
+    const cudaError_t e = vec ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tier_a_kernel<MODE, 2, true>, kThreads, 0)
+                              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tier_a_kernel<MODE, 1, false>, kThreads, 0);
+    n = (e == cudaSuccess && occ > 0) ? occ : 4;
+  }
+  return n;
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 template <int MODE>
@@ -144,22 +185,26 @@ static int launch_tier_a(const pbrcu_ctx* ctx, TierAParams p, uint32_t n_views, 
   if (MODE == MODE_TONEMAP) contiguous = contiguous && p.hdr_pitch == size_t(p.w) * 8;
   else contiguous = contiguous && p.pitch8 == size_t(p.w) * 8 && (MODE == MODE_FUSED_LDR || p.hdr_pitch == size_t(p.w) * 8);
   if (MODE != MODE_LIGHT) contiguous = contiguous && p.ldr_pitch == size_t(p.w) * 4;
+  bool flat = false;
   if (contiguous && uint64_t(p.w) * p.h < (1ull << 31)) {
     p.w = p.w * p.h;
     p.h = 1;
+    flat = vec;
   }
   const uint32_t vecw = vec ? 2 : 1;
   const uint64_t items = uint64_t((p.w + vecw - 1) / vecw) * p.h;
   const uint64_t per_block = uint64_t(kThreads) * kUnroll;
   uint64_t blocks = (items + per_block - 1) / per_block;
-  // persistent grid: 8 CTAs of 256 threads per SM = full occupancy, whole multiples of the SM count
-  const uint64_t cap = uint64_t(ctx->sm_count) * 8;
+  // persistent grid: exactly the CTAs that are resident at once (32 to 63 registers per thread depending on the
+  // mode: 4 to 8 CTAs of 256 threads per SM), so the grid is one full wave with no partial second one
+  const uint64_t cap = uint64_t(ctx->sm_count) * resident_ctas<MODE>(vec);
   uint64_t per_view_cap = n_views > 1 ? (cap + n_views - 1) / n_views : cap;
   if (per_view_cap < 1) per_view_cap = 1;
   if (blocks > per_view_cap) blocks = per_view_cap;
   dim3 grid(uint32_t(blocks), n_views, 1);
-  if (vec) tier_a_kernel<MODE, 2><<<grid, kThreads, 0, s>>>(p);
-  else tier_a_kernel<MODE, 1><<<grid, kThreads, 0, s>>>(p);
+  if (flat) tier_a_kernel<MODE, 2, true><<<grid, kThreads, 0, s>>>(p);
+  else if (vec) tier_a_kernel<MODE, 2, false><<<grid, kThreads, 0, s>>>(p);
+  else tier_a_kernel<MODE, 1, false><<<grid, kThreads, 0, s>>>(p);
   return launch_check("tier_a_kernel");
 }
 

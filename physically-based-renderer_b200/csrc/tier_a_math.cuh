@@ -9,6 +9,31 @@ namespace pbrcu {
 
 struct F4 { float x, y, z, w; };
 
+// Single MUFU ops with flush-to-zero: the libdevice forms (rsqrtf, __fdividef, __log2f, exp2f) wrap each MUFU in a
+// compare and two predicated rescales for subnormal arguments / results, a fifth of the fused pass's instructions.
+// What flushing changes: a subnormal squared distance (camera within 1e-19 of a texel's position without coinciding
+// with it) normalises like a zero vector, and colours below 2^-126 map to exactly 0 -- both allowed to the reference's
+// own shaders (SPIR-V without DenormPreserve) and far below the LDR quantum.
+__device__ __forceinline__ float mufu_rsq(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float mufu_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float mufu_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float mufu_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+// R16G16B16A16_UNORM decode without the conversion unit (I2F shares the MUFU pipe, the fused pass's busiest):
+// the 16 bits become the low mantissa of 2^23, so (2^23 + u) - 2^23 = u exactly.
+__device__ __forceinline__ float u16_lo_f(uint32_t packed) { return __uint_as_float(__byte_perm(packed, 0x4B000000u, 0x7610)) - 8388608.0f; }
+__device__ __forceinline__ float u16_hi_f(uint32_t packed) { return __uint_as_float(__byte_perm(packed, 0x4B000000u, 0x7632)) - 8388608.0f; }
+
+// UNORM8 encode of four channels, again without F2I: clamp (NaN -> 0), scale, and add 1.5 * 2^23 -- the sum's
+// unit in the last place is 1, so the add IS the round-to-nearest-even and the byte sits in the low mantissa bits
+// (same two roundings as lrintf(c * 255.0f)).
+__device__ __forceinline__ uint32_t unorm8_bits(float v) { return __float_as_uint(__fadd_rn(__fmul_rn(__saturatef(v), 255.0f), 12582912.0f)); }
+__device__ __forceinline__ uint32_t pack_unorm8x4(float r, float g, float b, float a) {
+  const uint32_t rg = __byte_perm(unorm8_bits(r), unorm8_bits(g), 0x0040);
+  const uint32_t ba = __byte_perm(unorm8_bits(b), unorm8_bits(a), 0x0040);
+  return __byte_perm(rg, ba, 0x5410);
+}
+
 // lighting.glsl:19-29.  pos/nrm: RGBA16F texel (two packed half2 words); alb: RGBA16_UNORM texel.
 // With L = V (:26), H = normalize(V+V); the shader's operation order is kept so NaN propagation for
 // normalize(0) (cleared texel seen from a camera at the origin) ends in max(NaN,0) = 0 like the
@@ -18,20 +43,21 @@ __device__ __forceinline__ F4 blinnphong_texel(uint2 pos, uint2 nrm, uint2 alb, 
   float2 pxy = h2_to_f2(pos.x), pzw = h2_to_f2(pos.y);
   float2 nxy = h2_to_f2(nrm.x), nzw = h2_to_f2(nrm.y);
   float dx = cx - pxy.x, dy = cy - pxy.y, dz = cz - pzw.x;
-  float inv = rsqrtf(dx * dx + dy * dy + dz * dz);                 // :25 normalize(cam - P)
+  float inv = mufu_rsq(dx * dx + dy * dy + dz * dz);                // :25 normalize(cam - P)
   float vx = dx * inv, vy = dy * inv, vz = dz * inv;
   float ndv = fmaxf(nxy.x * vx + nxy.y * vy + nzw.x * vz, 0.0f);   // BlinnPhong.lib.glsl:5
   float hx = vx + vx, hy = vy + vy, hz = vz + vz;                  // :6 H = normalize(V + L)
-  float hinv = rsqrtf(hx * hx + hy * hy + hz * hz);
+  float hinv = mufu_rsq(hx * hx + hy * hy + hz * hz);
   hx *= hinv; hy *= hinv; hz *= hinv;
   float ndh = fmaxf(nxy.x * hx + nxy.y * hy + nzw.x * hz, 0.0f);   // :7
   float s = ndh * ndh;                                             // :8 pow(NdotH, 64) = 6 squarings
   s *= s; s *= s; s *= s; s *= s; s *= s;
   F4 o;                                                            // :9 all four channels
-  o.x = unorm16_lo(alb.x) * ndv + s;
-  o.y = unorm16_hi(alb.x) * ndv + s;
-  o.z = unorm16_lo(alb.y) * ndv + s;
-  o.w = unorm16_hi(alb.y) * ndv + s;
+  const float k = 1.0f / 65535.0f;
+  o.x = (u16_lo_f(alb.x) * k) * ndv + s;
+  o.y = (u16_hi_f(alb.x) * k) * ndv + s;
+  o.z = (u16_lo_f(alb.y) * k) * ndv + s;
+  o.w = (u16_hi_f(alb.y) * k) * ndv + s;
   return o;
 }
 
@@ -47,12 +73,12 @@ __device__ __forceinline__ F4 unpack_rgba16f(uint2 t) {
 __device__ __forceinline__ float rrt_odt_fit(float c) {
   float num = c * (c + 0.0245786f) - 0.000090537f;
   float den = c * (0.983729f * c + 0.4329510f) + 0.238081f;
-  return __fdividef(num, den);
+  return num * mufu_rcp(den);  // den >= 0.238 for c >= 0 and at most ~4e9 for fp16 inputs: no range fix-up needed
 }
 // Gamma.lib.glsl:4-6 with the pinned negative-base behaviour: pow(max(x,0), 1/2.2).
 // x = 0 -> lg2 = -inf -> ex2(-inf) = 0.
 __device__ __forceinline__ float gamma22(float x) {
-  return exp2f(__log2f(fmaxf(x, 0.0f)) * (1.0f / 2.2f));
+  return mufu_ex2(mufu_lg2(fmaxf(x, 0.0f)) * (1.0f / 2.2f));
 }
 // aces+gamma.glsl:30-40.  mat3x3(a,b,c,d,e,f,g,h,i) fills COLUMNS: (M v).x = a v.x + d v.y + g v.z.
 __device__ __forceinline__ uint32_t tonemap_texel(F4 hdr) {
@@ -63,9 +89,7 @@ __device__ __forceinline__ uint32_t tonemap_texel(F4 hdr) {
   float ox = 1.60475f * fx + -0.10208f * fy + -0.00327f * fz;
   float oy = -0.53108f * fx + 1.10813f * fy + -0.07276f * fz;
   float oz = -0.07367f * fx + -0.00605f * fy + 1.07602f * fz;
-  uint32_t r = to_unorm8(gamma22(ox)), g = to_unorm8(gamma22(oy)), b = to_unorm8(gamma22(oz));
-  uint32_t a = to_unorm8(hdr.w);
-  return r | (g << 8) | (b << 16) | (a << 24);
+  return pack_unorm8x4(gamma22(ox), gamma22(oy), gamma22(oz), hdr.w);
 }
 
 }  // namespace pbrcu
