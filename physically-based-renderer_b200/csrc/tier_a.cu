@@ -30,23 +30,16 @@ constexpr int kUnroll = 2;  // independent texel PAIRS per thread per iteration
 template <int MODE>
 __device__ __forceinline__ void process_pair(uint8_t* hdr, uint8_t* ldr, uint4 a, uint4 b, uint4 c,
                                              float cx, float cy, float cz) {
-  F4 c0, c1;
+  F4x2 cc;
   if (MODE == MODE_TONEMAP) {
-    c0 = unpack_rgba16f(make_uint2(a.x, a.y));
-    c1 = unpack_rgba16f(make_uint2(a.z, a.w));
+    cc = unpack_rgba16f_pair(a);
   } else {
-    c0 = blinnphong_texel(make_uint2(a.x, a.y), make_uint2(b.x, b.y), make_uint2(c.x, c.y), cx, cy, cz);
-    c1 = blinnphong_texel(make_uint2(a.z, a.w), make_uint2(b.z, b.w), make_uint2(c.z, c.w), cx, cy, cz);
+    cc = blinnphong_pair(a, b, c, cx, cy, cz);
+    const uint4 h = pack_rgba16f_pair(cc);
+    if (MODE != MODE_FUSED_LDR) stg_stream(hdr, h);
+    if (MODE != MODE_LIGHT) cc = unpack_rgba16f_pair(h);  // the tonemapper reads the fp16-rounded attachment value
   }
-  if (MODE == MODE_LIGHT || MODE == MODE_FUSED_HDR_LDR || MODE == MODE_FUSED_LDR) {
-    uint2 h0 = pack_rgba16f(c0), h1 = pack_rgba16f(c1);
-    if (MODE != MODE_FUSED_LDR) stg_stream(hdr, make_uint4(h0.x, h0.y, h1.x, h1.y));
-    if (MODE != MODE_LIGHT) {  // the tonemapper reads the fp16-rounded attachment value
-      c0 = unpack_rgba16f(h0);
-      c1 = unpack_rgba16f(h1);
-    }
-  }
-  if (MODE != MODE_LIGHT) stg_stream8(ldr, make_uint2(tonemap_texel(c0), tonemap_texel(c1)));
+  if (MODE != MODE_LIGHT) stg_stream8(ldr, tonemap_pair(cc));
 }
 
 template <int MODE>

@@ -4,6 +4,7 @@
 // All arithmetic fp32; one RNE rounding at each store (fp16 / unorm8).
 #pragma once
 #include "common.cuh"
+#include "f32x2.cuh"
 
 namespace pbrcu {
 
@@ -90,6 +91,75 @@ __device__ __forceinline__ uint32_t tonemap_texel(F4 hdr) {
   float oy = -0.53108f * fx + 1.10813f * fy + -0.07276f * fz;
   float oz = -0.07367f * fx + -0.00605f * fy + 1.07602f * fz;
   return pack_unorm8x4(gamma22(ox), gamma22(oy), gamma22(oz), hdr.w);
+}
+
+// ---- the same two passes for a PAIR of neighbouring texels, texel 0 in the low and texel 1 in the high lane of
+// packed f32x2 instructions (f32x2.cuh): each lane is rounded like the scalar instruction, and the pair costs
+// little more than half the issue slots of two scalar texels -- the fused pass is bound by issue slots and the
+// MUFU pipe, not by HBM, until this is done.  Operation order as in blinnphong_texel / tonemap_texel.
+struct F4x2 { f2 x, y, z, w; };
+
+__device__ __forceinline__ F4x2 blinnphong_pair(uint4 pos, uint4 nrm, uint4 alb, float cx, float cy, float cz) {
+  const float2 p0xy = h2_to_f2(pos.x), p0zw = h2_to_f2(pos.y), p1xy = h2_to_f2(pos.z), p1zw = h2_to_f2(pos.w);
+  const float2 n0xy = h2_to_f2(nrm.x), n0zw = h2_to_f2(nrm.y), n1xy = h2_to_f2(nrm.z), n1zw = h2_to_f2(nrm.w);
+  const f2 nx = pk(n0xy.x, n1xy.x), ny = pk(n0xy.y, n1xy.y), nz = pk(n0zw.x, n1zw.x);
+  const f2 dx = sub2(dup(cx), pk(p0xy.x, p1xy.x)), dy = sub2(dup(cy), pk(p0xy.y, p1xy.y)), dz = sub2(dup(cz), pk(p0zw.x, p1zw.x));
+  const f2 inv = map2(fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))), mufu_rsq);          // :25 normalize(cam - P)
+  const f2 vx = mul2(dx, inv), vy = mul2(dy, inv), vz = mul2(dz, inv);
+  const f2 ndv = max2(fma2(nz, vz, fma2(ny, vy, mul2(nx, vx))), 0.0f);              // BlinnPhong.lib.glsl:5
+  f2 hx = add2(vx, vx), hy = add2(vy, vy), hz = add2(vz, vz);                        // :6 H = normalize(V + L)
+  const f2 hinv = map2(fma2(hz, hz, fma2(hy, hy, mul2(hx, hx))), mufu_rsq);
+  hx = mul2(hx, hinv); hy = mul2(hy, hinv); hz = mul2(hz, hinv);
+  const f2 ndh = max2(fma2(nz, hz, fma2(ny, hy, mul2(nx, hx))), 0.0f);              // :7
+  f2 s = mul2(ndh, ndh);                                                             // :8 pow(NdotH, 64) = 6 squarings
+  s = mul2(s, s); s = mul2(s, s); s = mul2(s, s); s = mul2(s, s); s = mul2(s, s);
+  const f2 k = dup(1.0f / 65535.0f), m = dup(8388608.0f);
+  auto u16 = [&](uint32_t w0, uint32_t w1, uint32_t sel) {
+    return mul2(sub2(pk(__uint_as_float(__byte_perm(w0, 0x4B000000u, sel)), __uint_as_float(__byte_perm(w1, 0x4B000000u, sel))), m), k);
+  };
+  F4x2 o;                                                                            // :9 all four channels
+  o.x = fma2(u16(alb.x, alb.z, 0x7610), ndv, s);
+  o.y = fma2(u16(alb.x, alb.z, 0x7632), ndv, s);
+  o.z = fma2(u16(alb.y, alb.w, 0x7610), ndv, s);
+  o.w = fma2(u16(alb.y, alb.w, 0x7632), ndv, s);
+  return o;
+}
+
+// two RGBA16F texels {texel 0 words, texel 1 words}
+__device__ __forceinline__ uint4 pack_rgba16f_pair(const F4x2& c) {
+  return make_uint4(f2_to_h2(lo(c.x), lo(c.y)), f2_to_h2(lo(c.z), lo(c.w)), f2_to_h2(hi(c.x), hi(c.y)), f2_to_h2(hi(c.z), hi(c.w)));
+}
+__device__ __forceinline__ F4x2 unpack_rgba16f_pair(uint4 t) {
+  const float2 a0 = h2_to_f2(t.x), b0 = h2_to_f2(t.y), a1 = h2_to_f2(t.z), b1 = h2_to_f2(t.w);
+  return F4x2{pk(a0.x, a1.x), pk(a0.y, a1.y), pk(b0.x, b1.x), pk(b0.y, b1.y)};
+}
+
+__device__ __forceinline__ f2 rrt_odt_fit2(f2 c) {
+  const f2 num = fma2(c, add2(c, dup(0.0245786f)), dup(-0.000090537f));
+  const f2 den = fma2(c, fma2(dup(0.983729f), c, dup(0.4329510f)), dup(0.238081f));
+  return mul2(num, map2(den, mufu_rcp));
+}
+__device__ __forceinline__ f2 gamma22_2(f2 x) {
+  return map2(mul2(map2(max2(x, 0.0f), mufu_lg2), dup(1.0f / 2.2f)), mufu_ex2);
+}
+__device__ __forceinline__ f2 unorm8_bits2(f2 v) { return add2(mul2(sat2(v), dup(255.0f)), dup(12582912.0f)); }
+
+// two RGBA8 texels
+__device__ __forceinline__ uint2 tonemap_pair(const F4x2& hdr) {
+  const f2 ax = fma2(dup(0.02840f), hdr.z, fma2(dup(0.07600f), hdr.y, mul2(dup(0.59719f), hdr.x)));
+  const f2 ay = fma2(dup(0.13383f), hdr.z, fma2(dup(0.90834f), hdr.y, mul2(dup(0.35458f), hdr.x)));
+  const f2 az = fma2(dup(0.83777f), hdr.z, fma2(dup(0.01566f), hdr.y, mul2(dup(0.04823f), hdr.x)));
+  const f2 fx = rrt_odt_fit2(ax), fy = rrt_odt_fit2(ay), fz = rrt_odt_fit2(az);
+  const f2 ox = fma2(dup(-0.00327f), fz, fma2(dup(-0.10208f), fy, mul2(dup(1.60475f), fx)));
+  const f2 oy = fma2(dup(-0.07276f), fz, fma2(dup(1.10813f), fy, mul2(dup(-0.53108f), fx)));
+  const f2 oz = fma2(dup(1.07602f), fz, fma2(dup(-0.00605f), fy, mul2(dup(-0.07367f), fx)));
+  const f2 r = unorm8_bits2(gamma22_2(ox)), g = unorm8_bits2(gamma22_2(oy)), b = unorm8_bits2(gamma22_2(oz)), a = unorm8_bits2(hdr.w);
+  auto pack = [](float r_, float g_, float b_, float a_) {
+    const uint32_t rg = __byte_perm(__float_as_uint(r_), __float_as_uint(g_), 0x0040);
+    const uint32_t ba = __byte_perm(__float_as_uint(b_), __float_as_uint(a_), 0x0040);
+    return __byte_perm(rg, ba, 0x5410);
+  };
+  return make_uint2(pack(lo(r), lo(g), lo(b), lo(a)), pack(hi(r), hi(g), hi(b), hi(a)));
 }
 
 }  // namespace pbrcu
