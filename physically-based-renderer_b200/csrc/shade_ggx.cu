@@ -393,6 +393,209 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
   cp_async_wait<0>();
 }
 
+// ---- K3, single-list form (LIST_ONE / LIST_ONE_BATCHED with footprint records or no IBL) ----
+// Same arithmetic as shade_ggx_kernel, laid out for the two things ncu showed to bound it (profiles/r01_k3_*):
+//  * dependent-issue latency: the packed light chain is ONE dependency chain per thread, and 5 warps per scheduler do
+//    not cover it.  Here two light pairs (four lights) are evaluated side by side, so the scheduler always has a
+//    second independent chain of the same warp to issue from;
+//  * L1 tag bandwidth: every record is fetched with ONE 256-bit load (one tag look-up per lane instead of two).
+// Registers for both come from deferring everything only the ambient term needs (tap weights, c_diff, occlusion,
+// emissive, alpha) to shared memory: a small per-thread stash, and the staged tile itself, which stays valid for the
+// whole iteration.  Unlit and outside pixels leave the iteration early instead of carrying neutral values through it.
+struct PairA { f2 dx, dy, dz, invd, NoL, w; };
+
+__device__ __forceinline__ Quad6 ldg_rec256(const uint4* p) {
+  Quad6 q;
+  uint32_t pad0, pad1;
+  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(q.w[0]), "=r"(q.w[1]), "=r"(q.w[2]), "=r"(q.w[3]), "=r"(q.w[4]), "=r"(q.w[5]), "=r"(pad0), "=r"(pad1)
+               : "l"(p));
+  return q;
+}
+
+template <bool BATCHED>
+__global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_kernel(const __grid_constant__ ShadeParams p) {
+  __shared__ float4 s_lp[kLightChunk];
+  __shared__ float4 s_lc[kLightChunk];
+  __shared__ TileStage s_tile[2];
+  __shared__ float4 s_amb[3][kShadeThreads];  // {irr_tx, irr_ty, p0_tx, p0_ty}, {p1_tx, p1_ty, lut_tx, lut_ty}, {lod_f, cdr, cdg, cdb}
+  {
+    // lights, two per entry as in shade_ggx_kernel, padded with null lights (colour 0: they add exactly 0) to a
+    // multiple of FOUR so the loop below always takes two pairs
+    const uint32_t cnt = p.n_lights;
+    if (threadIdx.x < ((cnt + 3) & ~3u)) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+      if (threadIdx.x < cnt) {
+        a = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * threadIdx.x);
+        b = __ldg(reinterpret_cast<const float4*>(p.lights) + 2 * threadIdx.x + 1);
+      }
+      float* lp = reinterpret_cast<float*>(s_lp + (threadIdx.x & ~1u)) + (threadIdx.x & 1u);
+      float* lc = reinterpret_cast<float*>(s_lc + (threadIdx.x & ~1u)) + (threadIdx.x & 1u);
+      lp[0] = a.x; lp[2] = a.y; lp[4] = a.z; lp[6] = a.w > 0.0f ? __fdividef(1.0f, a.w * a.w) : 0.0f;
+      lc[0] = b.x * b.w; lc[2] = b.y * b.w; lc[4] = b.z * b.w;
+    }
+  }
+  const uint32_t nitems = 2 * p.ntiles;  // per view
+  uint32_t tile = blockIdx.x, view = 0;
+  auto carry = [&](uint32_t& t, uint32_t& v) {
+    if (BATCHED)
+      while (t >= nitems && v < p.n_views) { t -= nitems; ++v; }
+  };
+  auto live = [&](uint32_t t, uint32_t v) { return BATCHED ? v < p.n_views : t < nitems; };
+  carry(tile, view);
+  int stage = 0;
+  ItemPos next = item_pos(p, tile);
+  next.view = view;
+  if (live(tile, view)) stage_tile<BATCHED>(p, s_tile[0], next);
+  cp_async_commit();
+  __syncthreads();
+  const uint32_t quads = (p.n_lights + 3) >> 2;
+  const f2 one = dup(1.0f);
+
+  uint32_t ntile = tile, nview = view;
+  for (; live(tile, view); tile = ntile, view = nview, stage ^= 1) {
+    const ItemPos ip = next;
+    ntile = tile + gridDim.x; nview = view;
+    carry(ntile, nview);
+    if (live(ntile, nview)) {  // next item in flight
+      next = item_pos(p, ntile);
+      next.view = nview;
+      stage_tile<BATCHED>(p, s_tile[stage ^ 1], next);
+    }
+    cp_async_commit();
+    cp_async_wait<1>();  // this item's group has landed (each thread reads only its own slots)
+
+    const uint32_t x = ip.x, y = ip.y;
+    if (!(x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1)) continue;
+    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
+    const TileStage& st = s_tile[stage];
+    const uint2 tn = st.px[1][threadIdx.x];
+    const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
+    if (nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f) {  // all-zero normal = cleared texel
+      stg_stream8(outp, make_uint2(0u, 0u));
+      continue;
+    }
+    // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
+    const uint2 tp = st.px[0][threadIdx.x];
+    const uint32_t to = st.orm[threadIdx.x];
+    const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
+    const float3 P = make_float3(pxy.x, pxy.y, pzw.x);
+    const float ninv = rsq(nxy.x * nxy.x + nxy.y * nxy.y + nzw.x * nzw.x);
+    const float3 N = make_float3(nxy.x * ninv, nxy.y * ninv, nzw.x * ninv);
+    float cx = p.cx, cy = p.cy, cz = p.cz;
+    if (BATCHED) { cx = __ldg(p.cams + 3 * ip.view); cy = __ldg(p.cams + 3 * ip.view + 1); cz = __ldg(p.cams + 3 * ip.view + 2); }
+    const float vx = cx - P.x, vy = cy - P.y, vz = cz - P.z;
+    const float vinv = rsq(vx * vx + vy * vy + vz * vz);
+    const float3 V = make_float3(vx * vinv, vy * vinv, vz * vinv);
+    const float NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
+    const float NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
+    const float rough = fminf(fmaxf(float((to >> 8) & 0xFFu) * (1.0f / 255.0f), 0.045f), 1.0f);
+    const float metal = float((to >> 16) & 0xFFu) * (1.0f / 255.0f), omm = 1.0f - metal;
+    float F0r, F0g, F0b, cdpr, cdpg, cdpb;
+    {
+      const uint2 ta = st.px[2][threadIdx.x];
+      const float base_r = unorm16_lo(ta.x), base_g = unorm16_hi(ta.x), base_b = unorm16_lo(ta.y);
+      F0r = 0.04f * omm + base_r * metal; F0g = 0.04f * omm + base_g * metal; F0b = 0.04f * omm + base_b * metal;
+      const float cdr = base_r * omm, cdg = base_g * omm, cdb = base_b * omm;
+      cdpr = cdr * kInvPi; cdpg = cdg * kInvPi; cdpb = cdb * kInvPi;
+      s_amb[2][threadIdx.x] = make_float4(0.f, cdr, cdg, cdb);
+    }
+    const float alpha = rough * rough;
+    const float a2 = alpha * alpha, oma2 = 1.0f - a2;
+    const float vv = NoV * NoV * oma2 + a2;
+    const float visV = vv * rsq(vv);
+    const float omF0r = 1.0f - F0r, omF0g = 1.0f - F0g, omF0b = 1.0f - F0b;
+    const float a2h = a2 * (0.5f * kInvPi);
+
+    // ---- ambient set-up: the four footprint records are loaded here and consumed after the light loop ----
+    Quad6 qi, q0, q1;
+    Quad8 ql;
+    if (p.has_ibl) {
+      const float3 Rv = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
+      const IblTaps taps = make_ibl_taps(p, N, Rv, NoV, rough);
+      q0 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p0));
+      q1 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p1));
+      qi = ldg_rec256(p.q_irr + 2 * size_t(taps.i_irr));
+      ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
+      s_amb[0][threadIdx.x] = make_float4(taps.irr_tx, taps.irr_ty, taps.p0_tx, taps.p0_ty);
+      s_amb[1][threadIdx.x] = make_float4(taps.p1_tx, taps.p1_ty, taps.lut_tx, taps.lut_ty);
+      reinterpret_cast<float*>(&s_amb[2][threadIdx.x])[0] = taps.lod_f;
+    }
+
+    // ---- direct lighting: four lights per iteration as two independent packed chains ----
+    f2 dr2 = dup(0.f), dg2 = dr2, db2 = dr2;
+    auto pair_a = [&](const float4 l0, const float4 l1) {
+      PairA a;
+      a.dx = sub2(pk(l0.x, l0.y), dup(P.x)); a.dy = sub2(pk(l0.z, l0.w), dup(P.y)); a.dz = sub2(pk(l1.x, l1.y), dup(P.z));
+      const f2 d2 = max2(fma2(a.dz, a.dz, fma2(a.dy, a.dy, mul2(a.dx, a.dx))), 1e-8f);
+      a.invd = map2(d2, rsq);
+      a.NoL = sat2(mul2(fma2(dup(N.z), a.dz, fma2(dup(N.y), a.dy, mul2(dup(N.x), a.dx))), a.invd));
+      const f2 qq = mul2(d2, pk(l1.z, l1.w));               // (d/range)^2; 0 for unlimited range
+      const f2 win = sat2(sub2(one, mul2(qq, qq)));         // clamp(1 - (d/range)^4, 0, 1)
+      a.w = mul2(mul2(mul2(a.invd, a.invd), win), a.NoL);   // inverse square * window * N.L
+      return a;
+    };
+    // radiance factor of a pair per channel: (1 - F) c_diff/pi + F D Vis = c_diff/pi + F (D Vis - c_diff/pi); the
+    // formulas are shade_ggx_kernel's (see the comments there)
+    auto pair_b = [&](const PairA& a, f2& br, f2& bg, f2& bb) {
+      const f2 hx = fma2(a.dx, a.invd, dup(V.x)), hy = fma2(a.dy, a.invd, dup(V.y)), hz = fma2(a.dz, a.invd, dup(V.z));
+      const f2 hh = max2(fma2(hz, hz, fma2(hy, hy, mul2(hx, hx))), 1e-12f);
+      const f2 nhinv = map2(hh, [](float v) { return -rsq(v); });
+      const f2 VoH = mul2(mul2(hh, nhinv), dup(-0.5f));
+      const f2 ex = fma2(hx, nhinv, dup(N.x)), ey = fma2(hy, nhinv, dup(N.y)), ez = fma2(hz, nhinv, dup(N.z));
+      const f2 sq = fma2(ez, ez, fma2(ey, ey, mul2(ex, ex)));
+      const f2 u = fma2(mul2(sq, sq), dup(-0.25f), sq);
+      const f2 ddn = fma2(u, dup(oma2), dup(a2));
+      const f2 dd = pk(lo(sq) > 2.0f ? lo(u) : lo(ddn), hi(sq) > 2.0f ? hi(u) : hi(ddn));
+      const f2 vl = fma2(mul2(a.NoL, a.NoL), dup(oma2), dup(a2));
+      const f2 den = fma2(dup(NoV), mul2(vl, map2(vl, rsq)), mul2(a.NoL, dup(visV)));
+      const f2 dv = mul2(dup(a2h), map2(mul2(mul2(dd, dd), den), rcp));
+      const f2 t = sub2(one, VoH), t2 = mul2(t, t), fc = mul2(mul2(t2, t2), t);
+      const f2 Fr = fma2(dup(omF0r), fc, dup(F0r)), Fg = fma2(dup(omF0g), fc, dup(F0g)), Fb = fma2(dup(omF0b), fc, dup(F0b));
+      br = fma2(Fr, sub2(dv, dup(cdpr)), dup(cdpr));
+      bg = fma2(Fg, sub2(dv, dup(cdpg)), dup(cdpg));
+      bb = fma2(Fb, sub2(dv, dup(cdpb)), dup(cdpb));
+    };
+    for (uint32_t it = 0; it < quads; ++it) {
+      const float4* lp = s_lp + 4 * it;
+      const PairA a = pair_a(lp[0], lp[1]), b = pair_a(lp[2], lp[3]);
+      if (fmaxf(fmaxf(lo(a.w), hi(a.w)), fmaxf(lo(b.w), hi(b.w))) > 0.0f) {
+        f2 ar, ag, ab, br, bg, bb;
+        pair_b(a, ar, ag, ab);
+        pair_b(b, br, bg, bb);
+        const float4* lc = s_lc + 4 * it;
+        const float4 c0 = lc[0], c1 = lc[1], c2 = lc[2], c3 = lc[3];
+        // the pairs are added in list order: the same sums as shade_ggx_kernel's
+        dr2 = fma2(ar, mul2(pk(c0.x, c0.y), a.w), dr2); dg2 = fma2(ag, mul2(pk(c0.z, c0.w), a.w), dg2); db2 = fma2(ab, mul2(pk(c1.x, c1.y), a.w), db2);
+        dr2 = fma2(br, mul2(pk(c2.x, c2.y), b.w), dr2); dg2 = fma2(bg, mul2(pk(c2.z, c2.w), b.w), dg2); db2 = fma2(bb, mul2(pk(c3.x, c3.y), b.w), db2);
+      }
+    }
+    const float dr = lo(dr2) + hi(dr2), dg = lo(dg2) + hi(dg2), db = lo(db2) + hi(db2);
+
+    // ---- ambient: split-sum image-based lighting (Karis 2013) ----
+    float ar = 0.f, ag = 0.f, ab = 0.f;
+    if (p.has_ibl) {
+      const float4 w0 = s_amb[0][threadIdx.x], w1 = s_amb[1][threadIdx.x], w2 = s_amb[2][threadIdx.x];
+      const RGB irr = quad_bilinear_rgb(qi, w0.x, w0.y);
+      RGB pre = quad_bilinear_rgb(q0, w0.z, w0.w);
+      const RGB pr1 = quad_bilinear_rgb(q1, w1.x, w1.y);
+      pre.r = lerpf(pre.r, pr1.r, w2.x); pre.g = lerpf(pre.g, pr1.g, w2.x); pre.b = lerpf(pre.b, pr1.b, w2.x);
+      const float2 sb = quad_bilinear_lut(ql, w1.z, w1.w);
+      const float occ = float(st.orm[threadIdx.x] & 0xFFu) * (1.0f / 255.0f);
+      ar = (irr.r * w2.y + pre.r * (F0r * sb.x + sb.y)) * occ;
+      ag = (irr.g * w2.z + pre.g * (F0g * sb.x + sb.y)) * occ;
+      ab = (irr.b * w2.w + pre.b * (F0b * sb.x + sb.y)) * occ;
+    }
+    const uint2 te = st.px[3][threadIdx.x];
+    const float2 exy = h2_to_f2(te.x), ezw = h2_to_f2(te.y);
+    const float base_a = unorm16_hi(st.px[2][threadIdx.x].y);
+    // oracle order: (direct + ambient) + emissive
+    const float Lr = fminf((dr + ar) + exy.x, 65504.0f), Lg = fminf((dg + ag) + exy.y, 65504.0f), Lb = fminf((db + ab) + ezw.x, 65504.0f);
+    stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+  }
+  cp_async_wait<0>();
+}
+
 // ---- K3c: per 16x16 tile, world-space AABB of the tile's non-cleared positions, then every light
 // whose range sphere meets it, in ascending light index (so K3 sums in the oracle's order).
 // One WARP per tile (eight tiles per CTA): the 256 pixels are read as eight fully coalesced 2-row slabs, the box is
@@ -563,6 +766,11 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   const bool one_list = p.tile_counts == nullptr && p.n_lights <= uint32_t(kLightChunk);
   PBRCU_REQUIRE(n_views == 1 || one_list, "batched shading takes no tile lists and at most 128 lights");
   const int lists = n_views > 1 ? LIST_ONE_BATCHED : one_list ? LIST_ONE : LIST_TILED;
+  if (!tex && lists != LIST_TILED && (p.q_pref || !p.has_ibl)) {  // one list, footprint records or no IBL
+    if (lists == LIST_ONE_BATCHED) shade_ggx_one_kernel<true><<<grid, kShadeThreads, 0, st>>>(p);
+    else shade_ggx_one_kernel<false><<<grid, kShadeThreads, 0, st>>>(p);
+    return launch_check("shade_ggx_one_kernel");
+  }
   if (tex) launch_shade<IBL_TEX>(p, lists, grid, st);
   else if (p.q_pref) launch_shade<IBL_RECORDS>(p, lists, grid, st);
   else launch_shade<IBL_PLAIN>(p, lists, grid, st);
