@@ -39,10 +39,10 @@ W4K, H4K = 3840, 2160
 N_LIGHTS = 4
 B_PER_PX_K3 = 44   # 36 read (pos 8 + nrm 8 + albedo 8 + emissive 8 + orm 4) + 8 written
 B_PER_PX_K1 = 32   # 24 read + 8 written
-# dram__bytes_read.sum + dram__bytes_write.sum of one shade_ggx_kernel launch on this workload, from the committed
-# `ncu --set full` capture (profiles/r01_k3_shade_ggx_ncu_details.txt): 519.3 MB + 60.7 MB; the 215 MB above the
+# dram__bytes_read.sum + dram__bytes_write.sum of one shade_ggx_one_kernel launch on this workload, from the committed
+# `ncu --set full` capture (profiles/r01_k3_one_kernel_ncu.txt): 523.1 MB + 61.0 MB; the 219 MB above the
 # algorithmic 365 MB are the IBL footprint records and write-allocate traffic
-K3_DRAM_TRAFFIC_BYTES = 585.7e6
+K3_DRAM_TRAFFIC_BYTES = 584.1e6
 ENV_W, ENV_H = 4096, 2048
 CUBE_RES, CUBE_MIPS, IBL_SAMPLES, IRR_RES, LUT_RES = 2048, 12, 1024, 64, 512
 CAM = (0.0, -1.0, -12.0)
@@ -554,7 +554,7 @@ def main_ours(args):
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 4), "traffic": K3_DRAM_TRAFFIC_BYTES, "traffic_unit": "bytes per launch (ncu, profiles/)",
                          "algorithmic_bytes_per_launch": B_PER_PX_K3 * px_step, "peak_source": peak_src,
-                         "kernel": "shade_ggx_kernel", "algorithmic_bytes_per_px": B_PER_PX_K3},
+                         "kernel": "shade_ggx_one_kernel", "algorithmic_bytes_per_px": B_PER_PX_K3},
             "e2e": {"value": round(e2e_value, 1), "unit": "Mpix/s", "h2d_bytes_per_step": px_step * 36,
                     "d2h_bytes_per_step": px_step * 8, "steps": e2e_steps, "api": "pbrcu_shade_frame_host (pinned host planes, 8 pipelined row bands)"},
             "gpu_launches": args.steps,

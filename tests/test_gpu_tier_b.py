@@ -186,6 +186,36 @@ def test_shade_matches_oracle(pbr, dev, oracle, w, h, nl, use_ibl):
         dev.lib.ibl_accel_free(dev.ctx, ibl2.accel)
 
 
+@pytest.mark.parametrize("nl", [1, 2, 3, 5, 6, 7, 9])
+def test_shade_single_list_kernel_light_counts_and_ragged_rect(pbr, dev, oracle, nl):
+    """shade_ggx_one_kernel (one light list + footprint records) takes FOUR lights per iteration and pads the list with null
+    lights: every count around the padding, on a rect that starts and ends inside tiles, with a pitched output whose
+    texels outside the rect must stay untouched."""
+    host, bufs = build_ibl(dev, oracle)
+    w, h = 75, 53
+    g = synth_gbuffer(w, h, seed=100 + nl, tier_b=True)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    lights = synth_lights(nl, seed=20 + nl)
+    ld = dev.upload(lights)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    cam = (0.5, -1.0, 12.0)
+    pitch = (w + 5) * 8
+    sentinel = np.full((h, w + 5, 4), 0x7B7B, np.uint16)
+    out = dev.upload(sentinel)
+    x0, y0, rw, rh = 5, 3, 61, 42
+    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr, nl, None, C.byref(ibl), pbr.Rect(x0, y0, rw, rh), out.ptr, pitch, None)
+    dev.sync()
+    got = out.download((h, w + 5, 4), np.uint16)
+    _, want = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, lights, host)
+    peak = float(max(f16(want).max(), 1.0))
+    assert_hdr_parity(got[y0:y0 + rh, x0:x0 + rw], want[y0:y0 + rh, x0:x0 + rw], peak=peak, rel_tol=REL, what=f"single-list kernel nl={nl}")
+    outside = np.ones((h, w + 5), bool)
+    outside[y0:y0 + rh, x0:x0 + rw] = False
+    assert (got[outside] == 0x7B7B).all(), "texels outside the rect were written"
+    assert (got[y0:y0 + rh, x0:x0 + rw][g["bg"][y0:y0 + rh, x0:x0 + rw]] == 0).all()
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+
+
 def test_shade_texture_unit_on_sharp_environment(pbr, dev, oracle):
     """K3's texture-unit path with a hard-edged 5e3 sun in the environment (the worst case for the unit's 8-bit
     weights): the contrast flags must route the affected pixels to the fp32-weight records."""
