@@ -66,15 +66,17 @@ __global__ void __launch_bounds__(kConvThreads) conv_kernel(const __grid_constan
   for (int s = threadIdx.x; s < p.nsamples; s += kConvThreads) table[s] = table_entry<MODE>(p, uint32_t(s));
   __syncthreads();
 
-  const int texel = threadIdx.x / G, lane = threadIdx.x % G;
-  int tx_in = texel % p.tw, ty_in = texel / p.tw;
-  if (G == 1 && p.tw % 8 == 0 && p.th % 4 == 0) {
-    // a warp covers an 8x4 texel patch instead of a 32x1 strip: its 32 fetches of one sample then fall
-    // into a compact 2-D footprint of the source level (fewer texture cache lines per request)
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, wpr = p.tw >> 3;
-    tx_in = (w % wpr) * 8 + (l & 7);
-    ty_in = (w / wpr) * 4 + (l >> 3);
-  }
+  // A warp holds TPW = 32 / G texels, each with G lanes that take every G-th sample.  The texels of a warp are a compact
+  // patch walked in Morton order (8x4 for G = 1, 4x4, 4x2, 2x2, 2x1, 1x1), lane = sample group * TPW + texel: the four lanes
+  // the texture unit filters together (4k .. 4k+3) are then a 2x2 block of texels taking the SAME sample, so their
+  // footprints overlap in the source level, instead of a 4x1 strip (G = 1: 25.7 -> 18.7 ms for the 2048^2 chain) or four
+  // unrelated samples of one texel (G >= 4).
+  constexpr int TPW = 32 / G;
+  constexpr int PW = TPW >= 32 ? 8 : TPW >= 8 ? 4 : TPW >= 2 ? 2 : 1, PH = TPW / PW;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, t = l % TPW, lane = l / TPW;
+  const int mx = (t & 1) | ((t >> 1) & 2) | ((t >> 2) & 4), my = ((t >> 1) & 1) | ((t >> 2) & 2);
+  const int ppr = p.tw / PW;  // patches per row of the block's tile
+  const int tx_in = (w % ppr) * PW + mx, ty_in = (w / ppr) * PH + my;
   const int x = blockIdx.x * p.tw + tx_in;
   const int grow = p.row_begin + blockIdx.y * p.th + ty_in;
   const bool valid = x < p.res && grow < p.row_end;
@@ -89,11 +91,39 @@ __global__ void __launch_bounds__(kConvThreads) conv_kernel(const __grid_constan
   const float3 B = make_float3(N.y * T.z - N.z * T.y, N.z * T.x - N.x * T.z, N.x * T.y - N.y * T.x);
 
   float ar = 0.f, ag = 0.f, ab = 0.f, wsum = 0.f;
-  for (int s = lane; s < p.nsamples; s += G) {
+  auto dir_of = [&](const float4 e) {
+    return make_float3(T.x * e.x + B.x * e.y + N.x * e.z, T.y * e.x + B.y * e.y + N.y * e.z, T.z * e.x + B.z * e.y + N.z * e.z);
+  };
+  auto add = [&](const float4 e, const RGB c) {
+    const float w = (MODE == CONV_GGX) ? e.z : 1.0f;
+    ar = fmaf(c.r, w, ar); ag = fmaf(c.g, w, ag); ab = fmaf(c.b, w, ab);
+    wsum += w;
+  };
+  int s = lane;
+  if (TEX) {
+    // four samples per iteration: their fetches are issued back to back, BEFORE any of the flag tests, so a thread has four
+    // fetches in flight instead of one (the small levels run a single partial wave and were bound by the fetch latency:
+    // level 4 of the 2048^2 chain 0.70 -> see DESIGN 3.2).  The sums are taken in sample order, as before.
+    for (; s + 3 * G < p.nsamples; s += 4 * G) {
+      float4 e[4], t[4];
+      float3 L[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        e[k] = table[s + k * G];
+        L[k] = dir_of(e[k]);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)  // Karis: `if (NoL > 0)`; a sample below the horizon is fetched and ignored
+        t[k] = texCubemapLod<float4>(p.tex, L[k].x, L[k].y, L[k].z, e[k].w);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (e[k].z > 0.0f) add(e[k], t[k].w > 0.0f ? cube_sample(p.src, L[k], e[k].w) : RGB{t[k].x, t[k].y, t[k].z});
+    }
+  }
+  for (; s < p.nsamples; s += G) {
     const float4 e = table[s];
-    if (e.z > 0.0f) {  // Karis: `if (NoL > 0)`; G == 1: uniform across the warp
-      const float3 L = make_float3(T.x * e.x + B.x * e.y + N.x * e.z, T.y * e.x + B.y * e.y + N.y * e.z,
-                                   T.z * e.x + B.z * e.y + N.z * e.z);
+    if (e.z > 0.0f) {  // Karis: `if (NoL > 0)`
+      const float3 L = dir_of(e);
       RGB c;
       if (TEX) {
         // alpha of the texture copy = contrast flag of the footprint (see contrast_flags_kernel): where the
@@ -104,13 +134,11 @@ __global__ void __launch_bounds__(kConvThreads) conv_kernel(const __grid_constan
       } else {
         c = cube_sample(p.src, L, e.w);
       }
-      const float w = (MODE == CONV_GGX) ? e.z : 1.0f;
-      ar = fmaf(c.r, w, ar); ag = fmaf(c.g, w, ag); ab = fmaf(c.b, w, ab);
-      wsum += w;
+      add(e, c);
     }
   }
 #pragma unroll
-  for (int off = G / 2; off > 0; off >>= 1) {  // warp-shuffle reduction over the texel's G lanes
+  for (int off = TPW; off < 32; off <<= 1) {  // warp-shuffle reduction over the texel's G lanes (TPW apart)
     ar += __shfl_xor_sync(0xffffffffu, ar, off);
     ag += __shfl_xor_sync(0xffffffffu, ag, off);
     ab += __shfl_xor_sync(0xffffffffu, ab, off);
@@ -134,11 +162,12 @@ static int launch_conv(const pbrcu_ctx* ctx, ConvParams p, cudaStream_t s) {
   const size_t texels = size_t(6) * p.res * p.res;
   int G = 1;
   while (G < 32 && texels * G < size_t(ctx->sm_count) * 1024) G *= 2;
-  const int per_block = kConvThreads / G;
-  p.tw = p.res < 32 ? p.res : 32;
-  if (p.tw > per_block) p.tw = per_block;
-  p.th = per_block / p.tw;
-  while (p.tw * p.th * G != kConvThreads) { --p.tw; p.th = per_block / p.tw; }  // res not a power of two
+  // block tile = the 8 warps' patches, 4 x 2 of them where the level is wide enough
+  const int tpw = 32 / G, pw = tpw >= 32 ? 8 : tpw >= 8 ? 4 : tpw >= 2 ? 2 : 1, ph = tpw / pw;
+  int ppr = 4;
+  while (ppr > 1 && ppr * pw > p.res) ppr /= 2;
+  p.tw = ppr * pw;
+  p.th = (kConvThreads / 32 / ppr) * ph;
   dim3 grid((p.res + p.tw - 1) / p.tw, (rows + p.th - 1) / p.th);
   const size_t smem = size_t(p.nsamples) * sizeof(float4);
 #define PBRCU_CONV_CASE(GG)                                                                          \
