@@ -66,15 +66,22 @@ __device__ __forceinline__ float hsub_hi(uint32_t w, float a) {
   return f;
 }
 
-// footprint origin and weights of a bilinear tap at normalised (u, v) in a res x res face
+// footprint origin and weights of a bilinear tap at normalised (u, v) in a res x res face.
+// floor() and the float -> int conversion are done on the FMA pipe: for 0 <= f < 2^22, f + 1.5 * 2^23 rounded DOWN is
+// exactly floor(f) + 1.5 * 2^23, whose bit pattern is 0x4B400000 + floor(f) -- FRND and F2I run on the quarter-rate XU pipe
+// and sit on the dependency chain that leads to the record loads.
 struct Tap { float tx, ty; int idx; };
-__device__ __forceinline__ Tap make_tap(float u, float v, float resf) {
+__device__ __forceinline__ Tap make_tap(float u, float v, int res) {
+  const float resf = float(res);
+  constexpr float kMagic = 12582912.0f;  // 1.5 * 2^23
   const float fx = fmaxf(fmaf(u, resf, -0.5f), 0.0f), fy = fmaxf(fmaf(v, resf, -0.5f), 0.0f);
-  const float x0 = floorf(fx), y0 = floorf(fy);
+  const float bx = __fadd_rd(fx, kMagic), by = __fadd_rd(fy, kMagic);
+  const float x0 = bx - kMagic, y0 = by - kMagic;  // exact
   Tap t;
   t.tx = fx - x0;
   t.ty = fy - y0;
-  t.idx = __float2int_rz(fmaf(y0, resf, x0));  // exact: < 2^24 for res <= 4096
+  const int ix = __float_as_int(bx) - 0x4B400000, iy = __float_as_int(by) - 0x4B400000;
+  t.idx = iy * res + ix;
   return t;
 }
 

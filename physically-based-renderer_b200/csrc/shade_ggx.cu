@@ -100,7 +100,7 @@ __device__ __forceinline__ IblTaps make_ibl_taps(const ShadeParams& p, float3 N,
   float u, v;
   cube_dir_to_face_uv(N, face, u, v);
   const int ires = int(p.irr.base_res);
-  Tap a = make_tap(u, v, float(ires));
+  Tap a = make_tap(u, v, ires);
   t.i_irr = face * ires * ires + a.idx; t.irr_tx = a.tx; t.irr_ty = a.ty;
   cube_dir_to_face_uv(R, face, u, v);
   const float lod = fminf(rough * float(p.pref.nmips - 1), float(p.pref.nmips - 1));  // rough >= 0.045 > 0
@@ -108,11 +108,11 @@ __device__ __forceinline__ IblTaps make_ibl_taps(const ShadeParams& p, float3 N,
   t.lod_f = lod - l0f;
   const int l0 = int(l0f), l1 = min(l0 + 1, int(p.pref.nmips) - 1);
   const int r0 = int(p.pref.base_res >> l0), r1 = int(p.pref.base_res >> l1);
-  a = make_tap(u, v, float(r0));
+  a = make_tap(u, v, r0);
   t.i_p0 = int(p.pref.mip_offset[l0]) + face * r0 * r0 + a.idx; t.p0_tx = a.tx; t.p0_ty = a.ty;
-  a = make_tap(u, v, float(r1));
+  a = make_tap(u, v, r1);
   t.i_p1 = int(p.pref.mip_offset[l1]) + face * r1 * r1 + a.idx; t.p1_tx = a.tx; t.p1_ty = a.ty;
-  a = make_tap(NoV, rough, float(p.lut_res));
+  a = make_tap(NoV, rough, int(p.lut_res));
   t.i_lut = a.idx; t.lut_tx = a.tx; t.lut_ty = a.ty;
   return t;
 }
@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
         tirr = texCubemapLod<float4>(p.t_irr, N.x, N.y, N.z, 0.0f);
         // a level fraction the unit would round to 1 hides the finer level's flags: treat it as flagged
         if (lod - floorf(lod) > 0.995f) tirr.w = 1.0f;
-        tlut = make_tap(NoV, rough, float(p.lut_res));
+        tlut = make_tap(NoV, rough, int(p.lut_res));
         ql = ldg_quad(p.q_lut + 2 * size_t(tlut.idx));
       }
     }
