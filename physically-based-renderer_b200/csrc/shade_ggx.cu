@@ -158,6 +158,54 @@ __device__ __forceinline__ void stage_tile(const ShadeParams& p, TileStage& st, 
   }
 }
 
+// ---- the light evaluation both K3 kernels share: KHR_lights_punctual point lights, Cook-Torrance GGX / Smith / Schlick,
+// two lights per call in the lanes of packed f32x2 instructions ----
+struct LightPixel {  // what the light loop reads of a pixel
+  float3 P, N, V;
+  float NoV, visV, a2, oma2, a2h, F0r, F0g, F0b, omF0r, omF0g, omF0b, cdpr, cdpg, cdpb;  // a2h = a2 / (2 pi), cdp = c_diff / pi
+};
+struct PairA { f2 dx, dy, dz, invd, NoL, w; };
+
+// geometry of a staged light pair {{x0,x1,y0,y1}, {z0,z1,w0,w1}} (w = 1/range^2, 0 = unlimited): w = inverse square * window * N.L
+__device__ __forceinline__ PairA light_pair_a(const LightPixel& s, const float4 l0, const float4 l1) {
+  const f2 one = dup(1.0f);
+  PairA a;
+  a.dx = sub2(pk(l0.x, l0.y), dup(s.P.x)); a.dy = sub2(pk(l0.z, l0.w), dup(s.P.y)); a.dz = sub2(pk(l1.x, l1.y), dup(s.P.z));
+  const f2 d2 = max2(fma2(a.dz, a.dz, fma2(a.dy, a.dy, mul2(a.dx, a.dx))), 1e-8f);
+  a.invd = map2(d2, rsq);
+  a.NoL = sat2(mul2(fma2(dup(s.N.z), a.dz, fma2(dup(s.N.y), a.dy, mul2(dup(s.N.x), a.dx))), a.invd));
+  const f2 qq = mul2(d2, pk(l1.z, l1.w));               // (d/range)^2; 0 for unlimited range
+  const f2 win = sat2(sub2(one, mul2(qq, qq)));         // clamp(1 - (d/range)^4, 0, 1)
+  a.w = mul2(mul2(mul2(a.invd, a.invd), win), a.NoL);
+  return a;
+}
+
+// radiance factor of the pair per channel: (1 - F) c_diff/pi + F D Vis = c_diff/pi + F (D Vis - c_diff/pi)
+__device__ __forceinline__ void light_pair_b(const LightPixel& s, const PairA& a, f2& br, f2& bg, f2& bb) {
+  const f2 one = dup(1.0f);
+  const f2 hx = fma2(a.dx, a.invd, dup(s.V.x)), hy = fma2(a.dy, a.invd, dup(s.V.y)), hz = fma2(a.dz, a.invd, dup(s.V.z));  // V + L
+  const f2 hh = max2(fma2(hz, hz, fma2(hy, hy, mul2(hx, hx))), 1e-12f);  // V = -L: grazing back-facing pixel
+  const f2 nhinv = map2(hh, [](float v) { return -rsq(v); });
+  // |V| = |L| = 1: V.h = 1 + V.L = |h|^2 / 2, so V.H = |h| / 2 (in [0, 1] by construction)
+  const f2 VoH = mul2(mul2(hh, nhinv), dup(-0.5f));
+  // 1 - NoH^2 without cancellation: sq = |N - H|^2 = 2 - 2 N.H  =>  u = 1 - (N.H)^2 = sq (1 - sq/4)
+  // (what the oracle takes from |N x H|^2).  D's denominator NoH^2 (a2 - 1) + 1 with
+  // NoH = max(N.H, 0) is then u (1 - a2) + a2, or just u where N.H < 0, i.e. sq > 2.
+  const f2 ex = fma2(hx, nhinv, dup(s.N.x)), ey = fma2(hy, nhinv, dup(s.N.y)), ez = fma2(hz, nhinv, dup(s.N.z));
+  const f2 sq = fma2(ez, ez, fma2(ey, ey, mul2(ex, ex)));
+  const f2 u = fma2(mul2(sq, sq), dup(-0.25f), sq);
+  const f2 ddn = fma2(u, dup(s.oma2), dup(s.a2));
+  const f2 dd = pk(lo(sq) > 2.0f ? lo(u) : lo(ddn), hi(sq) > 2.0f ? hi(u) : hi(ddn));
+  const f2 vl = fma2(mul2(a.NoL, a.NoL), dup(s.oma2), dup(s.a2));
+  const f2 den = fma2(dup(s.NoV), mul2(vl, map2(vl, rsq)), mul2(a.NoL, dup(s.visV)));
+  const f2 dv = mul2(dup(s.a2h), map2(mul2(mul2(dd, dd), den), rcp));  // D * Vis = a2/(pi dd^2) * 0.5/den
+  const f2 t = sub2(one, VoH), t2 = mul2(t, t), fc = mul2(mul2(t2, t2), t);
+  const f2 Fr = fma2(dup(s.omF0r), fc, dup(s.F0r)), Fg = fma2(dup(s.omF0g), fc, dup(s.F0g)), Fb = fma2(dup(s.omF0b), fc, dup(s.F0b));
+  br = fma2(Fr, sub2(dv, dup(s.cdpr)), dup(s.cdpr));
+  bg = fma2(Fg, sub2(dv, dup(s.cdpg)), dup(s.cdpg));
+  bb = fma2(Fb, sub2(dv, dup(s.cdpb)), dup(s.cdpb));
+}
+
 template <int IBL, int LISTS>
 __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
   constexpr bool ONE_LIST = LISTS != LIST_TILED, BATCHED = LISTS == LIST_ONE_BATCHED;
@@ -298,7 +346,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
       idx = p.tile_indices + size_t(t) * p.max_per_tile;
     }
     f2 dr2 = dup(0.f), dg2 = dr2, db2 = dr2;  // per lane: the even / the odd lights of the list, in list order
-    const f2 one = dup(1.0f);
+    const LightPixel lp{P, N, V, NoV, visV, a2, oma2, a2h, F0r, F0g, F0b, omF0r, omF0g, omF0b, cdpr, cdpg, cdpb};
     for (uint32_t base = 0; base < nl; base += kLightChunk) {
       const uint32_t cnt = ONE_LIST ? nl : min(nl - base, uint32_t(kLightChunk));
       if (!ONE_LIST) {
@@ -308,38 +356,14 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
       }
       if (!lit) continue;
       for (uint32_t j = 0; 2 * j < cnt; ++j) {
-        const float4 l0 = s_lp[2 * j], l1 = s_lp[2 * j + 1];
-        const f2 dx = sub2(pk(l0.x, l0.y), dup(P.x)), dy = sub2(pk(l0.z, l0.w), dup(P.y)), dz = sub2(pk(l1.x, l1.y), dup(P.z));
-        const f2 d2 = max2(fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))), 1e-8f);
-        const f2 invd = map2(d2, rsq);
-        const f2 NoL = sat2(mul2(fma2(dup(N.z), dz, fma2(dup(N.y), dy, mul2(dup(N.x), dx))), invd));
-        const f2 qq = mul2(d2, pk(l1.z, l1.w));               // (d/range)^2; 0 for unlimited range
-        const f2 win = sat2(sub2(one, mul2(qq, qq)));         // clamp(1 - (d/range)^4, 0, 1)
-        const f2 w = mul2(mul2(mul2(invd, invd), win), NoL);  // inverse square * window * N.L
-        if (lo(w) > 0.0f || hi(w) > 0.0f) {
-          const f2 hx = fma2(dx, invd, dup(V.x)), hy = fma2(dy, invd, dup(V.y)), hz = fma2(dz, invd, dup(V.z));  // V + L
-          const f2 hh = max2(fma2(hz, hz, fma2(hy, hy, mul2(hx, hx))), 1e-12f);  // V = -L: grazing back-facing pixel
-          const f2 nhinv = map2(hh, [](float x) { return -rsq(x); });
-          // |V| = |L| = 1: V.h = 1 + V.L = |h|^2 / 2, so V.H = |h| / 2 (in [0, 1] by construction)
-          const f2 VoH = mul2(mul2(hh, nhinv), dup(-0.5f));
-          // 1 - NoH^2 without cancellation: s = |N - H|^2 = 2 - 2 N.H  =>  u = 1 - (N.H)^2 = s (1 - s/4)
-          // (what the oracle takes from |N x H|^2).  D's denominator NoH^2 (a2 - 1) + 1 with
-          // NoH = max(N.H, 0) is then u (1 - a2) + a2, or just u where N.H < 0, i.e. s > 2.
-          const f2 ex = fma2(hx, nhinv, dup(N.x)), ey = fma2(hy, nhinv, dup(N.y)), ez = fma2(hz, nhinv, dup(N.z));
-          const f2 sq = fma2(ez, ez, fma2(ey, ey, mul2(ex, ex)));
-          const f2 u = fma2(mul2(sq, sq), dup(-0.25f), sq);
-          const f2 ddn = fma2(u, dup(oma2), dup(a2));
-          const f2 dd = pk(lo(sq) > 2.0f ? lo(u) : lo(ddn), hi(sq) > 2.0f ? hi(u) : hi(ddn));
-          const f2 vl = fma2(mul2(NoL, NoL), dup(oma2), dup(a2));
-          const f2 den = fma2(dup(NoV), mul2(vl, map2(vl, rsq)), mul2(NoL, dup(visV)));
-          const f2 dv = mul2(dup(a2h), map2(mul2(mul2(dd, dd), den), rcp));  // D * Vis = a2/(pi dd^2) * 0.5/den
-          const f2 t = sub2(one, VoH), t2 = mul2(t, t), fc = mul2(mul2(t2, t2), t);
-          const f2 Fr = fma2(dup(omF0r), fc, dup(F0r)), Fg = fma2(dup(omF0g), fc, dup(F0g)), Fb = fma2(dup(omF0b), fc, dup(F0b));
+        const PairA a = light_pair_a(lp, s_lp[2 * j], s_lp[2 * j + 1]);
+        if (lo(a.w) > 0.0f || hi(a.w) > 0.0f) {
+          f2 br, bg, bb;
+          light_pair_b(lp, a, br, bg, bb);
           const float4 c0 = s_lc[2 * j], c1 = s_lc[2 * j + 1];
-          // (1 - F) c_diff/pi + F D Vis = c_diff/pi + F (D Vis - c_diff/pi)
-          dr2 = fma2(fma2(Fr, sub2(dv, dup(cdpr)), dup(cdpr)), mul2(pk(c0.x, c0.y), w), dr2);
-          dg2 = fma2(fma2(Fg, sub2(dv, dup(cdpg)), dup(cdpg)), mul2(pk(c0.z, c0.w), w), dg2);
-          db2 = fma2(fma2(Fb, sub2(dv, dup(cdpb)), dup(cdpb)), mul2(pk(c1.x, c1.y), w), db2);
+          dr2 = fma2(br, mul2(pk(c0.x, c0.y), a.w), dr2);
+          dg2 = fma2(bg, mul2(pk(c0.z, c0.w), a.w), dg2);
+          db2 = fma2(bb, mul2(pk(c1.x, c1.y), a.w), db2);
         }
       }
     }
@@ -402,8 +426,6 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
 // Registers for both come from deferring everything only the ambient term needs (tap weights, c_diff, occlusion,
 // emissive, alpha) to shared memory: a small per-thread stash, and the staged tile itself, which stays valid for the
 // whole iteration.  Unlit and outside pixels leave the iteration early instead of carrying neutral values through it.
-struct PairA { f2 dx, dy, dz, invd, NoL, w; };
-
 __device__ __forceinline__ Quad6 ldg_rec256(const uint4* p) {
   Quad6 q;
   uint32_t pad0, pad1;
@@ -450,7 +472,6 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
   cp_async_commit();
   __syncthreads();
   const uint32_t quads = (p.n_lights + 3) >> 2;
-  const f2 one = dup(1.0f);
 
   uint32_t ntile = tile, nview = view;
   for (; live(tile, view); tile = ntile, view = nview, stage ^= 1) {
@@ -476,43 +497,43 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
       continue;
     }
     // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
+    LightPixel s;
     const uint2 tp = st.px[0][threadIdx.x];
     const uint32_t to = st.orm[threadIdx.x];
     const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
-    const float3 P = make_float3(pxy.x, pxy.y, pzw.x);
+    s.P = make_float3(pxy.x, pxy.y, pzw.x);
     const float ninv = rsq(nxy.x * nxy.x + nxy.y * nxy.y + nzw.x * nzw.x);
-    const float3 N = make_float3(nxy.x * ninv, nxy.y * ninv, nzw.x * ninv);
+    s.N = make_float3(nxy.x * ninv, nxy.y * ninv, nzw.x * ninv);
     float cx = p.cx, cy = p.cy, cz = p.cz;
     if (BATCHED) { cx = __ldg(p.cams + 3 * ip.view); cy = __ldg(p.cams + 3 * ip.view + 1); cz = __ldg(p.cams + 3 * ip.view + 2); }
-    const float vx = cx - P.x, vy = cy - P.y, vz = cz - P.z;
+    const float vx = cx - s.P.x, vy = cy - s.P.y, vz = cz - s.P.z;
     const float vinv = rsq(vx * vx + vy * vy + vz * vz);
-    const float3 V = make_float3(vx * vinv, vy * vinv, vz * vinv);
-    const float NoVraw = N.x * V.x + N.y * V.y + N.z * V.z;
-    const float NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
+    s.V = make_float3(vx * vinv, vy * vinv, vz * vinv);
+    const float NoVraw = s.N.x * s.V.x + s.N.y * s.V.y + s.N.z * s.V.z;
+    s.NoV = fminf(fmaxf(NoVraw, 1e-4f), 1.0f);
     const float rough = fminf(fmaxf(float((to >> 8) & 0xFFu) * (1.0f / 255.0f), 0.045f), 1.0f);
     const float metal = float((to >> 16) & 0xFFu) * (1.0f / 255.0f), omm = 1.0f - metal;
-    float F0r, F0g, F0b, cdpr, cdpg, cdpb;
     {
       const uint2 ta = st.px[2][threadIdx.x];
       const float base_r = unorm16_lo(ta.x), base_g = unorm16_hi(ta.x), base_b = unorm16_lo(ta.y);
-      F0r = 0.04f * omm + base_r * metal; F0g = 0.04f * omm + base_g * metal; F0b = 0.04f * omm + base_b * metal;
+      s.F0r = 0.04f * omm + base_r * metal; s.F0g = 0.04f * omm + base_g * metal; s.F0b = 0.04f * omm + base_b * metal;
       const float cdr = base_r * omm, cdg = base_g * omm, cdb = base_b * omm;
-      cdpr = cdr * kInvPi; cdpg = cdg * kInvPi; cdpb = cdb * kInvPi;
+      s.cdpr = cdr * kInvPi; s.cdpg = cdg * kInvPi; s.cdpb = cdb * kInvPi;
       s_amb[2][threadIdx.x] = make_float4(0.f, cdr, cdg, cdb);
     }
     const float alpha = rough * rough;
-    const float a2 = alpha * alpha, oma2 = 1.0f - a2;
-    const float vv = NoV * NoV * oma2 + a2;
-    const float visV = vv * rsq(vv);
-    const float omF0r = 1.0f - F0r, omF0g = 1.0f - F0g, omF0b = 1.0f - F0b;
-    const float a2h = a2 * (0.5f * kInvPi);
+    s.a2 = alpha * alpha; s.oma2 = 1.0f - s.a2;
+    const float vv = s.NoV * s.NoV * s.oma2 + s.a2;
+    s.visV = vv * rsq(vv);
+    s.omF0r = 1.0f - s.F0r; s.omF0g = 1.0f - s.F0g; s.omF0b = 1.0f - s.F0b;
+    s.a2h = s.a2 * (0.5f * kInvPi);
 
     // ---- ambient set-up: the four footprint records are loaded here and consumed after the light loop ----
     Quad6 qi, q0, q1;
     Quad8 ql;
     if (p.has_ibl) {
-      const float3 Rv = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
-      const IblTaps taps = make_ibl_taps(p, N, Rv, NoV, rough);
+      const float3 Rv = make_float3(2.0f * NoVraw * s.N.x - s.V.x, 2.0f * NoVraw * s.N.y - s.V.y, 2.0f * NoVraw * s.N.z - s.V.z);
+      const IblTaps taps = make_ibl_taps(p, s.N, Rv, s.NoV, rough);
       q0 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p0));
       q1 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p1));
       qi = ldg_rec256(p.q_irr + 2 * size_t(taps.i_irr));
@@ -524,45 +545,13 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
 
     // ---- direct lighting: four lights per iteration as two independent packed chains ----
     f2 dr2 = dup(0.f), dg2 = dr2, db2 = dr2;
-    auto pair_a = [&](const float4 l0, const float4 l1) {
-      PairA a;
-      a.dx = sub2(pk(l0.x, l0.y), dup(P.x)); a.dy = sub2(pk(l0.z, l0.w), dup(P.y)); a.dz = sub2(pk(l1.x, l1.y), dup(P.z));
-      const f2 d2 = max2(fma2(a.dz, a.dz, fma2(a.dy, a.dy, mul2(a.dx, a.dx))), 1e-8f);
-      a.invd = map2(d2, rsq);
-      a.NoL = sat2(mul2(fma2(dup(N.z), a.dz, fma2(dup(N.y), a.dy, mul2(dup(N.x), a.dx))), a.invd));
-      const f2 qq = mul2(d2, pk(l1.z, l1.w));               // (d/range)^2; 0 for unlimited range
-      const f2 win = sat2(sub2(one, mul2(qq, qq)));         // clamp(1 - (d/range)^4, 0, 1)
-      a.w = mul2(mul2(mul2(a.invd, a.invd), win), a.NoL);   // inverse square * window * N.L
-      return a;
-    };
-    // radiance factor of a pair per channel: (1 - F) c_diff/pi + F D Vis = c_diff/pi + F (D Vis - c_diff/pi); the
-    // formulas are shade_ggx_kernel's (see the comments there)
-    auto pair_b = [&](const PairA& a, f2& br, f2& bg, f2& bb) {
-      const f2 hx = fma2(a.dx, a.invd, dup(V.x)), hy = fma2(a.dy, a.invd, dup(V.y)), hz = fma2(a.dz, a.invd, dup(V.z));
-      const f2 hh = max2(fma2(hz, hz, fma2(hy, hy, mul2(hx, hx))), 1e-12f);
-      const f2 nhinv = map2(hh, [](float v) { return -rsq(v); });
-      const f2 VoH = mul2(mul2(hh, nhinv), dup(-0.5f));
-      const f2 ex = fma2(hx, nhinv, dup(N.x)), ey = fma2(hy, nhinv, dup(N.y)), ez = fma2(hz, nhinv, dup(N.z));
-      const f2 sq = fma2(ez, ez, fma2(ey, ey, mul2(ex, ex)));
-      const f2 u = fma2(mul2(sq, sq), dup(-0.25f), sq);
-      const f2 ddn = fma2(u, dup(oma2), dup(a2));
-      const f2 dd = pk(lo(sq) > 2.0f ? lo(u) : lo(ddn), hi(sq) > 2.0f ? hi(u) : hi(ddn));
-      const f2 vl = fma2(mul2(a.NoL, a.NoL), dup(oma2), dup(a2));
-      const f2 den = fma2(dup(NoV), mul2(vl, map2(vl, rsq)), mul2(a.NoL, dup(visV)));
-      const f2 dv = mul2(dup(a2h), map2(mul2(mul2(dd, dd), den), rcp));
-      const f2 t = sub2(one, VoH), t2 = mul2(t, t), fc = mul2(mul2(t2, t2), t);
-      const f2 Fr = fma2(dup(omF0r), fc, dup(F0r)), Fg = fma2(dup(omF0g), fc, dup(F0g)), Fb = fma2(dup(omF0b), fc, dup(F0b));
-      br = fma2(Fr, sub2(dv, dup(cdpr)), dup(cdpr));
-      bg = fma2(Fg, sub2(dv, dup(cdpg)), dup(cdpg));
-      bb = fma2(Fb, sub2(dv, dup(cdpb)), dup(cdpb));
-    };
     for (uint32_t it = 0; it < quads; ++it) {
       const float4* lp = s_lp + 4 * it;
-      const PairA a = pair_a(lp[0], lp[1]), b = pair_a(lp[2], lp[3]);
+      const PairA a = light_pair_a(s, lp[0], lp[1]), b = light_pair_a(s, lp[2], lp[3]);
       if (fmaxf(fmaxf(lo(a.w), hi(a.w)), fmaxf(lo(b.w), hi(b.w))) > 0.0f) {
         f2 ar, ag, ab, br, bg, bb;
-        pair_b(a, ar, ag, ab);
-        pair_b(b, br, bg, bb);
+        light_pair_b(s, a, ar, ag, ab);
+        light_pair_b(s, b, br, bg, bb);
         const float4* lc = s_lc + 4 * it;
         const float4 c0 = lc[0], c1 = lc[1], c2 = lc[2], c3 = lc[3];
         // the pairs are added in list order: the same sums as shade_ggx_kernel's
@@ -582,9 +571,9 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
       pre.r = lerpf(pre.r, pr1.r, w2.x); pre.g = lerpf(pre.g, pr1.g, w2.x); pre.b = lerpf(pre.b, pr1.b, w2.x);
       const float2 sb = quad_bilinear_lut(ql, w1.z, w1.w);
       const float occ = float(st.orm[threadIdx.x] & 0xFFu) * (1.0f / 255.0f);
-      ar = (irr.r * w2.y + pre.r * (F0r * sb.x + sb.y)) * occ;
-      ag = (irr.g * w2.z + pre.g * (F0g * sb.x + sb.y)) * occ;
-      ab = (irr.b * w2.w + pre.b * (F0b * sb.x + sb.y)) * occ;
+      ar = (irr.r * w2.y + pre.r * (s.F0r * sb.x + sb.y)) * occ;
+      ag = (irr.g * w2.z + pre.g * (s.F0g * sb.x + sb.y)) * occ;
+      ab = (irr.b * w2.w + pre.b * (s.F0b * sb.x + sb.y)) * occ;
     }
     const uint2 te = st.px[3][threadIdx.x];
     const float2 exy = h2_to_f2(te.x), ezw = h2_to_f2(te.y);
