@@ -206,7 +206,12 @@ int pbrcu_ibl_cube_mipgen(pbrcu_ctx* ctx, void* chain_dev, uint32_t base_res, ui
  * 8-texel footprint), so the texture copy carries a contrast flag and every sample whose footprint
  * spans more than 25 % falls back to fp32-weight software filtering: the result is within 1.5e-3
  * relative of the exact filter.  exact != 0 turns the texture unit off altogether (fp32 weights for
- * every sample, about 3x slower on a smooth environment). */
+ * every sample, about 4x slower on a smooth environment).
+ * The switch also covers K3's default path (ibl->accel set, one light list): there the two SMOOTH maps
+ * of the ambient term -- irradiance and the split-sum LUT -- are fetched through the texture unit (the
+ * irradiance copy carries the same kind of flag at 12 % footprint range with the record as fallback;
+ * within 5e-4 relative of the fp32-weight filter), the prefiltered cube always from the fp32-weight
+ * footprint records; exact != 0 takes all four taps from the records. */
 int pbrcu_ibl_set_exact_filtering(pbrcu_ctx* ctx, int exact);
 /* K3 (when ibl->accel is set): on != 0 fetches the prefiltered and irradiance cubes through the texture
  * unit (one TEX each; flagged copies, 12 % footprint range -> within 7e-4 relative of the fp32-weight

@@ -51,6 +51,8 @@ extern "C" int pbrcu_ibl_accel_free(pbrcu_ctx* ctx, pbrcu_ibl_accel* a) {
   if (a->lut) cudaFree(a->lut);
   cube_tex_destroy(&a->pref_tex);
   cube_tex_destroy(&a->irr_tex);
+  if (a->lut_tex) cudaDestroyTextureObject(a->lut_tex);
+  if (a->lut_array) cudaFreeArray(a->lut_array);
   delete a;
   return PBRCU_OK;
 }
@@ -99,6 +101,29 @@ extern "C" int pbrcu_ibl_accel_build(pbrcu_ctx* ctx, const pbrcu_ibl* ibl, pbrcu
     return rc;
   }
   a->bytes += cube_tex_bytes(a->pref_tex) + cube_tex_bytes(a->irr_tex);
+  {
+    const cudaChannelFormatDesc fmt = cudaCreateChannelDesc<float2>();
+    cudaError_t e = cudaMallocArray(&a->lut_array, &fmt, ibl->lut_res, ibl->lut_res);
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DToArrayAsync(a->lut_array, 0, 0, ibl->lut, size_t(ibl->lut_res) * 8, size_t(ibl->lut_res) * 8, ibl->lut_res,
+                                   cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) {
+      cudaResourceDesc rd{};
+      rd.resType = cudaResourceTypeArray;
+      rd.res.array.array = a->lut_array;
+      cudaTextureDesc td{};
+      td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+      td.filterMode = cudaFilterModeLinear;
+      td.readMode = cudaReadModeElementType;
+      td.normalizedCoords = 1;
+      e = cudaCreateTextureObject(&a->lut_tex, &rd, &td, nullptr);
+    }
+    if (e != cudaSuccess) {
+      pbrcu_ibl_accel_free(ctx, a);
+      return cuda_fail(e, "LUT texture");
+    }
+    a->bytes += n_lut * 8;
+  }
   *out = a;
   return PBRCU_OK;
 }

@@ -18,6 +18,10 @@ struct pbrcu_ibl_accel {
   // the prefiltered chain and the irradiance map as flagged hardware textures (cube_tex.cuh): K3 takes
   // one TEX fetch per map and falls back to the records above where the filtered flag is set
   pbrcu::CubeTex pref_tex, irr_tex;
+  // the LUT as a bilinear, clamp-to-edge 2-D float2 texture (K3's single-list kernel: the LUT is smooth, the unit's
+  // 8-bit weights cost at most 1/512 of the texel-to-texel range)
+  cudaArray_t lut_array;
+  cudaTextureObject_t lut_tex;
   size_t bytes;
 };
 

@@ -46,6 +46,7 @@ struct ShadeParams {
   uint32_t lut_res;
   const uint4 *q_pref, *q_irr, *q_lut;  // footprint records (pbrcu_ibl_accel); NULL: plain textures
   cudaTextureObject_t t_pref, t_irr;    // flagged hardware textures of the same maps (IBL_TEX)
+  cudaTextureObject_t t_lut;            // the LUT as a bilinear float2 texture (shade_ggx_one_kernel<.., AMBTEX>)
   // batched multi-view (LIST_ONE_BATCHED): view v reads its planes view_stride8 / view_stride4 bytes after view
   // v - 1's, its camera from cams[3 v ..], and writes out_view_stride bytes after view v - 1's output
   uint32_t n_views;
@@ -328,8 +329,9 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
       if (IBL == IBL_TEX) {
         // face selection, clamp-to-edge bilinear on two levels and the level blend in the texture unit
         const float lod = fminf(rough * float(p.pref.nmips - 1), float(p.pref.nmips - 1));
-        tpre = texCubemapLod<float4>(p.t_pref, Rv.x, Rv.y, Rv.z, lod);
-        tirr = texCubemapLod<float4>(p.t_irr, N.x, N.y, N.z, 0.0f);
+        // (directions tilted by 2^-20 so that exact ties of the major axis go X, Y, Z like cube_dir_to_face_uv)
+        tpre = texCubemapLod<float4>(p.t_pref, Rv.x * 1.00000095f, Rv.y * 1.00000048f, Rv.z, lod);
+        tirr = texCubemapLod<float4>(p.t_irr, N.x * 1.00000095f, N.y * 1.00000048f, N.z, 0.0f);
         // a level fraction the unit would round to 1 hides the finer level's flags: treat it as flagged
         if (lod - floorf(lod) > 0.995f) tirr.w = 1.0f;
         tlut = make_tap(NoV, rough, int(p.lut_res));
@@ -435,7 +437,12 @@ __device__ __forceinline__ Quad6 ldg_rec256(const uint4* p) {
   return q;
 }
 
-template <bool BATCHED>
+// AMBTEX: the two SMOOTH maps of the ambient term -- irradiance (a cosine convolution) and the split-sum LUT -- come from the
+// otherwise idle texture unit: one TEX each (face selection and bilinear in hardware) instead of face / tap arithmetic, a
+// scattered 256-bit load and a 24-instruction filter.  The unit's 8-bit weights cost at most 1/512 of the footprint's value
+// range, which for these maps is a few 1e-5 relative; an irradiance footprint whose range exceeds 12 % (the flag in the
+// texture's alpha) is re-filtered from its record.  The prefiltered cube keeps fp32 weights from the records in every mode.
+template <bool BATCHED, bool AMBTEX>
 __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_kernel(const __grid_constant__ ShadeParams p) {
   __shared__ float4 s_lp[kLightChunk];
   __shared__ float4 s_lc[kLightChunk];
@@ -531,15 +538,26 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
     // ---- ambient set-up: the four footprint records are loaded here and consumed after the light loop ----
     Quad6 qi, q0, q1;
     Quad8 ql;
+    float4 tirr = make_float4(0.f, 0.f, 0.f, 0.f);
+    float2 tlut = make_float2(0.f, 0.f);
     if (p.has_ibl) {
       const float3 Rv = make_float3(2.0f * NoVraw * s.N.x - s.V.x, 2.0f * NoVraw * s.N.y - s.V.y, 2.0f * NoVraw * s.N.z - s.V.z);
-      const IblTaps taps = make_ibl_taps(p, s.N, Rv, s.NoV, rough);
+      const IblTaps taps = make_ibl_taps(p, s.N, Rv, s.NoV, rough);  // (the taps a mode does not use are dead code)
       q0 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p0));
       q1 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p1));
-      qi = ldg_rec256(p.q_irr + 2 * size_t(taps.i_irr));
-      ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
-      s_amb[0][threadIdx.x] = make_float4(taps.irr_tx, taps.irr_ty, taps.p0_tx, taps.p0_ty);
-      s_amb[1][threadIdx.x] = make_float4(taps.p1_tx, taps.p1_ty, taps.lut_tx, taps.lut_ty);
+      if (AMBTEX) {
+        // the unit's own face selection breaks exact ties of the major axis (fp16 normals do produce them) its own way, and
+        // without seamless filtering the two faces give different edge texels: tilt the direction by 2^-20 so that ties
+        // go X, then Y, then Z like cube_dir_to_face_uv (moves the tap by 1e-6 of the face)
+        tirr = texCubemapLod<float4>(p.t_irr, s.N.x * 1.00000095f, s.N.y * 1.00000048f, s.N.z, 0.0f);
+        tlut = tex2D<float2>(p.t_lut, s.NoV, rough);
+        s_amb[0][threadIdx.x] = make_float4(taps.p0_tx, taps.p0_ty, taps.p1_tx, taps.p1_ty);
+      } else {
+        qi = ldg_rec256(p.q_irr + 2 * size_t(taps.i_irr));
+        ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
+        s_amb[0][threadIdx.x] = make_float4(taps.irr_tx, taps.irr_ty, taps.p0_tx, taps.p0_ty);
+        s_amb[1][threadIdx.x] = make_float4(taps.p1_tx, taps.p1_ty, taps.lut_tx, taps.lut_ty);
+      }
       reinterpret_cast<float*>(&s_amb[2][threadIdx.x])[0] = taps.lod_f;
     }
 
@@ -564,12 +582,30 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
     // ---- ambient: split-sum image-based lighting (Karis 2013) ----
     float ar = 0.f, ag = 0.f, ab = 0.f;
     if (p.has_ibl) {
-      const float4 w0 = s_amb[0][threadIdx.x], w1 = s_amb[1][threadIdx.x], w2 = s_amb[2][threadIdx.x];
-      const RGB irr = quad_bilinear_rgb(qi, w0.x, w0.y);
-      RGB pre = quad_bilinear_rgb(q0, w0.z, w0.w);
-      const RGB pr1 = quad_bilinear_rgb(q1, w1.x, w1.y);
+      const float4 w0 = s_amb[0][threadIdx.x], w2 = s_amb[2][threadIdx.x];
+      RGB irr, pre, pr1;
+      float2 sb;
+      if (AMBTEX) {
+        pre = quad_bilinear_rgb(q0, w0.x, w0.y);
+        pr1 = quad_bilinear_rgb(q1, w0.z, w0.w);
+        irr = RGB{tirr.x, tirr.y, tirr.z};
+        sb = tlut;
+        if (tirr.w > 0.0f) {  // a flagged texel took part in the fetch: redo this tap with fp32 weights from its record
+          int face;
+          float u, v;
+          cube_dir_to_face_uv(s.N, face, u, v);
+          const int ires = int(p.irr.base_res);
+          const Tap a = make_tap(u, v, ires);
+          irr = quad_bilinear_rgb(ldg_rec256(p.q_irr + 2 * size_t(face * ires * ires + a.idx)), a.tx, a.ty);
+        }
+      } else {
+        const float4 w1 = s_amb[1][threadIdx.x];
+        irr = quad_bilinear_rgb(qi, w0.x, w0.y);
+        pre = quad_bilinear_rgb(q0, w0.z, w0.w);
+        pr1 = quad_bilinear_rgb(q1, w1.x, w1.y);
+        sb = quad_bilinear_lut(ql, w1.z, w1.w);
+      }
       pre.r = lerpf(pre.r, pr1.r, w2.x); pre.g = lerpf(pre.g, pr1.g, w2.x); pre.b = lerpf(pre.b, pr1.b, w2.x);
-      const float2 sb = quad_bilinear_lut(ql, w1.z, w1.w);
       const float occ = float(st.orm[threadIdx.x] & 0xFFu) * (1.0f / 255.0f);
       ar = (irr.r * w2.y + pre.r * (s.F0r * sb.x + sb.y)) * occ;
       ag = (irr.g * w2.z + pre.g * (s.F0g * sb.x + sb.y)) * occ;
@@ -741,7 +777,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
       PBRCU_REQUIRE(a->pref_res == ibl->pref_res && a->pref_mips == ibl->pref_mips && a->irr_res == ibl->irr_res && a->lut_res == ibl->lut_res,
                     "ibl->accel was built for textures of another shape");
       p.q_pref = a->pref; p.q_irr = a->irr; p.q_lut = a->lut;
-      p.t_pref = a->pref_tex.tex; p.t_irr = a->irr_tex.tex;
+      p.t_pref = a->pref_tex.tex; p.t_irr = a->irr_tex.tex; p.t_lut = a->lut_tex;
     }
   }
   p.ntx = (p.x1 + kTile - 1) / kTile - p.tx0;
@@ -756,8 +792,15 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   PBRCU_REQUIRE(n_views == 1 || one_list, "batched shading takes no tile lists and at most 128 lights");
   const int lists = n_views > 1 ? LIST_ONE_BATCHED : one_list ? LIST_ONE : LIST_TILED;
   if (!tex && lists != LIST_TILED && (p.q_pref || !p.has_ibl)) {  // one list, footprint records or no IBL
-    if (lists == LIST_ONE_BATCHED) shade_ggx_one_kernel<true><<<grid, kShadeThreads, 0, st>>>(p);
-    else shade_ggx_one_kernel<false><<<grid, kShadeThreads, 0, st>>>(p);
+    // irradiance and LUT through the texture unit unless the caller asked for fp32 weights everywhere
+    const bool ambtex = p.has_ibl && p.t_irr && p.t_lut && !ctx->exact_ibl_filter;
+    if (lists == LIST_ONE_BATCHED) {
+      if (ambtex) shade_ggx_one_kernel<true, true><<<grid, kShadeThreads, 0, st>>>(p);
+      else shade_ggx_one_kernel<true, false><<<grid, kShadeThreads, 0, st>>>(p);
+    } else {
+      if (ambtex) shade_ggx_one_kernel<false, true><<<grid, kShadeThreads, 0, st>>>(p);
+      else shade_ggx_one_kernel<false, false><<<grid, kShadeThreads, 0, st>>>(p);
+    }
     return launch_check("shade_ggx_one_kernel");
   }
   if (tex) launch_shade<IBL_TEX>(p, lists, grid, st);

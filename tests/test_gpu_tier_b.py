@@ -170,7 +170,8 @@ def test_shade_matches_oracle(pbr, dev, oracle, w, h, nl, use_ibl):
         ibl2 = make_ibl_struct(pbr, host, bufs, dev, accel=True)
         n_cube = oracle.chain_texels(host["pref_res"], host["pref_mips"]) + host["irr"].size // 4
         # 32-byte footprint records of the three maps + the flagged RGBA16F texture copies of the two cubes
-        assert dev.lib.ibl_accel_bytes(ibl2.accel) == 32 * (n_cube + host["lut"].size // 2) + 8 * n_cube
+        # ... and the LUT as a float2 texture
+        assert dev.lib.ibl_accel_bytes(ibl2.accel) == 32 * (n_cube + host["lut"].size // 2) + 8 * n_cube + 8 * (host["lut"].size // 2)
         out2 = dev.alloc(w * h * 8)
         # opt-in: texture-unit fetches (8-bit weights), fp32-weight records where the contrast flag is set
         dev.lib.shade_set_texture_unit(dev.ctx, 1)
@@ -178,9 +179,15 @@ def test_shade_matches_oracle(pbr, dev, oracle, w, h, nl, use_ibl):
         dev.sync()
         dev.lib.shade_set_texture_unit(dev.ctx, 0)
         assert_hdr_parity(out2.download((h, w, 4), np.uint16), want, peak=peak, rel_tol=REL, what=f"shade (texture unit) {w}x{h} nl={nl}")
-        # default: one 256-bit footprint-record load per bilinear tap, bit-identical to the plain path
+        # default: prefiltered taps from footprint records (fp32 weights), irradiance and LUT through the texture unit
         dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr if ld else None, nl, None, C.byref(ibl2), pbr.WHOLE, out2.ptr, w * 8, None)
         dev.sync()
+        assert_hdr_parity(out2.download((h, w, 4), np.uint16), want, peak=peak, rel_tol=REL, what=f"shade (records + texture unit) {w}x{h} nl={nl}")
+        # fp32 weights everywhere: one 256-bit footprint-record load per bilinear tap, bit-identical to the plain path
+        dev.lib.ibl_set_exact_filtering(dev.ctx, 1)
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr if ld else None, nl, None, C.byref(ibl2), pbr.WHOLE, out2.ptr, w * 8, None)
+        dev.sync()
+        dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
         got2 = out2.download((h, w, 4), np.uint16)
         assert np.array_equal(got2, got), f"record path differs from the plain path in {np.count_nonzero(got2 != got)} values"
         dev.lib.ibl_accel_free(dev.ctx, ibl2.accel)
@@ -213,6 +220,35 @@ def test_shade_single_list_kernel_light_counts_and_ragged_rect(pbr, dev, oracle,
     outside[y0:y0 + rh, x0:x0 + rw] = False
     assert (got[outside] == 0x7B7B).all(), "texels outside the rect were written"
     assert (got[y0:y0 + rh, x0:x0 + rw][g["bg"][y0:y0 + rh, x0:x0 + rw]] == 0).all()
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+
+
+def test_shade_default_path_on_cube_face_ties(pbr, dev, oracle):
+    """fp16 normals do hit exact ties of the major axis (|x| == |y| ...).  The texture unit breaks them its own way and, without
+    seamless filtering, the two faces return different edge texels; the default path (irradiance through the unit) must still
+    pick the face the oracle picks (X, then Y, then Z)."""
+    host, bufs = build_ibl(dev, oracle)
+    w, h = 64, 48
+    g = synth_gbuffer(w, h, seed=77, tier_b=True)
+    ties = np.array([[1, 1, 0.3], [1, -1, 0.2], [-1, 1, -0.4], [0.5, 0.2, 0.5], [-0.5, 0.1, 0.5], [0.3, 0.7, 0.7], [0.2, -0.7, 0.7],
+                     [1, 1, 1], [-1, -1, -1], [1, 0, 1], [0, 1, 1], [1, 1, 0]], np.float32)
+    nrm = np.asarray(g["nrm"], np.float32).copy()
+    lit = ~g["bg"]
+    ys, xs = np.nonzero(lit)
+    for k, (y, x) in enumerate(zip(ys, xs)):
+        nrm[y, x, :3] = ties[k % len(ties)] * (0.25 + 0.125 * (k % 5))  # un-normalised on purpose: the kernels normalise
+    g["nrm"] = nrm.astype(np.float16)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    lights = synth_lights(4, seed=3)
+    ld = dev.upload(lights)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    cam = (0.5, -1.0, 12.0)
+    out = dev.alloc(w * h * 8)
+    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr, 4, None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
+    dev.sync()
+    got = out.download((h, w, 4), np.uint16)
+    _, want = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, lights, host)
+    assert_hdr_parity(got, want, peak=float(max(f16(want).max(), 1.0)), rel_tol=REL, what="default path on face ties")
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
 
 
