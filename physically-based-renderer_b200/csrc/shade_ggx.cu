@@ -65,6 +65,8 @@ enum : int {
 enum : int {
   IBL_PLAIN = 0,    // four 8-byte loads per bilinear tap from the plain chains, fp32 weights
   IBL_RECORDS = 1,  // one 256-bit footprint-record load per tap, fp32 weights (bit-identical to IBL_PLAIN)
+  IBL_RECORDS_AMBTEX = 3,  // IBL_RECORDS for the prefiltered cube; the two smooth maps -- irradiance (flagged copy, record
+                           // fallback) and the LUT -- through the texture unit (see shade_ggx_one_kernel)
   IBL_TEX = 2       // texture unit for the prefiltered and irradiance cubes (8-bit weights), records where
                     // the filtered contrast flag is set and for the LUT
 };
@@ -319,12 +321,18 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     float3 Rv = make_float3(0.f, 0.f, 0.f);
     if (lit && p.has_ibl) {
       Rv = make_float3(2.0f * NoVraw * N.x - V.x, 2.0f * NoVraw * N.y - V.y, 2.0f * NoVraw * N.z - V.z);
-      if (IBL == IBL_RECORDS) {
+      if (IBL == IBL_RECORDS || IBL == IBL_RECORDS_AMBTEX) {
         taps = make_ibl_taps(p, N, Rv, NoV, rough);
         q0 = ldg_rec(p.q_pref + 2 * size_t(taps.i_p0));
         q1 = ldg_rec(p.q_pref + 2 * size_t(taps.i_p1));
-        qi = ldg_rec(p.q_irr + 2 * size_t(taps.i_irr));
-        ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
+        if (IBL == IBL_RECORDS) {
+          qi = ldg_rec(p.q_irr + 2 * size_t(taps.i_irr));
+          ql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
+        } else {
+          tirr = texCubemapLod<float4>(p.t_irr, N.x * 1.00000095f, N.y * 1.00000048f, N.z, 0.0f);  // tilt: see below
+          const float2 l = tex2D<float2>(p.t_lut, NoV, rough);
+          tpre.x = l.x; tpre.y = l.y;
+        }
       }
       if (IBL == IBL_TEX) {
         // face selection, clamp-to-edge bilinear on two levels and the level blend in the texture unit
@@ -381,12 +389,21 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     if (p.has_ibl) {
       RGB irr, pre;
       float2 sb;
-      if (IBL == IBL_RECORDS) {
-        irr = quad_bilinear_rgb(qi, taps.irr_tx, taps.irr_ty);
+      if (IBL == IBL_RECORDS || IBL == IBL_RECORDS_AMBTEX) {
         pre = quad_bilinear_rgb(q0, taps.p0_tx, taps.p0_ty);
         const RGB pr1 = quad_bilinear_rgb(q1, taps.p1_tx, taps.p1_ty);
         pre.r = lerpf(pre.r, pr1.r, taps.lod_f); pre.g = lerpf(pre.g, pr1.g, taps.lod_f); pre.b = lerpf(pre.b, pr1.b, taps.lod_f);
-        sb = quad_bilinear_lut(ql, taps.lut_tx, taps.lut_ty);
+        if (IBL == IBL_RECORDS) {
+          irr = quad_bilinear_rgb(qi, taps.irr_tx, taps.irr_ty);
+          sb = quad_bilinear_lut(ql, taps.lut_tx, taps.lut_ty);
+        } else {
+          irr = RGB{tirr.x, tirr.y, tirr.z};
+          sb = make_float2(tpre.x, tpre.y);
+          if (tirr.w > 0.0f) {  // flagged footprint: fp32 weights from the record
+            qi = ldg_rec(p.q_irr + 2 * size_t(taps.i_irr));
+            irr = quad_bilinear_rgb(qi, taps.irr_tx, taps.irr_ty);
+          }
+        }
       } else if (IBL == IBL_TEX) {
         irr = RGB{tirr.x, tirr.y, tirr.z};
         pre = RGB{tpre.x, tpre.y, tpre.z};
@@ -804,6 +821,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
     return launch_check("shade_ggx_one_kernel");
   }
   if (tex) launch_shade<IBL_TEX>(p, lists, grid, st);
+  else if (p.q_pref && p.t_irr && p.t_lut && !ctx->exact_ibl_filter) launch_shade<IBL_RECORDS_AMBTEX>(p, lists, grid, st);
   else if (p.q_pref) launch_shade<IBL_RECORDS>(p, lists, grid, st);
   else launch_shade<IBL_PLAIN>(p, lists, grid, st);
   return launch_check("shade_ggx_kernel");
