@@ -40,9 +40,9 @@ N_LIGHTS = 4
 B_PER_PX_K3 = 44   # 36 read (pos 8 + nrm 8 + albedo 8 + emissive 8 + orm 4) + 8 written
 B_PER_PX_K1 = 32   # 24 read + 8 written
 # dram__bytes_read.sum + dram__bytes_write.sum of one shade_ggx_one_kernel launch on this workload, from the committed
-# `ncu --set full` capture (profiles/r01_k3_one_kernel_ncu.txt): 523.1 MB + 61.0 MB; the 219 MB above the
+# `ncu --set full` capture (profiles/r01_k3_one_kernel_ncu.txt): 516.9 MB + 62.2 MB; the 214 MB above the
 # algorithmic 365 MB are the IBL footprint records and write-allocate traffic
-K3_DRAM_TRAFFIC_BYTES = 584.1e6
+K3_DRAM_TRAFFIC_BYTES = 579.2e6
 ENV_W, ENV_H = 4096, 2048
 CUBE_RES, CUBE_MIPS, IBL_SAMPLES, IRR_RES, LUT_RES = 2048, 12, 1024, 64, 512
 CAM = (0.0, -1.0, -12.0)
