@@ -437,11 +437,11 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
 }
 
 // ---- K3, single-list form (LIST_ONE / LIST_ONE_BATCHED with footprint records or no IBL) ----
-// Same arithmetic as shade_ggx_kernel, laid out for the two things ncu showed to bound it (profiles/r01_k3_*):
+// Same arithmetic as shade_ggx_kernel, laid out for what ncu showed to bound it (profiles/r01_k3_*):
 //  * dependent-issue latency: the packed light chain is ONE dependency chain per thread, and 5 warps per scheduler do
 //    not cover it.  Here two light pairs (four lights) are evaluated side by side, so the scheduler always has a
 //    second independent chain of the same warp to issue from;
-//  * L1 tag bandwidth: every record is fetched with ONE 256-bit load (one tag look-up per lane instead of two).
+//  * every record is fetched with ONE 256-bit load (one request per lane instead of two).
 // Registers for both come from deferring everything only the ambient term needs (tap weights, c_diff, occlusion,
 // emissive, alpha) to shared memory: a small per-thread stash, and the staged tile itself, which stays valid for the
 // whole iteration.  Unlit and outside pixels leave the iteration early instead of carrying neutral values through it.
@@ -456,9 +456,9 @@ __device__ __forceinline__ Quad6 ldg_rec256(const uint4* p) {
 
 // AMBTEX: the two SMOOTH maps of the ambient term -- irradiance (a cosine convolution) and the split-sum LUT -- come from the
 // otherwise idle texture unit: one TEX each (face selection and bilinear in hardware) instead of face / tap arithmetic, a
-// scattered 256-bit load and a 24-instruction filter.  The unit's 8-bit weights cost at most 1/512 of the footprint's value
-// range, which for these maps is a few 1e-5 relative; an irradiance footprint whose range exceeds 12 % (the flag in the
-// texture's alpha) is re-filtered from its record.  The prefiltered cube keeps fp32 weights from the records in every mode.
+// scattered 256-bit load and a 24-instruction filter.  The unit's 8-bit weights cost at most 2/512 of the footprint's value
+// range; an irradiance footprint whose range exceeds 12 % of its minimum (the flag in the texture's alpha; error below
+// 4.7e-4 relative otherwise) is re-filtered from its record.  The prefiltered cube keeps fp32 weights from the records in every mode.
 template <bool BATCHED, bool AMBTEX>
 __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_kernel(const __grid_constant__ ShadeParams p) {
   __shared__ float4 s_lp[kLightChunk];
