@@ -412,3 +412,66 @@ def test_cluster_lights_on_a_row_band_equals_the_whole_frame(pbr, dev, oracle):
         for tx in range(whole.tiles_x):
             assert np.array_equal(iw[ty, tx, :cw[ty, tx]], ip[ty, tx, :cw[ty, tx]])
     dev.lib.light_tiles_free(dev.ctx, C.byref(whole)); dev.lib.light_tiles_free(dev.ctx, C.byref(part))
+
+
+def _plane(pbr, dev, ptr, nbytes):
+    b = pbr.DeviceBuffer.__new__(pbr.DeviceBuffer)
+    b.dev, b.nbytes, b.ptr = dev, nbytes, ptr
+    return b
+
+
+def test_shade_full_size_properties(pbr, dev, oracle):
+    """BASELINE shapes for K3 through size-independent properties, on device-generated gbuf_spheres:
+    3840x2160 with 4 lights + IBL: cleared texels -> exactly 0, finite everywhere, the 8 row bands of the multi-GPU
+    partition == the whole frame bit for bit, 4096 random texels vs the oracle run on the very bits the device generated;
+    7680x4320 with 256 ranged lights: clustered lists == brute force (<= 1 fp16 ulp), row bands == whole frame bit for bit,
+    and the same random-sample check."""
+    host, bufs = build_ibl(dev, oracle)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    cam = (0.0, -1.0, -12.0)
+    rng = np.random.default_rng(11)
+    for (w, h, nl, ranged) in [(3840, 2160, 4, False), (7680, 4320, 256, True)]:
+        gb = pbr.GBuffer()
+        dev.lib.gbuffer_alloc(dev.ctx, w, h, 1, C.byref(gb))
+        dev.lib.synth_gbuffer(dev.ctx, C.byref(gb), 1, 0x5EED0002, pbr.f3(*cam), pbr.f3(0, 0, 0), None)
+        lights = synth_lights(nl, seed=2, ranged=ranged)
+        ld = dev.upload(lights)
+        pitch = gb.pitch8
+        out = dev.alloc(pitch * h); out2 = dev.alloc(pitch * h)
+        tiles = None
+        if ranged:
+            tiles = pbr.LightTiles()
+            dev.lib.light_tiles_alloc(dev.ctx, w, h, 256, C.byref(tiles))
+            dev.lib.cluster_lights(dev.ctx, C.byref(gb), ld.ptr, nl, C.byref(tiles), None)
+        tp = C.byref(tiles) if tiles else None
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr, nl, tp, C.byref(ibl), pbr.WHOLE, out.ptr, pitch, None)
+        bands = 8
+        for r in range(bands):  # 16-row aligned bands, like partition.row_band
+            y0, y1 = (r * h // bands) // 16 * 16, ((r + 1) * h // bands) // 16 * 16 if r + 1 < bands else h
+            dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr, nl, tp, C.byref(ibl), pbr.Rect(0, y0, w, y1 - y0), out2.ptr, pitch, None)
+        dev.sync()
+        a = out.download((h, w, 4), np.uint16); b = out2.download((h, w, 4), np.uint16)
+        assert np.array_equal(a, b), f"{w}x{h}: row-band result differs from the whole-frame result"
+        if ranged:  # brute force over all 256 lights
+            dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ld.ptr, nl, None, C.byref(ibl), pbr.WHOLE, out2.ptr, pitch, None)
+            dev.sync()
+            b = out2.download((h, w, 4), np.uint16)
+            assert (np.abs(a.astype(np.int32) - b.astype(np.int32)) <= 1).all(), "clustered light lists changed the result"
+        planes = {k: _plane(pbr, dev, getattr(gb, k), (pitch if k != "orm" else gb.pitch4) * h) for k in ("positions", "normals", "albedo", "orm", "emissive")}
+        N = planes["normals"].download((h, w, 4), np.uint16)
+        bg = (N[..., :3] == 0).all(-1)
+        assert 0.02 < bg.mean() < 0.9
+        assert (a[bg] == 0).all()
+        assert np.isfinite(f16(a)).all()
+        ys, xs = rng.integers(0, h, 4096), rng.integers(0, w, 4096)
+        P = planes["positions"].download((h, w, 4), np.uint16)[ys, xs][None]
+        A = planes["albedo"].download((h, w, 4), np.uint16)[ys, xs][None]
+        E = planes["emissive"].download((h, w, 4), np.uint16)[ys, xs][None]
+        O = planes["orm"].download((h, w, 4), np.uint8)[ys, xs][None]
+        _, want = oracle.shade(P.view(np.float16), N[ys, xs][None].view(np.float16), A, O, E.view(np.float16), cam, lights, host)
+        assert_hdr_parity(a[ys, xs][None], want, peak=float(max(f16(want).max(), 1.0)), rel_tol=REL, what=f"{w}x{h} sample")
+        if tiles:
+            dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
+        out.free(); out2.free(); ld.free()
+        dev.lib.gbuffer_free(dev.ctx, C.byref(gb))
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
