@@ -475,3 +475,48 @@ def test_shade_full_size_properties(pbr, dev, oracle):
         out.free(); out2.free(); ld.free()
         dev.lib.gbuffer_free(dev.ctx, C.byref(gb))
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+
+
+def test_prefilter_full_size_properties(dev, oracle):
+    """BASELINE configs[2] (2048^2 cube, 12 mips, 1024 samples per texel) through size-independent properties:
+    level 0 is an exact copy; 2 and 8 row-block shards reproduce the unsharded chain bit for bit; the texture-unit result is
+    within tolerance of the fp32-weight result on every texel of every level; a few texels per level vs the oracle."""
+    res, nmips, ns = 2048, 12, 1024
+    n = oracle.chain_texels(res, nmips)
+    env = synth_environment(512, 256, 7)
+    src = dev.upload(env)
+    chain_d = dev.alloc(n * 8)
+    dev.lib.ibl_equirect_to_cube(dev.ctx, src.ptr, 512, 256, res, chain_d.ptr, None)
+    dev.lib.ibl_cube_mipgen(dev.ctx, chain_d.ptr, res, nmips, None)
+    whole = dev.alloc(n * 8); part = dev.alloc(n * 8); exact_d = dev.alloc(n * 8)
+    dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, whole.ptr, 0, nmips - 1, 0, 1, None)
+    dev.sync()
+    chain = chain_d.download((n, 4), np.uint16)
+    want = whole.download((n, 4), np.uint16)
+    assert np.array_equal(want[: 6 * res * res], chain[: 6 * res * res]), "level 0 (roughness 0) must be a copy"
+    for nshards in (2, 8):
+        part.zero()
+        for s in range(nshards):
+            dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, part.ptr, 0, nmips - 1, s, nshards, None)
+        dev.sync()
+        got = part.download((n, 4), np.uint16)
+        assert np.array_equal(got, want), f"{nshards} shards: {np.count_nonzero(got != want)} values differ"
+    dev.lib.ibl_set_exact_filtering(dev.ctx, 1)
+    dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, exact_d.ptr, 0, nmips - 1, 0, 1, None)
+    dev.sync()
+    dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+    ex = exact_d.download((n, 4), np.uint16)
+    a = oracle.mip_offset(res, 1)
+    fe, fw = f16(ex[a:])[:, :3], f16(want[a:])[:, :3]
+    assert (np.abs(fw - fe) <= 1e-3 + REL * np.abs(fe)).all(), "texture-unit prefilter outside the tolerance of the fp32-weight one"
+    rng = np.random.default_rng(5)
+    for m in range(1, nmips):
+        r = res >> m
+        off = oracle.mip_offset(res, m)
+        for _ in range(6):
+            f, x, y = int(rng.integers(6)), int(rng.integers(r)), int(rng.integers(r))
+            ref = oracle.prefilter_texel(chain, res, nmips, m, ns, f, x, y)[:3]
+            got = f16(want[off + (f * r + y) * r + x])[:3]
+            assert (np.abs(got - ref) <= 1e-3 + REL * np.abs(ref)).all(), (m, f, x, y, got, ref)
+    for b in (src, chain_d, whole, part, exact_d):
+        b.free()
