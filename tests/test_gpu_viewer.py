@@ -89,9 +89,11 @@ def check_frame(oracle, d, draws, W, H):
     return covered, eye, per_draw, ldr
 
 
-def test_viewer_single_frame_matches_oracle(viewer, oracle, tmp_path):
+@pytest.mark.parametrize("W,H", [(200, 120), (1024, 1024)], ids=["200x120", "baseline-config0-1024x1024"])
+def test_viewer_single_frame_matches_oracle(viewer, oracle, tmp_path, W, H):
+    """One headless frame of a glTF through the viewer; 1024x1024 is BASELINE configs[0] (the lavapipe run it names is
+    unavailable on this box: the checker is the oracle's geometry pass + the reference-pinned lighting / tonemap)."""
     path, draws = asset(tmp_path)
-    W, H = 200, 120
     r = subprocess.run([viewer, str(path), "-vulkan-validation", "--size", f"{W}x{H}", "--frames", "1", "--dt", "0", "--no-spin", "--position", "1,-2,-9", "--yaw", "1.6",
                         "--pitch", "0.2", "--fov", "1.2", "--dump", str(tmp_path), "--out", str(tmp_path / "frame.png"), "--hdr", str(tmp_path / "frame.pfm")],
                        capture_output=True, text=True)
@@ -104,7 +106,8 @@ def test_viewer_single_frame_matches_oracle(viewer, oracle, tmp_path):
     assert dec.returncode == 0 and dec.stdout.split() == [str(W), str(H)]
     assert np.array_equal(np.fromfile(tmp_path / "frame.rgba", np.uint8).reshape(H, W, 4), ldr)
     pfm = (tmp_path / "frame.pfm").read_bytes()
-    assert pfm.startswith(b"PF\n200 120\n-1.0\n") and len(pfm) == len(b"PF\n200 120\n-1.0\n") + W * H * 12
+    head = f"PF\n{W} {H}\n-1.0\n".encode()
+    assert pfm.startswith(head) and len(pfm) == len(head) + W * H * 12
 
 
 def test_viewer_frame_loop_moves_camera_and_spins_nodes(viewer, oracle, tmp_path):
