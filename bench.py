@@ -249,6 +249,7 @@ def extra_configs(scene, torch, dist, world, rank):
     tiles = pbr.LightTiles()
     lib.light_tiles_alloc(ctx, W8, H8, NL, C.byref(tiles))
     y0, y1 = row_band(H8, world, rank, align=16)
+    bands_all = [row_band(H8, world, r, align=16) for r in range(world)]
     if world > 1:
         # bands of equal COST, not equal height: one untimed whole-frame clustering stands in for "the previous frame's light
         # lists"; every rank derives the same cuts from the same counts (cost of a tile ~ 9 light-equivalents of fixed work +
@@ -258,7 +259,8 @@ def extra_configs(scene, torch, dist, world, rank):
         lib.memcpy_d2h(prev.ctypes.data, tiles.counts, prev.nbytes, scene.stream())
         torch.cuda.synchronize()
         row_costs = (9.0 + prev.reshape(tiles.tiles_y, tiles.tiles_x)).sum(axis=1)
-        y0, y1 = cost_balanced_bands(row_costs, H8, world)[rank]
+        bands_all = cost_balanced_bands(row_costs, H8, world)
+        y0, y1 = bands_all[rank]
     band = band_views(pbr, g, tiles, y0, y1)  # this rank's rows of the G-buffer and of the tile lists (pointer arithmetic only)
 
     def step8k(_):
@@ -269,6 +271,28 @@ def extra_configs(scene, torch, dist, world, rank):
                               hdr.data_ptr() + y0 * W8 * 8, W8 * 8, scene.stream())
 
     ms = timed(torch, dist, step8k, 5, 3)
+    gathered = None
+    if world > 1:
+        # north_star: "NCCL over NVLink is used only to gather the finished tiles": the same step followed by the exchange that
+        # leaves the whole HDR frame on every rank (one NCCL broadcast per band -- the cost-balanced bands differ in height)
+        def step8k_gather(i):
+            step8k(i)
+            for r, (b, e) in enumerate(bands_all):
+                if e > b:
+                    dist.broadcast(hdr[b * W8 * 8:e * W8 * 8], src=r)
+
+        ms_g = timed(torch, dist, step8k_gather, 5, 3)
+        # the gathered frame against the whole frame shaded on this rank alone (untimed)
+        whole = scene.buf(W8 * H8 * 8)
+        lib.cluster_lights(ctx, C.byref(g), lights.data_ptr(), NL, C.byref(tiles), scene.stream())
+        lib.shade_ggx_ibl(ctx, C.byref(g), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(tiles), C.byref(scene.ibl), pbr.WHOLE, whole.data_ptr(), W8 * 8, scene.stream())
+        torch.cuda.synchronize()
+        same = torch.tensor([int(torch.equal(whole, hdr))], device=hdr.device)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        gathered = {"ms_per_frame_with_gather": round(ms_g / 5, 4), "gather_bytes_per_frame": W8 * H8 * 8,
+                    "gathered_frame_equals_unsharded": bool(same.item())}
+        scene.keep = [t for t in scene.keep if t is not whole]
+        del whole
     # tile counts live in library-owned memory: copy this rank's out through the C ABI
     host_counts = np.empty(max(band.tiles.tiles_x * band.tiles.tiles_y, 1), np.uint32)
     lib.memcpy_d2h(host_counts.ctypes.data, band.tiles.counts, band.tiles.tiles_x * band.tiles.tiles_y * 4, scene.stream())
@@ -277,6 +301,8 @@ def extra_configs(scene, torch, dist, world, rank):
                                     "rows_per_rank": y1 - y0, "mean_lights_per_tile": round(float(host_counts.mean()), 2),
                                     "max_lights_per_tile": int(host_counts.max()), "scaling": "strong (cost-balanced row bands from the previous frame's light lists, no exchange)",
                                     "what": "pbrcu_cluster_lights + pbrcu_shade_ggx_ibl on the rank's row band, 256 point lights range U[2,6], IBL"}
+    if gathered:
+        out["config3_8k_256_lights"].update(gathered)
     lib.light_tiles_free(ctx, C.byref(tiles))
     # ---- config[4]: 256 views x 1080p, view blocks ----
     WV, HV, NV = 1920, 1080, 256
