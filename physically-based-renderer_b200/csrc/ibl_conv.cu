@@ -185,10 +185,12 @@ static int launch_conv(const pbrcu_ctx* ctx, ConvParams p, cudaStream_t s) {
 
 // ---- contrast flags for the texture-unit path ----
 // pass A: per-channel min / max over the 3x3 neighbourhood (clamped to the face) of every texel
-__global__ void __launch_bounds__(256) minmax3_kernel(const uint2* __restrict__ level, uint4* __restrict__ mm, int res, size_t n) {
-  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
-    const int x = int(i % res), y = int((i / res) % res);
-    const uint2* f = level + (i / (size_t(res) * res)) * size_t(res) * res;
+// (grid = (ceil(res / 32), ceil(res / 8), 6), block = 32 x 8: face, row and column straight from the indices)
+__global__ void __launch_bounds__(256) minmax3_kernel(const uint2* __restrict__ level, uint4* __restrict__ mm, int res) {
+  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (x < res && y < res) {
+    const size_t i = (size_t(blockIdx.z) * res + y) * res + x;
+    const uint2* f = level + size_t(blockIdx.z) * res * res;
     float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
     for (int dy = -1; dy <= 1; ++dy)
       for (int dx = -1; dx <= 1; ++dx) {
@@ -212,10 +214,11 @@ __device__ __forceinline__ void mm_merge(MinMax& a, const uint4* p) {
 // and the 3x3s of the 4x4 block of texels around its children hold the finer one.
 __global__ void __launch_bounds__(256) contrast_flags_kernel(const uint2* __restrict__ level, const uint4* __restrict__ mm,
                                                              const uint4* __restrict__ mm_up, const uint4* __restrict__ mm_down,
-                                                             uint2* __restrict__ out, int res, size_t n, float rel_range) {
-  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
-    const int x = int(i % res), y = int((i / res) % res);
-    const size_t face = i / (size_t(res) * res);
+                                                             uint2* __restrict__ out, int res, float rel_range) {
+  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (x < res && y < res) {
+    const size_t face = blockIdx.z;
+    const size_t i = (face * res + y) * res + x;
     MinMax a{{3.0e38f, 3.0e38f, 3.0e38f}, {-3.0e38f, -3.0e38f, -3.0e38f}};
     mm_merge(a, mm + i);
     if (mm_up != nullptr) {
@@ -279,16 +282,16 @@ int pbrcu::cube_tex_upload(pbrcu_ctx* ctx, CubeTex* t, const void* chain, uint32
   const uint2* src = static_cast<const uint2*>(chain);
   uint4* mm = static_cast<uint4*>(ctx->cube_mm);
   uint2* stage = static_cast<uint2*>(ctx->cube_stage);
-  auto blocks_for = [&](size_t n) { const size_t b = (n + 255) / 256; return unsigned(b < size_t(ctx->sm_count) * 16 ? b : size_t(ctx->sm_count) * 16); };
+  auto grid_of = [](size_t r) { return dim3(unsigned((r + 31) / 32), unsigned((r + 7) / 8), 6); };
   for (uint32_t m = 0; m < nmips; ++m) {
-    const size_t off = cube_mip_offset(base_res, m), r = base_res >> m, n = 6 * r * r;
-    minmax3_kernel<<<blocks_for(n), 256, 0, st>>>(src + off, mm + off, int(r), n);
+    const size_t off = cube_mip_offset(base_res, m), r = base_res >> m;
+    minmax3_kernel<<<grid_of(r), dim3(32, 8), 0, st>>>(src + off, mm + off, int(r));
   }
   if (int rc = launch_check("minmax3_kernel")) return rc;
   for (uint32_t m = 0; m < nmips; ++m) {
-    const size_t off = cube_mip_offset(base_res, m), r = base_res >> m, n = 6 * r * r;
-    contrast_flags_kernel<<<blocks_for(n), 256, 0, st>>>(src + off, mm + off, m + 1 < nmips ? mm + cube_mip_offset(base_res, m + 1) : nullptr,
-                                                          m > 0 && guard_coarser ? mm + cube_mip_offset(base_res, m - 1) : nullptr, stage + off, int(r), n, rel_range);
+    const size_t off = cube_mip_offset(base_res, m), r = base_res >> m;
+    contrast_flags_kernel<<<grid_of(r), dim3(32, 8), 0, st>>>(src + off, mm + off, m + 1 < nmips ? mm + cube_mip_offset(base_res, m + 1) : nullptr,
+                                                             m > 0 && guard_coarser ? mm + cube_mip_offset(base_res, m - 1) : nullptr, stage + off, int(r), rel_range);
   }
   if (int rc = launch_check("contrast_flags_kernel")) return rc;
   for (uint32_t m = 0; m < nmips; ++m) {

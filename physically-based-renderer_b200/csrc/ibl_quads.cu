@@ -11,11 +11,12 @@ constexpr float kShadeTexRelRange = 0.12f;
 
 // faces of one level: n = 6*res*res records (n_faces*res*res in general)
 template <bool CUBE>
-__global__ void __launch_bounds__(256) build_quads8_kernel(const uint2* __restrict__ src, uint4* __restrict__ dst, int res, size_t n) {
-  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
-    const int x = int(i % res);
-    const int y = int((i / res) % res);
-    const size_t face = i / (size_t(res) * res);
+// (grid = (ceil(res / 32), ceil(res / 8), faces), block = 32 x 8)
+__global__ void __launch_bounds__(256) build_quads8_kernel(const uint2* __restrict__ src, uint4* __restrict__ dst, int res) {
+  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (x < res && y < res) {
+    const size_t face = blockIdx.z;
+    const size_t i = (face * res + y) * res + x;
     const int x1 = min(x + 1, res - 1), y1 = min(y + 1, res - 1);
     const uint2* f = src + face * size_t(res) * res;
     const uint2 t00 = __ldg(f + size_t(y) * res + x), t10 = __ldg(f + size_t(y) * res + x1);
@@ -31,11 +32,10 @@ __global__ void __launch_bounds__(256) build_quads8_kernel(const uint2* __restri
 }
 
 static int build_level(const uint2* src, uint4* dst, int res, int faces, int sms, cudaStream_t st) {
-  const size_t n = size_t(faces) * res * res;
-  const size_t want = (n + 255) / 256;
-  const unsigned blocks = unsigned(want < size_t(sms) * 16 ? want : size_t(sms) * 16);
-  if (faces == 6) build_quads8_kernel<true><<<blocks, 256, 0, st>>>(src, dst, res, n);
-  else build_quads8_kernel<false><<<blocks, 256, 0, st>>>(src, dst, res, n);
+  (void)sms;
+  const dim3 grid(unsigned((res + 31) / 32), unsigned((res + 7) / 8), unsigned(faces));
+  if (faces == 6) build_quads8_kernel<true><<<grid, dim3(32, 8), 0, st>>>(src, dst, res);
+  else build_quads8_kernel<false><<<grid, dim3(32, 8), 0, st>>>(src, dst, res);
   return launch_check("build_quads8_kernel");
 }
 

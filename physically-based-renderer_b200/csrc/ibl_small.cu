@@ -63,7 +63,10 @@ __device__ __forceinline__ float4 equirect_fetch(const float4* src, int sw, int 
   const float x0f = floorf(fx), y0f = floorf(fy);
   const float tx = fx - x0f, ty = fy - y0f;
   int x0 = int(x0f), y0 = int(y0f), x1 = x0 + 1, y1 = y0 + 1;
-  x0 = ((x0 % sw) + sw) % sw; x1 = ((x1 % sw) + sw) % sw;
+  // u is in [0, 1]: x0 in [-1, sw], x1 in [0, sw + 1] -- wrap without a division
+  x0 = x0 < 0 ? x0 + sw : (x0 >= sw ? x0 - sw : x0);
+  x1 = x1 >= sw ? x1 - sw : x1;
+  x1 = x1 >= sw ? x1 - sw : x1;
   y0 = min(max(y0, 0), sh - 1); y1 = min(max(y1, 0), sh - 1);
   const float4 t00 = __ldg(src + size_t(y0) * sw + x0), t10 = __ldg(src + size_t(y0) * sw + x1);
   const float4 t01 = __ldg(src + size_t(y1) * sw + x0), t11 = __ldg(src + size_t(y1) * sw + x1);
@@ -75,26 +78,21 @@ __device__ __forceinline__ float4 equirect_fetch(const float4* src, int sw, int 
   return o;
 }
 
+// grid = (ceil(res / 32), ceil(res / 8), 6), block = 32 x 8: face, row and column straight from the indices
 __global__ void __launch_bounds__(256) equirect_to_cube_kernel(const float4* src, int sw, int sh, int res, uint2* out) {
-  const size_t total = size_t(6) * res * res;
-  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
-    const int x = int(i % res);
-    const int y = int((i / res) % res);
-    const int face = int(i / (size_t(res) * res));
-    const float4 c = equirect_fetch(src, sw, sh, normalize3(cube_texel_dir(face, x, y, res)));
-    stg_stream8(out + i, make_uint2(f2_to_h2(c.x, c.y), f2_to_h2(c.z, c.w)));
-  }
+  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y, face = blockIdx.z;
+  if (x >= res || y >= res) return;
+  const float4 c = equirect_fetch(src, sw, sh, normalize3(cube_texel_dir(face, x, y, res)));
+  stg_stream8(out + (size_t(face) * res + y) * res + x, make_uint2(f2_to_h2(c.x, c.y), f2_to_h2(c.z, c.w)));
 }
 
 // ---- K5: one level from the previous STORED level: ((t00 + t10) + (t01 + t11)) * 0.25, one RNE
 // rounding at the store (bit-exact contract: explicit non-contracted adds).
 __global__ void __launch_bounds__(256) cube_mip_kernel(const uint2* src, uint2* dst, int rd) {
   const int rs = rd * 2;
-  const size_t total = size_t(6) * rd * rd;
-  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
-    const int x = int(i % rd);
-    const int y = int((i / rd) % rd);
-    const int face = int(i / (size_t(rd) * rd));
+  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y, face = blockIdx.z;  // grid (rd/32, rd/8, 6), block 32 x 8
+  if (x < rd && y < rd) {
+    const size_t i = (size_t(face) * rd + y) * rd + x;
     const uint2* s0 = src + (size_t(face) * rs + 2 * y) * rs + 2 * x;
     // the two source texels of a row are 16 contiguous, 16-byte aligned bytes
     const uint4 r0 = *reinterpret_cast<const uint4*>(s0);
@@ -109,11 +107,6 @@ __global__ void __launch_bounds__(256) cube_mip_kernel(const uint2* src, uint2* 
   }
 }
 
-static uint32_t grid_for(const pbrcu_ctx* ctx, size_t items, int threads) {
-  size_t blocks = (items + threads - 1) / threads;
-  size_t cap = size_t(ctx->sm_count) * 8;
-  return uint32_t(blocks < cap ? (blocks ? blocks : 1) : cap);
-}
 
 }  // namespace pbrcu
 
@@ -144,8 +137,8 @@ extern "C" int pbrcu_ibl_equirect_to_cube(pbrcu_ctx* ctx, const float* src, uint
                                           void* out_base_dev, pbrcu_stream s) {
   PBRCU_REQUIRE(ctx && src && out_base_dev, "NULL argument");
   PBRCU_REQUIRE(sw > 0 && sh > 0 && res > 0, "empty extent");
-  const size_t total = size_t(6) * res * res;
-  equirect_to_cube_kernel<<<grid_for(ctx, total, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+  PBRCU_REQUIRE(res <= 65535u * 8u, "res too large");
+  equirect_to_cube_kernel<<<dim3((res + 31) / 32, (res + 7) / 8, 6), dim3(32, 8), 0, static_cast<cudaStream_t>(s)>>>(
       reinterpret_cast<const float4*>(src), int(sw), int(sh), int(res), static_cast<uint2*>(out_base_dev));
   return launch_check("equirect_to_cube_kernel");
 }
@@ -157,8 +150,7 @@ extern "C" int pbrcu_ibl_cube_mipgen(pbrcu_ctx* ctx, void* chain_dev, uint32_t b
   uint2* chain = static_cast<uint2*>(chain_dev);
   for (uint32_t m = 1; m < nmips; ++m) {
     const int rd = int(base_res >> m);
-    const size_t total = size_t(6) * rd * rd;
-    cube_mip_kernel<<<grid_for(ctx, total, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+    cube_mip_kernel<<<dim3(unsigned((rd + 31) / 32), unsigned((rd + 7) / 8), 6), dim3(32, 8), 0, static_cast<cudaStream_t>(s)>>>(
         chain + cube_mip_offset(base_res, m - 1), chain + cube_mip_offset(base_res, m), rd);
     if (int rc = launch_check("cube_mip_kernel")) return rc;
   }
