@@ -527,6 +527,17 @@ def cpu_sample(scene, torch, budget_s=12.0):
             "sample": f"{reps} passes over {rows} rows x {W4K} px of the 4K frame, {N_LIGHTS} lights + IBL, oracle/pbr_oracle_ibl.c, {dt * reps:.1f} s of CPU work"}, parity
 
 
+def bind_near_gpu(torch, local):
+    """Pins this rank to the NUMA node of its GPU (`partition.bind_host_near_device`); a no-op on one node."""
+    from pbr_b200 import partition as part
+    pr = torch.cuda.get_device_properties(local)
+    try:
+        bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+    except AttributeError:
+        return {"bound": False, "why_not": "torch does not report the PCI address"}
+    return part.bind_host_near_device(bus)
+
+
 def main_ours(args):
     import torch
     import pbr_b200 as pbr
@@ -536,6 +547,7 @@ def main_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dist = None
     torch.cuda.set_device(local)
+    host_placement = bind_near_gpu(torch, local)  # before any pinned allocation: first touch decides the node
     if world > 1:
         import torch.distributed as dist_mod
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -582,7 +594,8 @@ def main_ours(args):
                          "algorithmic_bytes_per_launch": B_PER_PX_K3 * px_step, "peak_source": peak_src,
                          "kernel": "shade_ggx_one_kernel", "algorithmic_bytes_per_px": B_PER_PX_K3},
             "e2e": {"value": round(e2e_value, 1), "unit": "Mpix/s", "h2d_bytes_per_step": px_step * 36,
-                    "d2h_bytes_per_step": px_step * 8, "steps": e2e_steps, "api": "pbrcu_shade_frame_host (pinned host planes, 8 pipelined row bands)"},
+                    "d2h_bytes_per_step": px_step * 8, "steps": e2e_steps, "api": "pbrcu_shade_frame_host (pinned host planes, 8 pipelined row bands)",
+                    "host_placement": host_placement},
             "gpu_launches": args.steps,
             "clocks": clocks,
             "cpu_baseline": cpu,

@@ -137,3 +137,41 @@ def cost_balanced_bands(tile_row_costs, height: int, world: int, tile: int = 16)
         cuts.append(r)
     cuts.append(n)
     return [(min(cuts[k] * tile, height), min(cuts[k + 1] * tile, height)) for k in range(world)]
+
+
+def _cpulist(text: str) -> set[int]:
+    """'0-15,32-47' -> {0..15, 32..47} (the sysfs cpulist syntax)."""
+    cpus: set[int] = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_host_near_device(pci_bus_id: str, sysfs: str = "/sys") -> dict:
+    """Pins the calling process to the CPUs of the NUMA node its GPU hangs off, so that the pinned
+    staging buffers allocated afterwards (first touch) and the copy-issuing thread sit on the socket whose
+    PCIe root complex serves that GPU.  One rank per GPU on a two-socket box otherwise has half its
+    host<->device copies cross the socket interconnect.  `pci_bus_id` is 'dddd:bb:dd.f' as CUDA reports it.
+    Does nothing (and says so) on a single-node host or when sysfs has no answer.  The reference runs one
+    host thread on one GPU (`core/GpuHandle.cpp:77-81`) and has no counterpart."""
+    import os
+    info = {"pci_bus_id": pci_bus_id, "node": None, "bound": False}
+    try:
+        nodes = [d for d in os.listdir(f"{sysfs}/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        info["nodes"] = len(nodes)
+        with open(f"{sysfs}/bus/pci/devices/{pci_bus_id.lower()}/numa_node") as f:
+            node = int(f.read().strip())
+        info["node"] = node
+        if node < 0 or len(nodes) < 2:
+            return info
+        with open(f"{sysfs}/devices/system/node/node{node}/cpulist") as f:
+            cpus = _cpulist(f.read()) & os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info["bound"], info["cpus"] = True, len(cpus)
+    except (OSError, ValueError) as e:
+        info["why_not"] = f"{type(e).__name__}: {e}"
+    return info

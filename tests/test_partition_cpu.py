@@ -93,3 +93,36 @@ def test_gloo_world2_gather(height):
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, True, 2.0), (1, True, 2.0)]
+
+
+def test_bind_host_near_device_on_a_fake_sysfs(pbr, tmp_path):
+    """Host placement for one rank per GPU: the rank is pinned to its GPU's NUMA node on a two-node host,
+    left alone on a one-node host, and a missing sysfs entry is reported instead of raised."""
+    P = pbr.partition
+    assert P._cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    mine = sorted(os.sched_getaffinity(0))
+    try:
+        def fake(nodes, gpu_node):
+            root = tmp_path / f"sys{nodes}{gpu_node}"
+            for n in range(nodes):
+                d = root / "devices/system/node" / f"node{n}"
+                d.mkdir(parents=True)
+                cpus = mine[n::nodes] if nodes > 1 else mine
+                (d / "cpulist").write_text(",".join(map(str, cpus)) + "\n")
+            (root / "devices/system/node/possible").write_text("0\n")  # a non-node entry, as in the real sysfs
+            dev = root / "bus/pci/devices/0000:1b:00.0"
+            dev.mkdir(parents=True)
+            (dev / "numa_node").write_text(f"{gpu_node}\n")
+            return str(root)
+
+        one = P.bind_host_near_device("0000:1B:00.0", sysfs=fake(1, 0))
+        assert one["bound"] is False and one["node"] == 0 and one["nodes"] == 1 and os.sched_getaffinity(0) == set(mine)
+        unknown = P.bind_host_near_device("0000:1B:00.0", sysfs=fake(2, -1))
+        assert unknown["bound"] is False and unknown["node"] == -1
+        absent = P.bind_host_near_device("0000:ff:00.0", sysfs=fake(3, 0))
+        assert absent["bound"] is False and "why_not" in absent
+        if len(mine) >= 2:
+            two = P.bind_host_near_device("0000:1B:00.0", sysfs=fake(2, 1))
+            assert two["bound"] is True and two["node"] == 1 and os.sched_getaffinity(0) == set(mine[1::2])
+    finally:
+        os.sched_setaffinity(0, mine)
