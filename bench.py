@@ -282,15 +282,42 @@ def extra_configs(scene, torch, dist, world, rank):
                     dist.broadcast(hdr[b * W8 * 8:e * W8 * 8], src=r)
 
         ms_g = timed(torch, dist, step8k_gather, 5, 3)
+        # the same frame with the gather fused into K3's stores: every rank's frame lives in symmetric memory, each rank
+        # stores its finished band into its own and (over NVLink, from inside the shading kernel) into every peer's frame;
+        # one device-side barrier orders the frame.  No exchange pass, no NCCL on the data path.
+        fused = {}
+        try:
+            from pbr_b200.partition import PeerFrames
+            pf = PeerFrames(W8 * H8 * 8, hdr.device, dist)
+            reps, nrep = pf.replica_array(y0 * W8 * 8)
+
+            def step8k_fused(_):
+                if y1 > y0:
+                    lib.cluster_lights(ctx, C.byref(band.gbuffer), lights.data_ptr(), NL, C.byref(band.tiles), scene.stream())
+                    lib.shade_ggx_ibl_replicated(ctx, C.byref(band.gbuffer), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(band.tiles), C.byref(scene.ibl),
+                                                 pbr.WHOLE, pf.local.data_ptr() + y0 * W8 * 8, W8 * 8, reps, nrep, scene.stream())
+                pf.barrier()
+
+            pf.local.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            ms_f = timed(torch, dist, step8k_fused, 5, 3)
+            fused = {"ms_per_frame_fused_gather": round(ms_f / 5, 4), "fused_gather": "pbrcu_shade_ggx_ibl_replicated: K3 stores each finished texel "
+                     "into the frame of every rank (torch symmetric memory, NVLink P2P stores) + one device-side barrier"}
+        except Exception as e:  # no symmetric memory on this box: the NCCL figures above stand alone
+            pf = None
+            fused = {"fused_gather_unavailable": f"{type(e).__name__}: {e}"[:200]}
         # the gathered frame against the whole frame shaded on this rank alone (untimed)
         whole = scene.buf(W8 * H8 * 8)
         lib.cluster_lights(ctx, C.byref(g), lights.data_ptr(), NL, C.byref(tiles), scene.stream())
         lib.shade_ggx_ibl(ctx, C.byref(g), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(tiles), C.byref(scene.ibl), pbr.WHOLE, whole.data_ptr(), W8 * 8, scene.stream())
         torch.cuda.synchronize()
-        same = torch.tensor([int(torch.equal(whole, hdr))], device=hdr.device)
+        same = torch.tensor([int(torch.equal(whole, hdr)), int(pf is None or torch.equal(whole, pf.local))], device=hdr.device)
         dist.all_reduce(same, op=dist.ReduceOp.MIN)
         gathered = {"ms_per_frame_with_gather": round(ms_g / 5, 4), "gather_bytes_per_frame": W8 * H8 * 8,
-                    "gathered_frame_equals_unsharded": bool(same.item())}
+                    "gathered_frame_equals_unsharded": bool(same[0].item()), **fused}
+        if pf is not None:
+            gathered["fused_gathered_frame_equals_unsharded"] = bool(same[1].item())
         scene.keep = [t for t in scene.keep if t is not whole]
         del whole
     # tile counts live in library-owned memory: copy this rank's out through the C ABI

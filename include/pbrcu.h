@@ -160,6 +160,22 @@ int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
                         const pbrcu_light* lights_dev, uint32_t n_lights,
                         const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
                         void* out_rgba16f, size_t out_pitch, pbrcu_stream s);
+/* K3 with the gather fused into its stores (multi-GPU row bands, north_star: "NCCL over NVLink is used only to
+ * gather the finished tiles" -- here the finished texels leave the shading kernel already gathered).  Same
+ * arguments and results as pbrcu_shade_ggx_ibl; in addition every texel of rect is stored at the same byte
+ * offset (y * out_pitch + x * 8) of each of the n_replicas buffers in replica_outs (a HOST array of device
+ * pointers, 8-byte aligned).  A replica is the same-shaped frame of another GPU mapped into this process
+ * (cudaIpcOpenMemHandle, CUDA VMM / torch symmetric memory, or peer access in a one-process setup): its stores
+ * travel over NVLink while the kernel shades the following texels, so a rank that shades rows [y0, y1) into its own
+ * frame and into its peers' frames leaves the whole frame on every GPU with no separate exchange pass.  The caller
+ * orders frames: a barrier across the ranks after the launches complete and before anyone reads (or overwrites)
+ * a frame.  The reference renders on one GPU (`core/GpuHandle.cpp:77-81`) and has no counterpart. */
+#define PBRCU_MAX_REPLICAS 15
+int pbrcu_shade_ggx_ibl_replicated(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                                   const pbrcu_light* lights_dev, uint32_t n_lights,
+                                   const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
+                                   void* out_rgba16f, size_t out_pitch, void* const* replica_outs,
+                                   uint32_t n_replicas, pbrcu_stream s);
 /* One GGX+IBL frame through HOST buffers (the end-to-end path of the headline metric): the frame is
  * cut into n_bands row bands (0 = 8) pipelined over two internal streams, so the H2D copy of band
  * i+1 overlaps the shading and D2H read-back of band i.  lights_host is a host array; ibl textures

@@ -52,7 +52,17 @@ struct ShadeParams {
   uint32_t n_views;
   size_t view_stride8, view_stride4, out_view_stride;
   const float* cams;
+  // pbrcu_shade_ggx_ibl_replicated: every finished texel is also stored at the same byte offset of these buffers
+  // (peer-mapped memory of the other GPUs: the stores travel over NVLink while the kernel shades the next texels)
+  uint32_t n_replicas;
+  uint8_t* replica[PBRCU_MAX_REPLICAS];
 };
+
+// the finished texel: streamed to the local frame and to every replica
+__device__ __forceinline__ void store_texel(const ShadeParams& p, size_t off, uint2 v) {
+  stg_stream8(p.out + off, v);
+  for (uint32_t k = 0; k < p.n_replicas; ++k) stg_stream8(p.replica[k] + off, v);
+}
 
 // how a work item gets its light list
 enum : int {
@@ -379,9 +389,9 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     }
     const float dr = lo(dr2) + hi(dr2), dg = lo(dg2) + hi(dg2), db = lo(db2) + hi(db2);
     if (!inside) continue;
-    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
+    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
     if (!lit) {
-      stg_stream8(outp, make_uint2(0u, 0u));
+      store_texel(p, outo, make_uint2(0u, 0u));
       continue;
     }
     // ---- ambient: split-sum image-based lighting (Karis 2013) ----
@@ -431,7 +441,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     }
     // oracle order: (direct + ambient) + emissive
     Lr = fminf((dr + ar) + Lr, 65504.0f); Lg = fminf((dg + ag) + Lg, 65504.0f); Lb = fminf((db + ab) + Lb, 65504.0f);
-    stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+    store_texel(p, outo, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
   }
   cp_async_wait<0>();
 }
@@ -512,12 +522,12 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
 
     const uint32_t x = ip.x, y = ip.y;
     if (!(x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1)) continue;
-    uint8_t* outp = p.out + size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
+    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
     const TileStage& st = s_tile[stage];
     const uint2 tn = st.px[1][threadIdx.x];
     const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
     if (nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f) {  // all-zero normal = cleared texel
-      stg_stream8(outp, make_uint2(0u, 0u));
+      store_texel(p, outo, make_uint2(0u, 0u));
       continue;
     }
     // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
@@ -633,7 +643,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
     const float base_a = unorm16_hi(st.px[2][threadIdx.x].y);
     // oracle order: (direct + ambient) + emissive
     const float Lr = fminf((dr + ar) + exy.x, 65504.0f), Lg = fminf((dg + ag) + exy.y, 65504.0f), Lb = fminf((db + ab) + ezw.x, 65504.0f);
-    stg_stream8(outp, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+    store_texel(p, outo, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
   }
   cp_async_wait<0>();
 }
@@ -756,8 +766,11 @@ static void launch_shade(const ShadeParams& p, int lists, uint32_t grid, cudaStr
 // argument checks and kernel parameters shared by the single-view and the batched entry; n_views > 1 = batched
 static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_dev, uint32_t n_lights,
                         const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch,
-                        uint32_t n_views, size_t view_stride8, size_t view_stride4, size_t out_view_stride, pbrcu_stream s) {
+                        uint32_t n_views, size_t view_stride8, size_t view_stride4, size_t out_view_stride, pbrcu_stream s,
+                        void* const* replicas = nullptr, uint32_t n_replicas = 0) {
   PBRCU_REQUIRE(ctx && g && cam_pos && out_rgba16f, "NULL argument");
+  PBRCU_REQUIRE(n_replicas <= PBRCU_MAX_REPLICAS && (n_replicas == 0 || replicas), "too many replicas or replicas NULL");
+  for (uint32_t k = 0; k < n_replicas; ++k) PBRCU_REQUIRE(replicas[k] && reinterpret_cast<uintptr_t>(replicas[k]) % 8 == 0, "replica NULL or not 8-byte aligned");
   PBRCU_REQUIRE(g->positions && g->normals && g->albedo && g->orm && g->emissive, "gbuffer plane is NULL (K3 needs the tier-1 planes)");
   PBRCU_REQUIRE(g->pitch8 >= size_t(g->width) * 8 && g->pitch8 % 8 == 0 && g->pitch4 >= size_t(g->width) * 4 && g->pitch4 % 4 == 0, "bad gbuffer pitch");
   PBRCU_REQUIRE(out_pitch >= size_t(g->width) * 8 && out_pitch % 8 == 0, "out_pitch too small or not a multiple of 8");
@@ -769,6 +782,8 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   p.pos = static_cast<const uint8_t*>(g->positions); p.nrm = static_cast<const uint8_t*>(g->normals);
   p.alb = static_cast<const uint8_t*>(g->albedo); p.orm = static_cast<const uint8_t*>(g->orm);
   p.emi = static_cast<const uint8_t*>(g->emissive); p.out = static_cast<uint8_t*>(out_rgba16f);
+  p.n_replicas = n_replicas;
+  for (uint32_t k = 0; k < n_replicas; ++k) p.replica[k] = static_cast<uint8_t*>(replicas[k]);
   p.pitch8 = g->pitch8; p.pitch4 = g->pitch4; p.out_pitch = out_pitch;
   p.x0 = rect.x0; p.y0 = rect.y0; p.x1 = rect.x0 + rect.w; p.y1 = rect.y0 + rect.h;
   p.tx0 = rect.x0 / kTile; p.ty0 = rect.y0 / kTile;
@@ -831,6 +846,13 @@ extern "C" int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
                                    const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
                                    const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch, pbrcu_stream s) {
   return shade_common(ctx, g, cam_pos, lights_dev, n_lights, tiles, ibl, rect, out_rgba16f, out_pitch, 1, 0, 0, 0, s);
+}
+
+extern "C" int pbrcu_shade_ggx_ibl_replicated(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                                              const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
+                                              const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch,
+                                              void* const* replica_outs, uint32_t n_replicas, pbrcu_stream s) {
+  return shade_common(ctx, g, cam_pos, lights_dev, n_lights, tiles, ibl, rect, out_rgba16f, out_pitch, 1, 0, 0, 0, s, replica_outs, n_replicas);
 }
 
 extern "C" int pbrcu_shade_ggx_ibl_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,

@@ -175,3 +175,34 @@ def bind_host_near_device(pci_bus_id: str, sysfs: str = "/sys") -> dict:
     except (OSError, ValueError) as e:
         info["why_not"] = f"{type(e).__name__}: {e}"
     return info
+
+
+class PeerFrames:
+    """This rank's frame buffer in symmetric memory plus the same buffer of every other rank mapped into this
+    process: what `pbrcu_shade_ggx_ibl_replicated` needs to store a finished row band straight into the peers'
+    frames over NVLink.  `local` is a uint8 tensor; `peers` the mapped device addresses of the other ranks' buffers
+    (rank order, self left out); `barrier()` = every rank's launches so far have completed (device-side, on the
+    current stream) -- call it after the replicated launch and before reading or overwriting a frame."""
+
+    def __init__(self, nbytes: int, device, dist):
+        import torch
+        import torch.distributed._symmetric_memory as symm
+
+        self.local = symm.empty(nbytes, dtype=torch.uint8, device=device)
+        self._handle = symm.rendezvous(self.local, dist.group.WORLD)
+        h = self._handle
+        off = int(getattr(h, "offset", 0))
+        self.rank, self.world = int(h.rank), int(h.world_size)
+        ptrs = [int(p) + off for p in h.buffer_ptrs]
+        if ptrs[self.rank] != self.local.data_ptr():
+            raise RuntimeError("symmetric memory: the mapped address of this rank's buffer is not the tensor's")
+        self.peers = [p for r, p in enumerate(ptrs) if r != self.rank]
+
+    def replica_array(self, byte_offset: int = 0):
+        """(ctypes array of void*, count) of the peers' buffers advanced by byte_offset -- the replica_outs argument."""
+        import ctypes as C
+        arr = (C.c_void_p * max(len(self.peers), 1))(*[p + byte_offset for p in self.peers])
+        return arr, len(self.peers)
+
+    def barrier(self):
+        self._handle.barrier()

@@ -520,3 +520,56 @@ def test_prefilter_full_size_properties(dev, oracle):
             assert (np.abs(got - ref) <= 1e-3 + REL * np.abs(ref)).all(), (m, f, x, y, got, ref)
     for b in (src, chain_d, whole, part, exact_d):
         b.free()
+
+
+@pytest.mark.parametrize("mode", ["one-list", "tile-lists", "no-ibl"])
+def test_shade_replicated_stores_equal_the_plain_frame(pbr, dev, oracle, mode):
+    """pbrcu_shade_ggx_ibl_replicated (the row-band gather fused into K3's stores): every replica receives exactly the
+    texels of the rect, bit-identical to the plain entry point, and nothing outside the rect -- here with the replicas in
+    local memory; the N = 2..8 bench runs the same call on peer-mapped frames and checks the gathered frame."""
+    w, h, nl = 150, 70, 7
+    host, bufs = build_ibl(dev, oracle)
+    g = synth_gbuffer(w, h, seed=5, tier_b=True)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    lights = synth_lights(nl, seed=2)
+    ld = dev.upload(lights)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    tiles = pbr.LightTiles()
+    dev.lib.light_tiles_alloc(dev.ctx, w, h, 16, C.byref(tiles))
+    dev.lib.cluster_lights(dev.ctx, C.byref(gb), ld.ptr, nl, C.byref(tiles), None)
+    targ = C.byref(tiles) if mode == "tile-lists" else None
+    iarg = None if mode == "no-ibl" else C.byref(ibl)
+    cam = pbr.f3(0.5, -1.0, 12.0)
+    plain = dev.alloc(w * h * 8)
+    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.WHOLE, plain.ptr, w * 8, None)
+    dev.sync()
+    want = plain.download((h, w, 4), np.uint16)
+    sentinel = np.full((h, w, 4), 0x7B7B, np.uint16)
+    rect = (3, 17, 140, 37)  # starts and ends inside tiles
+    own = dev.upload(sentinel)
+    reps = [dev.upload(sentinel) for _ in range(3)]
+    ptrs = (C.c_void_p * 3)(*[r.ptr for r in reps])
+    dev.lib.shade_ggx_ibl_replicated(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.Rect(*rect), own.ptr, w * 8, ptrs, 3, None)
+    dev.sync()
+    expect = sentinel.copy()
+    expect[rect[1]:rect[1] + rect[3], rect[0]:rect[0] + rect[2]] = want[rect[1]:rect[1] + rect[3], rect[0]:rect[0] + rect[2]]
+    for what, buf in [("own frame", own)] + [(f"replica {k}", r) for k, r in enumerate(reps)]:
+        got = buf.download((h, w, 4), np.uint16)
+        assert np.array_equal(got, expect), f"{mode}: {what} differs in {np.count_nonzero(got != expect)} values"
+    # no replicas = the plain call
+    dev.lib.shade_ggx_ibl_replicated(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.WHOLE, own.ptr, w * 8, None, 0, None)
+    dev.sync()
+    assert np.array_equal(own.download((h, w, 4), np.uint16), want)
+    with pytest.raises(pbr.PbrcuError):  # more replicas than PBRCU_MAX_REPLICAS
+        many = (C.c_void_p * 16)(*[reps[0].ptr] * 16)
+        dev.lib.shade_ggx_ibl_replicated(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.WHOLE, own.ptr, w * 8, many, 16, None)
+    with pytest.raises(pbr.PbrcuError):  # a NULL replica
+        bad = (C.c_void_p * 2)(reps[0].ptr, None)
+        dev.lib.shade_ggx_ibl_replicated(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.WHOLE, own.ptr, w * 8, bad, 2, None)
+    with pytest.raises(pbr.PbrcuError):  # a misaligned replica
+        odd = (C.c_void_p * 1)(reps[0].ptr + 4)
+        dev.lib.shade_ggx_ibl_replicated(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.WHOLE, own.ptr, w * 8, odd, 1, None)
+    dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+    for b in (plain, own, ld, *reps):
+        b.free()
