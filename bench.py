@@ -304,6 +304,27 @@ def extra_configs(scene, torch, dist, world, rank):
             ms_f = timed(torch, dist, step8k_fused, 5, 3)
             fused = {"ms_per_frame_fused_gather": round(ms_f / 5, 4), "fused_gather": "pbrcu_shade_ggx_ibl_replicated: K3 stores each finished texel "
                      "into the frame of every rank (torch symmetric memory, NVLink P2P stores) + one device-side barrier"}
+            if pf.multicast:
+                def step8k_mc(_):
+                    if y1 > y0:
+                        lib.cluster_lights(ctx, C.byref(band.gbuffer), lights.data_ptr(), NL, C.byref(band.tiles), scene.stream())
+                        lib.shade_ggx_ibl_multicast(ctx, C.byref(band.gbuffer), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(band.tiles), C.byref(scene.ibl),
+                                                    pbr.WHOLE, pf.multicast + y0 * W8 * 8, W8 * 8, scene.stream())
+                    pf.barrier()
+
+                check = scene.buf(W8 * H8 * 8)
+                check.copy_(pf.local)  # the P2P-store result, compared below
+                pf.local.zero_()
+                torch.cuda.synchronize()
+                dist.barrier()
+                ms_m = timed(torch, dist, step8k_mc, 5, 3)
+                fused.update({"ms_per_frame_multicast_gather": round(ms_m / 5, 4), "multicast_gather": "pbrcu_shade_ggx_ibl_multicast: one multimem.st per "
+                              "texel to the NVSwitch multicast address of the frames + one device-side barrier",
+                              "multicast_frame_equals_p2p_frame": bool(torch.equal(check, pf.local))})
+                scene.keep = [t for t in scene.keep if t is not check]
+                del check
+            else:
+                fused["multicast_gather_unavailable"] = "symmetric memory reports no multicast address on this box"
         except Exception as e:  # no symmetric memory on this box: the NCCL figures above stand alone
             pf = None
             fused = {"fused_gather_unavailable": f"{type(e).__name__}: {e}"[:200]}

@@ -176,6 +176,16 @@ int pbrcu_shade_ggx_ibl_replicated(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const
                                    const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
                                    void* out_rgba16f, size_t out_pitch, void* const* replica_outs,
                                    uint32_t n_replicas, pbrcu_stream s);
+/* The same gather with ONE store per texel: out_multicast is a multicast (multimem) address -- a CUDA VMM multicast
+ * object (cuMulticastCreate / cuMulticastBindMem; torch symmetric memory's multicast_ptr) bound to the same-shaped
+ * frame on every GPU of the team, this one included.  K3 stores each finished texel with `multimem.st` and the
+ * NVSwitch writes it into every bound frame, so a rank's NVLink egress is its own band once, whatever the team size.
+ * Needs NVSwitch multicast (NVLS); results are read through the ordinary per-GPU address of the frame after the
+ * cross-rank barrier.  Same arguments otherwise as pbrcu_shade_ggx_ibl. */
+int pbrcu_shade_ggx_ibl_multicast(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                                  const pbrcu_light* lights_dev, uint32_t n_lights,
+                                  const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
+                                  void* out_multicast, size_t out_pitch, pbrcu_stream s);
 /* One GGX+IBL frame through HOST buffers (the end-to-end path of the headline metric): the frame is
  * cut into n_bands row bands (0 = 8) pipelined over two internal streams, so the H2D copy of band
  * i+1 overlaps the shading and D2H read-back of band i.  lights_host is a host array; ibl textures

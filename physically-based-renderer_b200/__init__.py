@@ -117,6 +117,7 @@ _SIGNATURES = {
     "pbrcu_cube_chain_texels": (_sz, [_u32, _u32]),
     "pbrcu_cube_mip_offset": (_sz, [_u32, _u32]),
     "pbrcu_shade_ggx_ibl": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, _vp]),
+    "pbrcu_shade_ggx_ibl_multicast": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, _vp]),
     "pbrcu_shade_ggx_ibl_replicated": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, C.POINTER(_vp), _u32, _vp]),
     "pbrcu_shade_ggx_ibl_batched": (_i, [_vp, _PG, _sz, _sz, _u32, _f3, _vp, _u32, _PI, _vp, _sz, _sz, _vp]),
     "pbrcu_shade_frame_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _f3, _vp, _u32, _PI, _vp, _u32, _vp]),

@@ -56,10 +56,17 @@ struct ShadeParams {
   // (peer-mapped memory of the other GPUs: the stores travel over NVLink while the kernel shades the next texels)
   uint32_t n_replicas;
   uint8_t* replica[PBRCU_MAX_REPLICAS];
+  int out_is_multicast;  // pbrcu_shade_ggx_ibl_multicast: `out` is a multimem address
 };
 
-// the finished texel: streamed to the local frame and to every replica
+// the finished texel: streamed to the local frame and to every replica; or ONE multimem store to a multicast address,
+// which the NVSwitch delivers to the frame of every GPU bound to it (this one included)
 __device__ __forceinline__ void store_texel(const ShadeParams& p, size_t off, uint2 v) {
+  if (p.out_is_multicast) {
+    const unsigned long long bits = (static_cast<unsigned long long>(v.y) << 32) | v.x;
+    asm volatile("multimem.st.weak.global.b64 [%0], %1;" ::"l"(p.out + off), "l"(bits) : "memory");
+    return;
+  }
   stg_stream8(p.out + off, v);
   for (uint32_t k = 0; k < p.n_replicas; ++k) stg_stream8(p.replica[k] + off, v);
 }
@@ -767,7 +774,7 @@ static void launch_shade(const ShadeParams& p, int lists, uint32_t grid, cudaStr
 static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_dev, uint32_t n_lights,
                         const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch,
                         uint32_t n_views, size_t view_stride8, size_t view_stride4, size_t out_view_stride, pbrcu_stream s,
-                        void* const* replicas = nullptr, uint32_t n_replicas = 0) {
+                        void* const* replicas = nullptr, uint32_t n_replicas = 0, bool multicast = false) {
   PBRCU_REQUIRE(ctx && g && cam_pos && out_rgba16f, "NULL argument");
   PBRCU_REQUIRE(n_replicas <= PBRCU_MAX_REPLICAS && (n_replicas == 0 || replicas), "too many replicas or replicas NULL");
   for (uint32_t k = 0; k < n_replicas; ++k) PBRCU_REQUIRE(replicas[k] && reinterpret_cast<uintptr_t>(replicas[k]) % 8 == 0, "replica NULL or not 8-byte aligned");
@@ -783,6 +790,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   p.alb = static_cast<const uint8_t*>(g->albedo); p.orm = static_cast<const uint8_t*>(g->orm);
   p.emi = static_cast<const uint8_t*>(g->emissive); p.out = static_cast<uint8_t*>(out_rgba16f);
   p.n_replicas = n_replicas;
+  p.out_is_multicast = multicast ? 1 : 0;
   for (uint32_t k = 0; k < n_replicas; ++k) p.replica[k] = static_cast<uint8_t*>(replicas[k]);
   p.pitch8 = g->pitch8; p.pitch4 = g->pitch4; p.out_pitch = out_pitch;
   p.x0 = rect.x0; p.y0 = rect.y0; p.x1 = rect.x0 + rect.w; p.y1 = rect.y0 + rect.h;
@@ -853,6 +861,12 @@ extern "C" int pbrcu_shade_ggx_ibl_replicated(pbrcu_ctx* ctx, const pbrcu_gbuffe
                                               const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch,
                                               void* const* replica_outs, uint32_t n_replicas, pbrcu_stream s) {
   return shade_common(ctx, g, cam_pos, lights_dev, n_lights, tiles, ibl, rect, out_rgba16f, out_pitch, 1, 0, 0, 0, s, replica_outs, n_replicas);
+}
+
+extern "C" int pbrcu_shade_ggx_ibl_multicast(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
+                                             const pbrcu_light* lights_dev, uint32_t n_lights, const pbrcu_light_tiles* tiles,
+                                             const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_multicast, size_t out_pitch, pbrcu_stream s) {
+  return shade_common(ctx, g, cam_pos, lights_dev, n_lights, tiles, ibl, rect, out_multicast, out_pitch, 1, 0, 0, 0, s, nullptr, 0, true);
 }
 
 extern "C" int pbrcu_shade_ggx_ibl_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,

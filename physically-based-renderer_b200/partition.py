@@ -197,6 +197,9 @@ class PeerFrames:
         if ptrs[self.rank] != self.local.data_ptr():
             raise RuntimeError("symmetric memory: the mapped address of this rank's buffer is not the tensor's")
         self.peers = [p for r, p in enumerate(ptrs) if r != self.rank]
+        # NVSwitch multicast address of the same buffers (0 when the box has no NVLS multicast)
+        mc = int(getattr(h, "multicast_ptr", 0) or 0)
+        self.multicast = mc + off if mc else 0
 
     def replica_array(self, byte_offset: int = 0):
         """(ctypes array of void*, count) of the peers' buffers advanced by byte_offset -- the replica_outs argument."""
