@@ -402,19 +402,47 @@ def prefilter_sharded(scene, torch, dist, world, rank):
     dst = scene.buf(scene.pref.numel())
 
     def conv(_):
-        lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, dst.data_ptr(), 0, CUBE_MIPS - 1, rank, world, scene.stream())
+        # level 0 (a copy of the source level, which every rank holds) whole on every rank; levels 1.. by row blocks
+        lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, dst.data_ptr(), 0, 0, 0, 1, scene.stream())
+        lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, dst.data_ptr(), 1, CUBE_MIPS - 1, rank, world, scene.stream())
 
     def step(i):
         conv(i)
-        gather_chain(dst, CUBE_RES, CUBE_MIPS, world, rank, dist if world > 1 else None)
+        gather_chain(dst, CUBE_RES, CUBE_MIPS, world, rank, dist if world > 1 else None, first_level=1)
 
     ms_conv = timed(torch, dist, conv, 3, 2) / 3
     dst.zero_()
     ms = timed(torch, dist, step, 3, 2) / 3
     same = bool(torch.equal(dst, scene.pref))
-    return {"ms_prefilter_and_gather": round(ms, 3), "ms_prefilter_shard_only": round(ms_conv, 3), "shards": world,
-            "gathered_chain_equals_unsharded": same, "gather_bytes_per_rank": int(dst.numel() * (world - 1) // world),
-            "scaling": "strong (row blocks of every level; NCCL all-gather of the finished chain)"}
+    fused = {}
+    if world > 1:
+        # the same with the gather fused into K7's stores: chains in symmetric memory, every finished texel also stored
+        # into the peers' chains (NVLink P2P stores), one device-side barrier -- no NCCL on the data path
+        try:
+            from pbr_b200.partition import PeerFrames
+            pf = PeerFrames(dst.numel(), dst.device, dist)
+            reps, nrep = pf.replica_array(0)
+
+            def step_fused(_):
+                lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, pf.local.data_ptr(), 0, 0, 0, 1, scene.stream())
+                lib.ibl_prefilter_ggx_replicated(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, pf.local.data_ptr(), 1, CUBE_MIPS - 1,
+                                                 rank, world, reps, nrep, scene.stream())
+                pf.barrier()
+
+            pf.local.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            ms_f = timed(torch, dist, step_fused, 3, 2) / 3
+            ok = torch.tensor([int(torch.equal(pf.local, scene.pref))], device=dst.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            fused = {"ms_prefilter_fused_gather": round(ms_f, 3), "fused_chain_equals_unsharded": bool(ok.item()),
+                     "fused_gather": "pbrcu_ibl_prefilter_ggx_replicated: K7 stores each finished texel into every rank's chain (symmetric memory, NVLink P2P stores)"}
+            del pf
+        except Exception as e:
+            fused = {"fused_gather_unavailable": f"{type(e).__name__}: {e}"[:200]}
+    return {**fused, "ms_prefilter_and_gather": round(ms, 3), "ms_prefilter_shard_only": round(ms_conv, 3), "shards": world,
+            "gathered_chain_equals_unsharded": same, "gather_bytes_per_rank": int((dst.numel() - 6 * CUBE_RES * CUBE_RES * 8) * (world - 1) // world),
+            "scaling": "strong (row blocks of levels 1..; level 0 copied whole on every rank; NCCL all-gather of levels 1..)"}
 
 
 def geometry_bench(scene, torch, dist, world, rank):

@@ -252,6 +252,15 @@ int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t 
                             uint32_t nmips, uint32_t nsamples, void* dst_chain_dev,
                             uint32_t first_mip, uint32_t last_mip, uint32_t shard, uint32_t nshards,
                             pbrcu_stream s);
+/* K7 with the all-gather of a sharded prefilter fused into its stores: as pbrcu_ibl_prefilter_ggx, and every texel
+ * this shard finishes is also stored at the same index of each replica chain (HOST array of n_replicas <=
+ * PBRCU_MAX_REPLICAS device pointers: the peers' destination chains mapped into this process, see
+ * pbrcu_shade_ggx_ibl_replicated).  When every rank has run its shard and the ranks have passed a barrier, every
+ * GPU holds the whole chain -- no exchange pass. */
+int pbrcu_ibl_prefilter_ggx_replicated(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res,
+                                       uint32_t nmips, uint32_t nsamples, void* dst_chain_dev,
+                                       uint32_t first_mip, uint32_t last_mip, uint32_t shard, uint32_t nshards,
+                                       void* const* replica_chains, uint32_t n_replicas, pbrcu_stream s);
 /* K6: cosine-weighted irradiance (E/pi), 6*res^2 RGBA16F */
 int pbrcu_ibl_irradiance(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
                          uint32_t res, uint32_t nsamples, void* out_dev, pbrcu_stream s);

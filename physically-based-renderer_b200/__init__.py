@@ -135,6 +135,7 @@ _SIGNATURES = {
     "pbrcu_shade_set_texture_unit": (_i, [_vp, _i]),
     "pbrcu_geometry_pass": (_i, [_vp, C.POINTER(GBuffer), _vp, _vp, C.POINTER(Draw), C.c_uint32, _vp, _vp]),
     "pbrcu_ibl_prefilter_ggx": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, _vp]),
+    "pbrcu_ibl_prefilter_ggx_replicated": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, C.POINTER(_vp), _u32, _vp]),
     "pbrcu_ibl_irradiance": (_i, [_vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
     "pbrcu_synth_gbuffer": (_i, [_vp, _PG, _i, _u64, _f3, _f3, _vp]),
     "pbrcu_synth_environment": (_i, [_vp, _vp, _u32, _u32, _u64, _vp]),

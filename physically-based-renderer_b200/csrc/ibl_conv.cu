@@ -24,6 +24,10 @@ struct ConvParams {
   float roughness;    // CONV_GGX only
   int row_begin, row_end;  // global rows (face*res + y) handled by this launch (multi-GPU shard)
   int tw, th;         // texel tile per block: tw*th*G == kConvThreads
+  // pbrcu_ibl_prefilter_ggx_replicated: the finished texel is also stored at the same index of these levels (the
+  // peers' chains mapped into this process -- the all-gather of a sharded prefilter fused into the kernel's stores)
+  int n_replicas;
+  uint2* replica_level[PBRCU_MAX_REPLICAS];
 };
 
 template <int MODE>
@@ -147,8 +151,10 @@ __global__ void __launch_bounds__(kConvThreads) conv_kernel(const __grid_constan
   if (valid && lane == 0) {
     const float inv = 1.0f / wsum;
     const size_t idx = (size_t(face) * p.res + y) * p.res + x;
-    p.dst_level[idx] = make_uint2(f2_to_h2(fminf(ar * inv, 65504.f), fminf(ag * inv, 65504.f)),
-                                  f2_to_h2(fminf(ab * inv, 65504.f), 1.0f));
+    const uint2 texel = make_uint2(f2_to_h2(fminf(ar * inv, 65504.f), fminf(ag * inv, 65504.f)),
+                                   f2_to_h2(fminf(ab * inv, 65504.f), 1.0f));
+    p.dst_level[idx] = texel;
+    for (int k = 0; k < p.n_replicas; ++k) p.replica_level[k][idx] = texel;
   }
 }
 
@@ -325,10 +331,12 @@ extern "C" int pbrcu_ibl_set_exact_filtering(pbrcu_ctx* ctx, int exact) {
   return PBRCU_OK;
 }
 
-extern "C" int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
-                                       uint32_t nsamples, void* dst_chain_dev, uint32_t first_mip, uint32_t last_mip,
-                                       uint32_t shard, uint32_t nshards, pbrcu_stream s) {
+static int prefilter_common(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
+                            uint32_t nsamples, void* dst_chain_dev, uint32_t first_mip, uint32_t last_mip,
+                            uint32_t shard, uint32_t nshards, void* const* replicas, uint32_t n_replicas, pbrcu_stream s) {
   PBRCU_REQUIRE(ctx && src_chain_dev && dst_chain_dev, "NULL argument");
+  PBRCU_REQUIRE(n_replicas <= PBRCU_MAX_REPLICAS && (n_replicas == 0 || replicas), "too many replicas or replicas NULL");
+  for (uint32_t k = 0; k < n_replicas; ++k) PBRCU_REQUIRE(replicas[k] && reinterpret_cast<uintptr_t>(replicas[k]) % 8 == 0, "replica NULL or not 8-byte aligned");
   PBRCU_REQUIRE(base_res > 0 && (base_res & (base_res - 1)) == 0, "base_res must be a power of two");
   PBRCU_REQUIRE(nmips >= 2 && nmips <= 16 && (base_res >> (nmips - 1)) >= 1, "nmips out of range for base_res");
   PBRCU_REQUIRE(first_mip <= last_mip && last_mip < nmips, "mip range out of bounds");
@@ -348,6 +356,9 @@ extern "C" int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev
       const uint2* src = static_cast<const uint2*>(src_chain_dev) + off;
       PBRCU_CUDA(cudaMemcpyAsync(dst + size_t(rb) * res, src + size_t(rb) * res, size_t(re - rb) * res * 8,
                                  cudaMemcpyDeviceToDevice, st));
+      for (uint32_t k = 0; k < n_replicas; ++k)
+        PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint2*>(replicas[k]) + off + size_t(rb) * res, src + size_t(rb) * res, size_t(re - rb) * res * 8,
+                                   cudaMemcpyDefault, st));
       continue;
     }
     ConvParams p{};
@@ -359,9 +370,25 @@ extern "C" int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev
     p.row_begin = rb;
     p.row_end = re;
     p.tex = ctx->cube.tex;
+    p.n_replicas = int(n_replicas);
+    for (uint32_t k = 0; k < n_replicas; ++k) p.replica_level[k] = static_cast<uint2*>(replicas[k]) + off;
     if (int rc = tex ? launch_conv<CONV_GGX, true>(ctx, p, st) : launch_conv<CONV_GGX, false>(ctx, p, st)) return rc;
   }
   return PBRCU_OK;
+}
+
+extern "C" int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
+                                       uint32_t nsamples, void* dst_chain_dev, uint32_t first_mip, uint32_t last_mip,
+                                       uint32_t shard, uint32_t nshards, pbrcu_stream s) {
+  return prefilter_common(ctx, src_chain_dev, base_res, nmips, nsamples, dst_chain_dev, first_mip, last_mip, shard, nshards, nullptr, 0, s);
+}
+
+extern "C" int pbrcu_ibl_prefilter_ggx_replicated(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
+                                                  uint32_t nsamples, void* dst_chain_dev, uint32_t first_mip, uint32_t last_mip,
+                                                  uint32_t shard, uint32_t nshards, void* const* replica_chains, uint32_t n_replicas,
+                                                  pbrcu_stream s) {
+  return prefilter_common(ctx, src_chain_dev, base_res, nmips, nsamples, dst_chain_dev, first_mip, last_mip, shard, nshards,
+                          replica_chains, n_replicas, s);
 }
 
 extern "C" int pbrcu_ibl_irradiance(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,

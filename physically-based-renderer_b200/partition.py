@@ -66,15 +66,17 @@ def chain_blocks(base_res: int, nmips: int, world: int, rank: int, texel_bytes: 
     return out
 
 
-def gather_chain(chain, base_res: int, nmips: int, world: int, rank: int, dist=None, texel_bytes: int = 8):
+def gather_chain(chain, base_res: int, nmips: int, world: int, rank: int, dist=None, texel_bytes: int = 8, first_level: int = 0):
     """All-gathers a sharded prefilter result: `chain` is the full-size flat uint8 tensor in which this rank
     has written only its chain_blocks; on return every rank holds the whole chain.  Levels whose rows divide
     evenly go through ONE in-place all-gather each (NCCL: all_gather_into_tensor), the tiny tail levels
-    through per-owner broadcasts."""
+    through per-owner broadcasts.  `first_level` = 1 leaves level 0 out of the exchange: the prefiltered
+    level 0 is a copy of the source level every rank already holds (K4/K5 are replicated), so a rank copies it
+    whole (shard 0 of 1 for that level) and three quarters of the chain's bytes never touch NVLink."""
     if dist is None or world == 1:
         return chain
     blocks = [chain_blocks(base_res, nmips, world, r, texel_bytes) for r in range(world)]
-    for m in range(nmips):
+    for m in range(first_level, nmips):
         lens = {blocks[r][m][1] for r in range(world)}
         off0 = blocks[0][m][0]
         if len(lens) == 1 and chain.is_cuda and hasattr(dist, "all_gather_into_tensor"):

@@ -573,3 +573,31 @@ def test_shade_replicated_stores_equal_the_plain_frame(pbr, dev, oracle, mode):
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
     for b in (plain, own, ld, *reps):
         b.free()
+
+
+@pytest.mark.parametrize("exact", [0, 1])
+def test_prefilter_replicated_stores_build_the_whole_chain(dev, oracle, exact):
+    """pbrcu_ibl_prefilter_ggx_replicated (the all-gather of a sharded prefilter fused into K7's stores): three "ranks"
+    each run their shard into their own chain with the other two as replicas; afterwards all three chains are complete
+    and bit-identical to the unsharded prefilter.  Replicas in local memory here; the N >= 2 bench maps peer memory."""
+    res, nmips, ns = 64, 7, 128
+    _, chain_d, chain = make_env_chain(dev, oracle, res, nmips, seed=4)
+    dev.lib.ibl_set_exact_filtering(dev.ctx, exact)
+    whole = dev.alloc(chain.nbytes)
+    dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, whole.ptr, 0, nmips - 1, 0, 1, None)
+    dev.sync()
+    want = whole.download(chain.shape, np.uint16)
+    world = 3
+    chains = [dev.upload(np.full(chain.shape, 0x7B7B, np.uint16)) for _ in range(world)]
+    for r in range(world):
+        others = (C.c_void_p * (world - 1))(*[chains[k].ptr for k in range(world) if k != r])
+        dev.lib.ibl_prefilter_ggx_replicated(dev.ctx, chain_d.ptr, res, nmips, ns, chains[r].ptr, 0, nmips - 1, r, world, others, world - 1, None)
+    dev.sync()
+    for r in range(world):
+        got = chains[r].download(chain.shape, np.uint16)
+        assert np.array_equal(got, want), f"chain of rank {r} differs from the unsharded prefilter in {np.count_nonzero(got != want)} values"
+    with pytest.raises(Exception):
+        dev.lib.ibl_prefilter_ggx_replicated(dev.ctx, chain_d.ptr, res, nmips, ns, chains[0].ptr, 0, nmips - 1, 0, 1, None, 2, None)
+    dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+    for b in (whole, *chains):
+        b.free()
