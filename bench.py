@@ -554,7 +554,7 @@ def run_e2e(scene, torch, dist, host, out, steps, warmup):
     def step(_):
         lib.shade_frame_host(ctx, host["positions"].data_ptr(), host["normals"].data_ptr(), host["albedo"].data_ptr(),
                              host["orm"].data_ptr(), host["emissive"].data_ptr(), W4K, H4K, cam, lights.ctypes.data,
-                             N_LIGHTS, C.byref(scene.ibl), out.data_ptr(), 8, scene.stream())
+                             N_LIGHTS, C.byref(scene.ibl), out.data_ptr(), 4, scene.stream())
 
     return timed(torch, dist, step, steps, warmup)
 
@@ -670,7 +670,7 @@ def main_ours(args):
                          "algorithmic_bytes_per_launch": B_PER_PX_K3 * px_step, "peak_source": peak_src,
                          "kernel": "shade_ggx_one_kernel", "algorithmic_bytes_per_px": B_PER_PX_K3},
             "e2e": {"value": round(e2e_value, 1), "unit": "Mpix/s", "h2d_bytes_per_step": px_step * 36,
-                    "d2h_bytes_per_step": px_step * 8, "steps": e2e_steps, "api": "pbrcu_shade_frame_host (pinned host planes, 8 pipelined row bands)",
+                    "d2h_bytes_per_step": px_step * 8, "steps": e2e_steps, "api": "pbrcu_shade_frame_host (pinned host planes, 4 pipelined row bands, tapered 8:4:2:1)",
                     "host_placement": host_placement},
             "gpu_launches": args.steps,
             "clocks": clocks,

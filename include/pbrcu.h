@@ -187,8 +187,9 @@ int pbrcu_shade_ggx_ibl_multicast(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const 
                                   const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
                                   void* out_multicast, size_t out_pitch, pbrcu_stream s);
 /* One GGX+IBL frame through HOST buffers (the end-to-end path of the headline metric): the frame is
- * cut into n_bands row bands (0 = 8) pipelined over two internal streams, so the H2D copy of band
- * i+1 overlaps the shading and D2H read-back of band i.  lights_host is a host array; ibl textures
+ * cut into n_bands row bands (0 = 4; the last three shrink by halves so little is left to do after
+ * the last byte has arrived) pipelined over two internal streams, so the H2D copy of band i+1 overlaps the
+ * shading and D2H read-back of band i.  lights_host is a host array; ibl textures
  * are device-resident (precomputed once).  Host planes should be pinned.  Synchronises before return. */
 int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,
                            const void* albedo_host, const void* orm_host, const void* emissive_host,

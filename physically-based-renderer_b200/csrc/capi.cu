@@ -295,6 +295,16 @@ static int ensure_pipe(pbrcu_ctx* ctx) {
   return PBRCU_OK;
 }
 
+// First row of band b of n: equal bands, except that the last three shrink by halves (8, .., 8, 4, 2, 1 units).  What is left
+// to do after the frame's last byte has arrived -- shading and reading back the final band -- is then a forty-seventh of the
+// frame at n = 8, not an eighth, for the same number of copies.
+static uint32_t host_band_row(uint32_t height, uint32_t b, uint32_t n) {
+  if (n < 4) return uint32_t(uint64_t(height) * b / n);
+  const uint32_t body = 8 * (n - 3), units = body + 7;
+  const uint32_t u = b <= n - 3 ? 8 * b : b == n - 2 ? body + 4 : b == n - 1 ? body + 6 : units;
+  return uint32_t(uint64_t(height) * u / units);
+}
+
 extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,
                                       const void* albedo_host, const void* orm_host, const void* emissive_host,
                                       uint32_t width, uint32_t height, const float cam_pos[3],
@@ -303,7 +313,7 @@ extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host
   PBRCU_REQUIRE(ctx && positions_host && normals_host && albedo_host && orm_host && emissive_host && cam_pos && hdr_out_host, "NULL argument");
   PBRCU_REQUIRE(width > 0 && height > 0, "empty extent");
   PBRCU_REQUIRE(n_lights == 0 || lights_host, "lights_host is NULL");
-  if (n_bands == 0) n_bands = 8;
+  if (n_bands == 0) n_bands = 4;
   if (n_bands > 64) n_bands = 64;
   if (n_bands > height) n_bands = height;
   cudaStream_t st = static_cast<cudaStream_t>(s);
@@ -332,7 +342,7 @@ extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host
   // share it and every band would arrive late), copies-out overlap them on the other direction of the link.
   cudaStream_t in = ctx->pipe[0], work = ctx->pipe[1];
   for (uint32_t b = 0; b < n_bands; ++b) {
-    const uint32_t y0 = uint32_t(uint64_t(height) * b / n_bands), y1 = uint32_t(uint64_t(height) * (b + 1) / n_bands);
+    const uint32_t y0 = host_band_row(height, b, n_bands), y1 = host_band_row(height, b + 1, n_bands);
     if (y1 == y0) continue;
     for (int i = 0; i < 5; ++i) {
       const size_t pitch = (i == 3) ? p4 : p8;
