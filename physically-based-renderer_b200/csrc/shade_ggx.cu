@@ -61,7 +61,12 @@ struct ShadeParams {
 
 // the finished texel: streamed to the local frame and to every replica; or ONE multimem store to a multicast address,
 // which the NVSwitch delivers to the frame of every GPU bound to it (this one included)
+template <bool PEERS>
 __device__ __forceinline__ void store_texel(const ShadeParams& p, size_t off, uint2 v) {
+  if (!PEERS) {  // the single-GPU kernels carry none of the bookkeeping below
+    stg_stream8(p.out + off, v);
+    return;
+  }
   if (p.out_is_multicast) {
     const unsigned long long bits = (static_cast<unsigned long long>(v.y) << 32) | v.x;
     asm volatile("multimem.st.weak.global.b64 [%0], %1;" ::"l"(p.out + off), "l"(bits) : "memory");
@@ -226,7 +231,7 @@ __device__ __forceinline__ void light_pair_b(const LightPixel& s, const PairA& a
   bb = fma2(Fb, sub2(dv, dup(s.cdpb)), dup(s.cdpb));
 }
 
-template <int IBL, int LISTS>
+template <int IBL, int LISTS, bool PEERS = false>
 __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kernel(const __grid_constant__ ShadeParams p) {
   constexpr bool ONE_LIST = LISTS != LIST_TILED, BATCHED = LISTS == LIST_ONE_BATCHED;
   // staged lights, two per entry (lane 0 = light 2j, lane 1 = light 2j+1):
@@ -398,7 +403,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     if (!inside) continue;
     const size_t outo = size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
     if (!lit) {
-      store_texel(p, outo, make_uint2(0u, 0u));
+      store_texel<PEERS>(p, outo, make_uint2(0u, 0u));
       continue;
     }
     // ---- ambient: split-sum image-based lighting (Karis 2013) ----
@@ -448,7 +453,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     }
     // oracle order: (direct + ambient) + emissive
     Lr = fminf((dr + ar) + Lr, 65504.0f); Lg = fminf((dg + ag) + Lg, 65504.0f); Lb = fminf((db + ab) + Lb, 65504.0f);
-    store_texel(p, outo, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+    store_texel<PEERS>(p, outo, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
   }
   cp_async_wait<0>();
 }
@@ -476,7 +481,7 @@ __device__ __forceinline__ Quad6 ldg_rec256(const uint4* p) {
 // scattered 256-bit load and a 24-instruction filter.  The unit's 8-bit weights cost at most 2/512 of the footprint's value
 // range; an irradiance footprint whose range exceeds 12 % of its minimum (the flag in the texture's alpha; error below
 // 4.7e-4 relative otherwise) is re-filtered from its record.  The prefiltered cube keeps fp32 weights from the records in every mode.
-template <bool BATCHED, bool AMBTEX>
+template <bool BATCHED, bool AMBTEX, bool PEERS = false>
 __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_kernel(const __grid_constant__ ShadeParams p) {
   __shared__ float4 s_lp[kLightChunk];
   __shared__ float4 s_lc[kLightChunk];
@@ -534,7 +539,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
     const uint2 tn = st.px[1][threadIdx.x];
     const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
     if (nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f) {  // all-zero normal = cleared texel
-      store_texel(p, outo, make_uint2(0u, 0u));
+      store_texel<PEERS>(p, outo, make_uint2(0u, 0u));
       continue;
     }
     // ---- per-pixel set-up (glTF 2.0 Appendix B material model) ----
@@ -650,7 +655,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
     const float base_a = unorm16_hi(st.px[2][threadIdx.x].y);
     // oracle order: (direct + ambient) + emissive
     const float Lr = fminf((dr + ar) + exy.x, 65504.0f), Lg = fminf((dg + ag) + exy.y, 65504.0f), Lb = fminf((db + ab) + ezw.x, 65504.0f);
-    store_texel(p, outo, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+    store_texel<PEERS>(p, outo, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
   }
   cp_async_wait<0>();
 }
@@ -765,8 +770,11 @@ extern "C" int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on) {
 
 template <int IBL>
 static void launch_shade(const ShadeParams& p, int lists, uint32_t grid, cudaStream_t st) {
+  const bool peers = p.n_replicas != 0 || p.out_is_multicast;  // single view only (shade_common)
   if (lists == LIST_ONE_BATCHED) shade_ggx_kernel<IBL, LIST_ONE_BATCHED><<<grid, kShadeThreads, 0, st>>>(p);
+  else if (lists == LIST_ONE && peers) shade_ggx_kernel<IBL, LIST_ONE, true><<<grid, kShadeThreads, 0, st>>>(p);
   else if (lists == LIST_ONE) shade_ggx_kernel<IBL, LIST_ONE><<<grid, kShadeThreads, 0, st>>>(p);
+  else if (peers) shade_ggx_kernel<IBL, LIST_TILED, true><<<grid, kShadeThreads, 0, st>>>(p);
   else shade_ggx_kernel<IBL, LIST_TILED><<<grid, kShadeThreads, 0, st>>>(p);
 }
 
@@ -837,6 +845,9 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
     if (lists == LIST_ONE_BATCHED) {
       if (ambtex) shade_ggx_one_kernel<true, true><<<grid, kShadeThreads, 0, st>>>(p);
       else shade_ggx_one_kernel<true, false><<<grid, kShadeThreads, 0, st>>>(p);
+    } else if (p.n_replicas != 0 || p.out_is_multicast) {
+      if (ambtex) shade_ggx_one_kernel<false, true, true><<<grid, kShadeThreads, 0, st>>>(p);
+      else shade_ggx_one_kernel<false, false, true><<<grid, kShadeThreads, 0, st>>>(p);
     } else {
       if (ambtex) shade_ggx_one_kernel<false, true><<<grid, kShadeThreads, 0, st>>>(p);
       else shade_ggx_one_kernel<false, false><<<grid, kShadeThreads, 0, st>>>(p);
