@@ -601,3 +601,32 @@ def test_prefilter_replicated_stores_build_the_whole_chain(dev, oracle, exact):
     dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
     for b in (whole, *chains):
         b.free()
+
+
+@pytest.mark.parametrize("w,h,bands", [(37, 1, 0), (64, 3, 8), (200, 4, 4), (130, 7, 4), (256, 33, 0), (160, 90, 8), (96, 70, 64), (320, 180, 1)])
+def test_shade_frame_host_equals_the_device_path(pbr, dev, oracle, w, h, bands):
+    """pbrcu_shade_frame_host (the e2e call of the headline metric: host planes in, HDR frame out, tapered row bands pipelined
+    over two streams) must return the bits of pbrcu_shade_ggx_ibl on the same inputs -- at heights smaller than the band
+    count, bands that come out empty, one band, and the 64-band maximum; and must leave the bytes after the frame alone."""
+    host, bufs = build_ibl(dev, oracle)
+    g = synth_gbuffer(w, h, seed=11 * w + h, tier_b=True)
+    nl = 5
+    lights = synth_lights(nl, seed=6)
+    ld = dev.upload(lights)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    cam = pbr.f3(0.5, -1.0, 12.0)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    out = dev.alloc(w * h * 8)
+    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), cam, ld.ptr, nl, None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
+    dev.sync()
+    want = out.download((h, w, 4), np.uint16)
+    planes = {k: np.ascontiguousarray(g[k]) for k in ("pos", "nrm", "alb", "orm", "emi")}
+    got = np.full((h + 2, w, 4), 0x7B7B, np.uint16)  # two guard rows after the frame
+    for _ in range(2):  # twice: the staging buffers and events are reused
+        dev.lib.shade_frame_host(dev.ctx, planes["pos"].ctypes.data, planes["nrm"].ctypes.data, planes["alb"].ctypes.data, planes["orm"].ctypes.data,
+                                 planes["emi"].ctypes.data, w, h, cam, lights.ctypes.data, nl, C.byref(ibl), got.ctypes.data, bands, None)
+        assert np.array_equal(got[:h], want), f"{np.count_nonzero(got[:h] != want)} values differ from the device path"
+        assert (got[h:] == 0x7B7B).all(), "wrote past the frame"
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+    for b in (out, ld, *bufs):
+        b.free()
