@@ -648,6 +648,14 @@ def main_ours(args):
     e2e_steps = max(3, min(args.steps, 20))
     ms_e2e = run_e2e(scene, torch, dist, host, out, e2e_steps, 3)
     e2e_value = world * px_step * e2e_steps / (ms_e2e * 1e-3) / 1e6
+    # the reference's own frame (Tier A) through host buffers, same protocol
+    ldr_host = torch.empty(W4K * H4K * 4, dtype=torch.uint8, pin_memory=True)
+
+    def step_a_host(_):
+        dev.lib.frame_host(dev.ctx, host["positions"].data_ptr(), host["normals"].data_ptr(), host["albedo"].data_ptr(), W4K, H4K, pbr.f3(*CAM),
+                           out.data_ptr(), ldr_host.data_ptr(), scene.stream())
+
+    ms_a_e2e = timed(torch, dist, step_a_host, e2e_steps, 3)
     clocks = sampler.stop()
 
     extra = None if args.no_extra else extra_configs(scene, torch, dist, world, rank)
@@ -680,7 +688,9 @@ def main_ours(args):
                        "lighting_mpix_s": round(world * px_step * args.steps / (ms_k1 * 1e-3) / 1e6, 1),
                        "lighting_gbs": round(k1_gbs, 1), "lighting_roofline_frac": round(k1_gbs / peak, 4),
                        "fused_ldr_mpix_s": round(world * px_step * args.steps / (ms_fused * 1e-3) / 1e6, 1),
-                       "fused_ldr_roofline_frac": round(28 * px_step * args.steps / (ms_fused * 1e-3) / 1e9 / peak, 4)},
+                       "fused_ldr_roofline_frac": round(28 * px_step * args.steps / (ms_fused * 1e-3) / 1e9 / peak, 4),
+                       "frame_host_mpix_s": round(world * px_step * e2e_steps / (ms_a_e2e * 1e-3) / 1e6, 1),
+                       "frame_host": "pbrcu_frame_host: three pinned host planes in (24 B/px), lighting + ACES tonemap, HDR and LDR frames out (12 B/px), 4 tapered row bands"},
             "other_configs": extra,
             "ibl_precompute_ms": scene.ibl_ms,
             "prefilter_error": scene.prefilter_error,

@@ -250,39 +250,6 @@ static int ensure_stage(pbrcu_ctx* ctx, int i, size_t bytes) {
   return PBRCU_OK;
 }
 
-extern "C" int pbrcu_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,
-                                const void* albedo_host, uint32_t width, uint32_t height,
-                                const float cam_pos[3], void* hdr_out_host, void* ldr_out_host,
-                                pbrcu_stream s) {
-  PBRCU_REQUIRE(ctx && positions_host && normals_host && albedo_host && cam_pos, "NULL argument");
-  PBRCU_REQUIRE(width > 0 && height > 0, "empty extent");
-  PBRCU_REQUIRE(hdr_out_host || ldr_out_host, "no output requested");
-  cudaStream_t st = static_cast<cudaStream_t>(s);
-  size_t b8 = size_t(width) * height * 8, b4 = size_t(width) * height * 4;
-  int rc;
-  for (int i = 0; i < 3; ++i)
-    if ((rc = ensure_stage(ctx, i, b8))) return rc;
-  if (hdr_out_host && (rc = ensure_stage(ctx, 3, b8))) return rc;
-  if (ldr_out_host && (rc = ensure_stage(ctx, 4, b4))) return rc;
-  PBRCU_CUDA(cudaMemcpyAsync(ctx->stage[0], positions_host, b8, cudaMemcpyHostToDevice, st));
-  PBRCU_CUDA(cudaMemcpyAsync(ctx->stage[1], normals_host, b8, cudaMemcpyHostToDevice, st));
-  PBRCU_CUDA(cudaMemcpyAsync(ctx->stage[2], albedo_host, b8, cudaMemcpyHostToDevice, st));
-  pbrcu_gbuffer g{};
-  g.positions = ctx->stage[0]; g.normals = ctx->stage[1]; g.albedo = ctx->stage[2];
-  g.width = width; g.height = height; g.pitch8 = size_t(width) * 8; g.pitch4 = size_t(width) * 4;
-  pbrcu_rect all{0, 0, 0, 0};
-  if (ldr_out_host)
-    rc = pbrcu_lighting_tonemap_fused(ctx, &g, cam_pos, all, hdr_out_host ? ctx->stage[3] : nullptr,
-                                      size_t(width) * 8, ctx->stage[4], size_t(width) * 4, s);
-  else
-    rc = pbrcu_lighting_blinnphong(ctx, &g, cam_pos, all, ctx->stage[3], size_t(width) * 8, s);
-  if (rc) return rc;
-  if (hdr_out_host) PBRCU_CUDA(cudaMemcpyAsync(hdr_out_host, ctx->stage[3], b8, cudaMemcpyDeviceToHost, st));
-  if (ldr_out_host) PBRCU_CUDA(cudaMemcpyAsync(ldr_out_host, ctx->stage[4], b4, cudaMemcpyDeviceToHost, st));
-  PBRCU_CUDA(cudaStreamSynchronize(st));
-  return PBRCU_OK;
-}
-
 // ---- one GGX+IBL frame through host buffers, pipelined in row bands ---------------------------
 static int ensure_pipe(pbrcu_ctx* ctx) {
   if (ctx->pipe[0]) return PBRCU_OK;
@@ -303,6 +270,68 @@ static uint32_t host_band_row(uint32_t height, uint32_t b, uint32_t n) {
   const uint32_t body = 8 * (n - 3), units = body + 7;
   const uint32_t u = b <= n - 3 ? 8 * b : b == n - 2 ? body + 4 : b == n - 1 ? body + 6 : units;
   return uint32_t(uint64_t(height) * u / units);
+}
+
+// The reference's frame (lighting.glsl then aces+gamma.glsl) through host buffers.  Frames of half a megapixel or more are cut
+// into 4 tapered row bands and pipelined like pbrcu_shade_frame_host: copies-in back to back on one stream, the fused
+// K1+K2 launch and the read-back of each band on the other.  Smaller frames (the viewer's) go in one piece on the caller's stream.
+extern "C" int pbrcu_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,
+                                const void* albedo_host, uint32_t width, uint32_t height,
+                                const float cam_pos[3], void* hdr_out_host, void* ldr_out_host,
+                                pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && positions_host && normals_host && albedo_host && cam_pos, "NULL argument");
+  PBRCU_REQUIRE(width > 0 && height > 0, "empty extent");
+  PBRCU_REQUIRE(hdr_out_host || ldr_out_host, "no output requested");
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  const size_t p8 = size_t(width) * 8, p4 = size_t(width) * 4;
+  int rc;
+  for (int i = 0; i < 3; ++i)
+    if ((rc = ensure_stage(ctx, i, p8 * height))) return rc;
+  if (hdr_out_host && (rc = ensure_stage(ctx, 3, p8 * height))) return rc;
+  if (ldr_out_host && (rc = ensure_stage(ctx, 4, p4 * height))) return rc;
+  const bool piped = uint64_t(width) * height >= (1u << 19) && height >= 4;
+  const uint32_t n_bands = piped ? 4 : 1;
+  cudaStream_t in = st, work = st;
+  if (piped) {
+    if ((rc = ensure_pipe(ctx))) return rc;
+    in = ctx->pipe[0]; work = ctx->pipe[1];
+    PBRCU_CUDA(cudaEventRecord(ctx->pipe_start, st));
+    for (int i = 0; i < 2; ++i) PBRCU_CUDA(cudaStreamWaitEvent(ctx->pipe[i], ctx->pipe_start, 0));
+  }
+  pbrcu_gbuffer g{};
+  g.positions = ctx->stage[0]; g.normals = ctx->stage[1]; g.albedo = ctx->stage[2];
+  g.width = width; g.height = height; g.pitch8 = p8; g.pitch4 = p4;
+  const void* src[3] = {positions_host, normals_host, albedo_host};
+  for (uint32_t b = 0; b < n_bands; ++b) {
+    const uint32_t y0 = host_band_row(height, b, n_bands), y1 = host_band_row(height, b + 1, n_bands);
+    if (y1 == y0) continue;
+    for (int i = 0; i < 3; ++i)
+      PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(ctx->stage[i]) + y0 * p8, static_cast<const uint8_t*>(src[i]) + y0 * p8,
+                                 size_t(y1 - y0) * p8, cudaMemcpyHostToDevice, in));
+    if (piped) {
+      PBRCU_CUDA(cudaEventRecord(ctx->band_ready[b], in));
+      PBRCU_CUDA(cudaStreamWaitEvent(work, ctx->band_ready[b], 0));
+    }
+    const pbrcu_rect band{0, y0, width, y1 - y0};
+    if (ldr_out_host)
+      rc = pbrcu_lighting_tonemap_fused(ctx, &g, cam_pos, band, hdr_out_host ? ctx->stage[3] : nullptr, p8, ctx->stage[4], p4, work);
+    else
+      rc = pbrcu_lighting_blinnphong(ctx, &g, cam_pos, band, ctx->stage[3], p8, work);
+    if (rc) return rc;
+    if (hdr_out_host)
+      PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(hdr_out_host) + y0 * p8, static_cast<uint8_t*>(ctx->stage[3]) + y0 * p8,
+                                 size_t(y1 - y0) * p8, cudaMemcpyDeviceToHost, work));
+    if (ldr_out_host)
+      PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(ldr_out_host) + y0 * p4, static_cast<uint8_t*>(ctx->stage[4]) + y0 * p4,
+                                 size_t(y1 - y0) * p4, cudaMemcpyDeviceToHost, work));
+  }
+  if (piped)
+    for (int i = 0; i < 2; ++i) {
+      PBRCU_CUDA(cudaEventRecord(ctx->pipe_done[i], ctx->pipe[i]));
+      PBRCU_CUDA(cudaStreamWaitEvent(st, ctx->pipe_done[i], 0));
+    }
+  PBRCU_CUDA(cudaStreamSynchronize(st));
+  return PBRCU_OK;
 }
 
 extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host, const void* normals_host,

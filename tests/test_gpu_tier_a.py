@@ -160,6 +160,31 @@ def test_frame_host(pbr, dev, oracle):
     assert np.abs(ldr.astype(int) - oracle.tonemap(want).astype(int)).max() <= 2
 
 
+@pytest.mark.parametrize("w,h", [(1024, 520), (2000, 263), (640, 360)])
+@pytest.mark.parametrize("outputs", ["hdr+ldr", "hdr", "ldr"])
+def test_frame_host_banded_equals_the_device_path(pbr, dev, oracle, w, h, outputs):
+    """pbrcu_frame_host pipelines frames of half a megapixel or more in four tapered row bands (copies-in on one stream,
+    K1+K2 and the read-back on another); smaller frames go in one piece.  Both must return the bits of the device-side
+    calls on the same planes, for every combination of requested outputs, and leave the rows after the frame alone."""
+    g = synth_gbuffer(w, h, seed=w + 3 * h)
+    cam = pbr.f3(1.0, 2.0, 10.0)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"])
+    hdr_d, ldr_d = dev.alloc(w * h * 8), dev.alloc(w * h * 4)
+    dev.lib.lighting_tonemap_fused(dev.ctx, C.byref(gb), cam, pbr.WHOLE, hdr_d.ptr, w * 8, ldr_d.ptr, w * 4, None)
+    dev.sync()
+    want_hdr, want_ldr = hdr_d.download((h, w, 4), np.uint16), ldr_d.download((h, w, 4), np.uint8)
+    hdr = np.full((h + 1, w, 4), 0x7B7B, np.uint16)
+    ldr = np.full((h + 1, w, 4), 0x7B, np.uint8)
+    for _ in range(2):
+        dev.lib.frame_host(dev.ctx, g["pos"].ctypes.data, g["nrm"].ctypes.data, g["alb"].ctypes.data, w, h, cam,
+                           hdr.ctypes.data if "hdr" in outputs else None, ldr.ctypes.data if "ldr" in outputs else None, None)
+        if "hdr" in outputs:
+            assert np.array_equal(hdr[:h], want_hdr) and (hdr[h:] == 0x7B7B).all()
+        if "ldr" in outputs:
+            assert np.array_equal(ldr[:h], want_ldr) and (ldr[h:] == 0x7B).all()
+    hdr_d.free(); ldr_d.free()
+
+
 def test_full_size_properties(pbr, dev, oracle):
     """BASELINE shapes (4K, 8K) through size-independent properties: device-generated gbuf_spheres,
     cleared texels -> exactly 0, every value in [0, 2], row-band tiling == whole-frame result, and a
