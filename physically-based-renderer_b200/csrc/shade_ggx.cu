@@ -678,10 +678,12 @@ __global__ void __launch_bounds__(kClusterThreads) cluster_lights_kernel(
     const uint32_t y = ty * kTile + 2 * k + (lane >> 4);
     if (x < width && y < height) {
       const size_t o8 = size_t(y) * pitch8 + size_t(x) * 8;
+      // both planes are fetched at once (the position does not wait for the normal's test): all sixteen loads of a lane are
+      // in flight together -- 165 -> 133 us on the 8K frame (scratch/k3c_time.py)
       const uint2 tn = __ldg(reinterpret_cast<const uint2*>(nrm + o8));
+      const uint2 tp = __ldg(reinterpret_cast<const uint2*>(pos + o8));
       const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
       if (!(nxy.x == 0.0f && nxy.y == 0.0f && nzw.x == 0.0f)) {
-        const uint2 tp = __ldg(reinterpret_cast<const uint2*>(pos + o8));
         const float2 pxy = h2_to_f2(tp.x), pzw = h2_to_f2(tp.y);
         mn[0] = fminf(mn[0], pxy.x); mx[0] = fmaxf(mx[0], pxy.x);
         mn[1] = fminf(mn[1], pxy.y); mx[1] = fmaxf(mx[1], pxy.y);
