@@ -1,8 +1,10 @@
 """Host-side partitioning of the hot path across the GPUs of one box.
 
 Every unit of the path is independent (pixels, views, cube texels), so ranks own disjoint, contiguous
-blocks and there is NO data-path collective; NCCL (through torch.distributed) is used only to gather
-finished tiles / faces when a caller wants the whole image on every rank."""
+blocks and there is NO data-path collective.  When a caller wants the whole image (or prefiltered chain) on
+every rank there are two ways: NCCL through torch.distributed (`gather_rows`, `gather_chain`), or -- faster,
+no exchange pass -- the kernels' own stores into the peers' buffers (`PeerFrames` + the C ABI's
+`pbrcu_shade_ggx_ibl_replicated` / `_multicast` / `pbrcu_ibl_prefilter_ggx_replicated`)."""
 from __future__ import annotations
 
 
