@@ -24,6 +24,15 @@ int cuda_fail(cudaError_t e, const char* what) {
   return PBRCU_ERR_CUDA;
 }
 
+bool is_host_pointer(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();  // (pre-CUDA-11 behaviour for unregistered memory)
+    return true;
+  }
+  return a.type == cudaMemoryTypeUnregistered || a.type == cudaMemoryTypeHost;
+}
+
 }  // namespace pbrcu
 
 using namespace pbrcu;
@@ -352,13 +361,6 @@ extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host
   for (int i = 0; i < 6; ++i)
     if ((rc = ensure_stage(ctx, i, need[i]))) return rc;
   if ((rc = ensure_pipe(ctx))) return rc;
-  if (ctx->lights_cap < n_lights) {
-    if (ctx->lights_dev) PBRCU_CUDA(cudaFree(ctx->lights_dev));
-    ctx->lights_dev = nullptr; ctx->lights_cap = 0;
-    PBRCU_CUDA(cudaMalloc(&ctx->lights_dev, size_t(n_lights) * sizeof(pbrcu_light)));
-    ctx->lights_cap = n_lights;
-  }
-  if (n_lights) PBRCU_CUDA(cudaMemcpyAsync(ctx->lights_dev, lights_host, size_t(n_lights) * sizeof(pbrcu_light), cudaMemcpyHostToDevice, st));
   PBRCU_CUDA(cudaEventRecord(ctx->pipe_start, st));
   for (int i = 0; i < 2; ++i) PBRCU_CUDA(cudaStreamWaitEvent(ctx->pipe[i], ctx->pipe_start, 0));
   pbrcu_gbuffer g{};
@@ -380,7 +382,7 @@ extern "C" int pbrcu_shade_frame_host(pbrcu_ctx* ctx, const void* positions_host
     }
     PBRCU_CUDA(cudaEventRecord(ctx->band_ready[b], in));
     PBRCU_CUDA(cudaStreamWaitEvent(work, ctx->band_ready[b], 0));
-    if ((rc = pbrcu_shade_ggx_ibl(ctx, &g, cam_pos, ctx->lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, y0, width, y1 - y0},
+    if ((rc = pbrcu_shade_ggx_ibl(ctx, &g, cam_pos, lights_host, n_lights, nullptr, ibl, pbrcu_rect{0, y0, width, y1 - y0},
                                   ctx->stage[5], p8, work)))
       return rc;
     PBRCU_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(hdr_out_host) + y0 * p8, static_cast<uint8_t*>(ctx->stage[5]) + y0 * p8,

@@ -46,6 +46,8 @@ struct pbrcu_ctx {
 namespace pbrcu {
 
 void set_error(const char* fmt, ...);
+// true for pageable or pinned HOST memory (entry points that take "device or host" arrays of small records)
+bool is_host_pointer(const void* p);
 int cuda_fail(cudaError_t e, const char* what);
 
 #define PBRCU_CUDA(call)                                         \

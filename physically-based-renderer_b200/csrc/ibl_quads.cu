@@ -39,6 +39,66 @@ static int build_level(const uint2* src, uint4* dst, int res, int faces, int sms
   return launch_check("build_quads8_kernel");
 }
 
+// ---- gather atlases (GatherTex, ibl_quads.cuh) ----
+// one level: every slot texel, gutter included, copies the face texel its coordinates clamp to
+// (grid = (ceil((res + 2) / 32), ceil((res + 2) / 8), faces), block = 32 x 8)
+__global__ void __launch_bounds__(256) build_atlas_kernel(const uint2* __restrict__ src, uint2* __restrict__ atlas, size_t atlas_w, int res,
+                                                          uint32_t ax, uint32_t ay) {
+  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (x < res + 2 && y < res + 2) {
+    const size_t face = blockIdx.z;
+    const int sx = min(max(x - 1, 0), res - 1), sy = min(max(y - 1, 0), res - 1);
+    atlas[(size_t(ay) + face * size_t(res + 2) + y) * atlas_w + ax + x] = __ldg(src + (face * res + sy) * size_t(res) + sx);
+  }
+}
+
+void gather_tex_destroy(GatherTex* t) {
+  if (t->tex) cudaDestroyTextureObject(t->tex);
+  if (t->array) cudaFreeArray(t->array);
+  t->tex = 0; t->array = nullptr; t->width = t->height = 0;
+}
+
+// chain: `faces` faces per level, 8-byte texels (RGBA16F, or RG32F when rg32f); builds the atlas in a stream-ordered
+// staging buffer and copies it into a 2-D array created for texture gathers
+static int gather_tex_build(pbrcu_ctx* ctx, GatherTex* t, const void* chain, uint32_t base_res, uint32_t nmips, uint32_t faces, bool rg32f,
+                            cudaStream_t st) {
+  uint32_t w, h;
+  atlas_extent(base_res, nmips, faces, w, h);
+  cudaDeviceProp prop;
+  PBRCU_CUDA(cudaGetDeviceProperties(&prop, ctx->device));
+  if (int(w) > prop.maxTexture2DGather[0] || int(h) > prop.maxTexture2DGather[1]) {
+    set_error("gather atlas of %u x %u texels exceeds the device's texture-gather limit (%d x %d)", w, h, prop.maxTexture2DGather[0], prop.maxTexture2DGather[1]);
+    return PBRCU_ERR_INVALID;
+  }
+  const cudaChannelFormatDesc fmt = rg32f ? cudaCreateChannelDesc<float2>() : cudaCreateChannelDescHalf4();
+  PBRCU_CUDA(cudaMallocArray(&t->array, &fmt, w, h, cudaArrayTextureGather));
+  t->width = w; t->height = h;
+  uint2* stage = nullptr;
+  PBRCU_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&stage), size_t(w) * h * 8, st));
+  PBRCU_CUDA(cudaMemsetAsync(stage, 0, size_t(w) * h * 8, st));
+  const uint2* src = static_cast<const uint2*>(chain);
+  size_t off = 0;
+  for (uint32_t m = 0; m < nmips; ++m) {
+    const AtlasLevel a = atlas_level(base_res, m);
+    const dim3 grid((a.res + 2 + 31) / 32, (a.res + 2 + 7) / 8, faces);
+    build_atlas_kernel<<<grid, dim3(32, 8), 0, st>>>(src + off, stage, w, int(a.res), a.ax, a.ay);
+    off += size_t(faces) * a.res * a.res;
+  }
+  if (int rc = launch_check("build_atlas_kernel")) return rc;
+  PBRCU_CUDA(cudaMemcpy2DToArrayAsync(t->array, 0, 0, stage, size_t(w) * 8, size_t(w) * 8, h, cudaMemcpyDeviceToDevice, st));
+  PBRCU_CUDA(cudaFreeAsync(stage, st));
+  cudaResourceDesc rd{};
+  rd.resType = cudaResourceTypeArray;
+  rd.res.array.array = t->array;
+  cudaTextureDesc td{};
+  td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+  td.filterMode = cudaFilterModeLinear;  // (a gather always takes the bilinear footprint; the kernels pass its exact centre)
+  td.readMode = cudaReadModeElementType;
+  td.normalizedCoords = 0;
+  PBRCU_CUDA(cudaCreateTextureObject(&t->tex, &rd, &td, nullptr));
+  return PBRCU_OK;
+}
+
 }  // namespace pbrcu
 
 using namespace pbrcu;
@@ -49,6 +109,9 @@ extern "C" int pbrcu_ibl_accel_free(pbrcu_ctx* ctx, pbrcu_ibl_accel* a) {
   if (a->pref) cudaFree(a->pref);
   if (a->irr) cudaFree(a->irr);
   if (a->lut) cudaFree(a->lut);
+  gather_tex_destroy(&a->g_pref);
+  gather_tex_destroy(&a->g_irr);
+  gather_tex_destroy(&a->g_lut);
   cube_tex_destroy(&a->pref_tex);
   cube_tex_destroy(&a->irr_tex);
   if (a->lut_tex) cudaDestroyTextureObject(a->lut_tex);
@@ -124,6 +187,13 @@ extern "C" int pbrcu_ibl_accel_build(pbrcu_ctx* ctx, const pbrcu_ibl* ibl, pbrcu
     }
     a->bytes += n_lut * 8;
   }
+  if ((rc = gather_tex_build(ctx, &a->g_pref, ibl->prefiltered, ibl->pref_res, ibl->pref_mips, 6, false, st)) ||
+      (rc = gather_tex_build(ctx, &a->g_irr, ibl->irradiance, ibl->irr_res, 1, 6, false, st)) ||
+      (rc = gather_tex_build(ctx, &a->g_lut, ibl->lut, ibl->lut_res, 1, 1, true, st))) {
+    pbrcu_ibl_accel_free(ctx, a);
+    return rc;
+  }
+  a->bytes += (size_t(a->g_pref.width) * a->g_pref.height + size_t(a->g_irr.width) * a->g_irr.height + size_t(a->g_lut.width) * a->g_lut.height) * 8;
   *out = a;
   return PBRCU_OK;
 }

@@ -10,7 +10,41 @@
 #pragma once
 #include "cube_tex.cuh"
 
+namespace pbrcu {
+// A texture the shading kernels read with GATHERS (tld4: the four texels of a bilinear footprint, one channel per
+// instruction, converted to fp32 by the texture unit) and filter with their own fp32 weights -- the unit does the
+// addressing, the edge clamp and the fp16 unpack, the result is bit-identical to cube.cuh's four-load face_bilinear.
+// Layout ("atlas", one 2-D array because tld4 has neither layers nor levels): every face of every level is stored with
+// a one-texel gutter that repeats its edge texels (clamp-to-edge without any clamp arithmetic), i.e. in a slot of
+// (res + 2)^2 texels; level 0's six slots are stacked in a first column, the slots of levels 1.. in a second one.
+// Texel (i, j), i, j in [-1, res], of face f of level l lives at (ax_l + 1 + i, ay_l + f (res_l + 2) + 1 + j); the
+// footprint whose origin is (i0, j0) is gathered at the corner its four texels share, (ax_l + i0 + 2, ay_l + f (res_l + 2) + j0 + 2).
+struct GatherTex {
+  cudaArray_t array;
+  cudaTextureObject_t tex;
+  uint32_t width, height;
+};
+struct AtlasLevel { uint32_t res, ax, ay; };
+inline AtlasLevel atlas_level(uint32_t base_res, uint32_t level) {
+  AtlasLevel a{base_res >> level, 0u, 0u};
+  if (level >= 1) {
+    a.ax = base_res + 2;
+    for (uint32_t k = 1; k < level; ++k) a.ay += 6 * ((base_res >> k) + 2);
+  }
+  return a;
+}
+inline void atlas_extent(uint32_t base_res, uint32_t nmips, uint32_t faces, uint32_t& w, uint32_t& h) {
+  w = base_res + 2 + (nmips > 1 ? (base_res >> 1) + 2 : 0);
+  uint32_t h1 = 0;
+  for (uint32_t k = 1; k < nmips; ++k) h1 += faces * ((base_res >> k) + 2);
+  h = faces * (base_res + 2);
+  if (h1 > h) h = h1;
+}
+}  // namespace pbrcu
+
 struct pbrcu_ibl_accel {
+  // gather atlases of the prefiltered chain, the irradiance map (both RGBA16F) and the LUT (RG32F, one face, one level)
+  pbrcu::GatherTex g_pref, g_irr, g_lut;
   uint4* pref;      // chain_texels(pref_res, pref_mips) records, same level/face/row order as the chain
   uint4* irr;       // 6*irr_res^2 records
   uint4* lut;       // lut_res^2 records of 4 x float2
