@@ -43,11 +43,19 @@ private:
   core::SharedGpuHandle _gpu;
   PbrRenderSystemCreateInfo _info;
   std::shared_ptr<Environment const> _environment;
-  Allocation _lightsDevice;  // grown on demand
+  Allocation _lightsDevice;  // grown on demand (clustered shading only: short light lists travel in the kernel's parameters)
   std::size_t _lightsCapacity {};
+  pbrcu_light_tiles _tiles {};  // per-tile light lists of the clustered pass, re-allocated when the extent or the light count grows
+  std::uint32_t _tilesWidth {}, _tilesHeight {};
 
 public:
+  // more lights than this are culled per 16x16 tile first (K3c, pbrcu_cluster_lights) instead of being looped by every pixel
+  static constexpr std::size_t CLUSTERED_LIGHTS_THRESHOLD = 8;
+
   PbrRenderSystem(core::SharedGpuHandle gpu, PbrRenderSystemCreateInfo info) : _gpu(std::move(gpu)), _info(info) {}
+  PbrRenderSystem(PbrRenderSystem const&) = delete;
+  auto operator=(PbrRenderSystem const&) -> PbrRenderSystem& = delete;
+  ~PbrRenderSystem() { (void)pbrcu_light_tiles_free(_gpu ? _gpu->getContext() : nullptr, &_tiles); }
 
   [[nodiscard]] auto allocateGBuffer(IAllocator& allocator, vk::Extent2D extent) -> GBuffer {
     return GBuffer {allocator, extent, _info.shadingModel == ShadingModel::MetallicRoughness};
@@ -125,8 +133,7 @@ private:
     // drawn when the scene has no camera (:486-499)
     auto const camera = scene.findCamera();
     if (!camera) {
-      for (std::uint32_t y = 0; y < rect.h; ++y)
-        core::check(pbrcu_memset(static_cast<char*>(target.data) + y * target.pitch, 0, std::size_t(rect.w) * 8, stream), "PbrRenderSystem: clear");
+      core::check(pbrcu_memset_2d(target.data, target.pitch, 0, std::size_t(rect.w) * 8, rect.h, stream), "PbrRenderSystem: clear");
       return;
     }
     if (rect.w == 0 || rect.h == 0) return;
@@ -140,6 +147,16 @@ private:
     if (!gBuffer.isExtended())
       throw std::runtime_error("pbr::PbrRenderSystem::render: MetallicRoughness shading needs an extended G-buffer");
     auto const lights = scene.getLights();
+    auto const nLights = static_cast<std::uint32_t>(lights.size());
+    pbrcu_ibl ibl {};
+    if (_environment) ibl = _environment->raw();
+    if (lights.size() <= CLUSTERED_LIGHTS_THRESHOLD) {
+      // a short list goes to the kernel as HOST data (it travels in the kernel's parameter block: no upload, no staging)
+      core::check(pbrcu_shade_ggx_ibl(ctx, &g, cam, reinterpret_cast<pbrcu_light const*>(lights.data()), nLights, nullptr, _environment ? &ibl : nullptr, rect, target.data, target.pitch, stream),
+                  "PbrRenderSystem: GGX shading pass");
+      return;
+    }
+    // many lights: per-tile light lists first (K3c), then every pixel loops its tile's list only
     if (lights.size() > _lightsCapacity) {
       _lightsDevice = Allocation {};
       void* p = nullptr;
@@ -147,13 +164,15 @@ private:
       _lightsDevice = Allocation {_gpu, p, lights.size() * sizeof(pbrcu_light), false};
       _lightsCapacity = lights.size();
     }
-    if (!lights.empty())
-      core::check(pbrcu_memcpy_h2d(_lightsDevice.get(), lights.data(), lights.size() * sizeof(pbrcu_light), stream), "PbrRenderSystem: light upload");
-    pbrcu_ibl ibl {};
-    if (_environment) ibl = _environment->raw();
-    core::check(pbrcu_shade_ggx_ibl(ctx, &g, cam, static_cast<pbrcu_light const*>(_lightsDevice.get()),
-                                    static_cast<std::uint32_t>(lights.size()), nullptr, _environment ? &ibl : nullptr, rect,
-                                    target.data, target.pitch, stream),
+    core::check(pbrcu_memcpy_h2d(_lightsDevice.get(), lights.data(), lights.size() * sizeof(pbrcu_light), stream), "PbrRenderSystem: light upload");
+    if (_tilesWidth != ext.width || _tilesHeight != ext.height || _tiles.max_per_tile < nLights) {
+      core::check(pbrcu_light_tiles_free(ctx, &_tiles), "PbrRenderSystem: light tiles");
+      core::check(pbrcu_light_tiles_alloc(ctx, ext.width, ext.height, nLights < 1024 ? nLights : 1024, &_tiles), "PbrRenderSystem: light tiles");
+      _tilesWidth = ext.width; _tilesHeight = ext.height;
+    }
+    auto const* lightsDev = static_cast<pbrcu_light const*>(_lightsDevice.get());
+    core::check(pbrcu_cluster_lights(ctx, &g, lightsDev, nLights, &_tiles, stream), "PbrRenderSystem: light clustering");
+    core::check(pbrcu_shade_ggx_ibl(ctx, &g, cam, lightsDev, nLights, &_tiles, _environment ? &ibl : nullptr, rect, target.data, target.pitch, stream),
                 "PbrRenderSystem: GGX shading pass");
   }
 };

@@ -85,9 +85,9 @@ public:
     }
     for (auto const& t : _imageTransfers) {
       std::memcpy(staging + offset, t.data.data(), t.data.size());
-      for (std::uint32_t y = 0; y < t.rows; ++y)
-        core::check(pbrcu_memcpy_h2d(static_cast<char*>(t.image.data) + y * t.image.pitch, staging + offset + y * t.rowBytes, t.rowBytes, cmdBuffer.stream()),
-                    "TransferStager: image copy");
+      // one pitched copy per image (the staging rows are tightly packed, the image rows pitch apart)
+      core::check(pbrcu_memcpy_h2d_2d(t.image.data, t.image.pitch, staging + offset, t.rowBytes, t.rowBytes, t.rows, cmdBuffer.stream()),
+                  "TransferStager: image copy");
       offset += t.data.size();
     }
     _bufferTransfers.clear();

@@ -45,6 +45,8 @@ class Asset {
   }
 
 public:
+  static constexpr std::size_t MAX_NODE_DEPTH = 256;
+
   Asset(Document asset, AssetDependencies dependencies) noexcept : _dependencies(std::move(dependencies)), _asset(std::move(asset)) {}
 
   [[nodiscard]] auto getDocument() const noexcept -> Document const& { return _asset; }
@@ -104,6 +106,9 @@ public:
       indices.resize(vertices.size());
       for (std::size_t i = 0; i < indices.size(); ++i) indices[i] = static_cast<std::uint16_t>(i);
     }
+    // K10 addresses its vertex cache at vertex_offset + index: an index past the primitive's vertices (a malformed or
+    // hostile file) would read another draw's vertices or run off the buffer
+    Document::requireIndicesBelow(indices, vertices.size());
     MeshBuilder::Primitive out;
     out.material = loadMaterial(stager, need(primitive.material, "primitive without a material"));
     out.vertices = std::move(vertices);
@@ -127,7 +132,9 @@ public:
     return mesh;
   }
 
-  [[nodiscard]] auto loadNode(TransferStager& stager, std::size_t index, std::pmr::polymorphic_allocator<> alloc = {}) -> Node {
+  // (depth: a node graph with a cycle, or an absurdly deep one, is rejected instead of overflowing the stack)
+  [[nodiscard]] auto loadNode(TransferStager& stager, std::size_t index, std::pmr::polymorphic_allocator<> alloc = {}, std::size_t depth = 0) -> Node {
+    if (depth > MAX_NODE_DEPTH) throw std::runtime_error("glTF node hierarchy deeper than " + std::to_string(MAX_NODE_DEPTH) + " levels (cycle?)");
     auto const& gltfNode = _asset.nodes.at(index);
     auto const& trs = gltfNode.transform;
     Transform const transform {
@@ -136,7 +143,7 @@ public:
         .scale {trs.scale[0], trs.scale[1], trs.scale[2]},
     };
     Node node(std::pmr::string(gltfNode.name, alloc), transform, alloc);
-    for (auto const childIdx : gltfNode.children) node.addChild(loadNode(stager, childIdx, alloc));
+    for (auto const childIdx : gltfNode.children) node.addChild(loadNode(stager, childIdx, alloc, depth + 1));
     if (gltfNode.mesh) node.setMesh(loadMesh(stager, *gltfNode.mesh));
     return node;
   }

@@ -308,6 +308,28 @@ private:
     for (auto const& s : scenes)
       for (auto const n : s.nodes)
         if (n >= nodes.size()) fail("scene node out of range");
+    // glTF 2.0, 3.5.2: the node hierarchy is a set of strict trees.  A cycle (or a child with two parents) would send
+    // the recursive loaders into unbounded recursion; reject it here, iteratively.
+    std::vector<std::uint8_t> hasParent(nodes.size(), 0);
+    for (auto const& n : nodes)
+      for (auto const c : n.children) {
+        if (hasParent[c]) fail("node has more than one parent");
+        hasParent[c] = 1;
+      }
+    std::vector<std::uint8_t> reached(nodes.size(), 0);
+    std::vector<std::size_t> stack;
+    for (std::size_t r = 0; r < nodes.size(); ++r)
+      if (!hasParent[r]) {
+        stack.push_back(r);
+        while (!stack.empty()) {
+          std::size_t const i = stack.back();
+          stack.pop_back();
+          reached[i] = 1;
+          for (auto const c : nodes[i].children) stack.push_back(c);
+        }
+      }
+    for (std::size_t i = 0; i < nodes.size(); ++i)
+      if (!reached[i]) fail("node hierarchy contains a cycle");  // every node of a forest hangs below a parentless root
   }
 
   // one component of one element, converted to double (exactly representable for every component type)
@@ -362,6 +384,23 @@ public:
     return doc;
   }
 
+  // every index of a primitive must address one of its vertices (K10 reads its vertex cache at vertex_offset + index)
+  static auto requireIndicesBelow(std::span<std::uint16_t const> indices, std::size_t vertexCount) -> void {
+    for (auto const idx : indices)
+      if (idx >= vertexCount) fail("primitive index " + std::to_string(idx) + " addresses a vertex past its " + std::to_string(vertexCount) + " vertices");
+  }
+
+  // count elements of elem bytes, stride apart, starting byteOffset bytes into a view of byteLength bytes -- without
+  // the size_t wrap-around a huge count or stride from an untrusted file would cause in (count - 1) * stride + elem
+  [[nodiscard]] static auto accessorFits(std::size_t count, std::size_t byteOffset, std::size_t stride, std::size_t elem, std::size_t byteLength) noexcept
+      -> bool {
+    if (count == 0) return true;
+    if (byteOffset > byteLength || elem > byteLength - byteOffset) return false;
+    if (count == 1) return true;
+    if (stride == 0) return false;
+    return count - 1 <= (byteLength - byteOffset - elem) / stride;
+  }
+
   // fastgltf::iterateAccessorWithIndex<vecN> for float targets: fn(std::array<float, N>, index).  The accessor must
   // have at least N components per element (extra ones are ignored, like reading a VEC4 colour as vec3).
   template <std::size_t N, typename Fn> auto iterateFloats(std::size_t accessorIndex, Fn&& fn) const -> void {
@@ -374,7 +413,7 @@ public:
     }
     BufferView const& bv = bufferViews.at(*a.bufferView);
     std::size_t const elem = csize * std::size_t(a.components), stride = bv.byteStride.value_or(elem);
-    if (a.count > 0 && (a.byteOffset > bv.byteLength || (a.count - 1) * stride + elem > bv.byteLength - a.byteOffset)) fail("accessor outside its bufferView");
+    if (!accessorFits(a.count, a.byteOffset, stride, elem, bv.byteLength)) fail("accessor outside its bufferView");
     std::uint8_t const* base = buffers[bv.buffer].data() + bv.byteOffset + a.byteOffset;
     for (std::size_t i = 0; i < a.count; ++i) {
       std::array<float, N> out {};
@@ -406,7 +445,7 @@ public:
     }
     BufferView const& bv = bufferViews.at(*a.bufferView);
     std::size_t const elem = csize * std::size_t(a.components), stride = bv.byteStride.value_or(elem);
-    if (a.count > 0 && (a.byteOffset > bv.byteLength || (a.count - 1) * stride + elem > bv.byteLength - a.byteOffset)) fail("accessor outside its bufferView");
+    if (!accessorFits(a.count, a.byteOffset, stride, elem, bv.byteLength)) fail("accessor outside its bufferView");
     std::uint8_t const* base = buffers[bv.buffer].data() + bv.byteOffset + a.byteOffset;
     for (std::size_t i = 0; i < a.count; ++i) {
       double const v = component(base + i * stride, a.componentType);

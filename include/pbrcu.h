@@ -23,6 +23,14 @@
  * (a cudaStream_t passed as void*; NULL = the legacy default stream) and is asynchronous.  Buffers
  * are caller-owned device memory unless the name ends in _host.  There is no CPU fallback: without
  * a CUDA device every compute entry point fails with PBRCU_ERR_CUDA.
+ *
+ * Ordering rules.  (1) The allocation calls (pbrcu_gbuffer_alloc, pbrcu_image_alloc) return with their
+ * clears COMPLETE, so the memory may be used on any stream at once.  (2) One stream at a time per
+ * pbrcu_ctx for the entry points that use scratch memory owned by the context: pbrcu_geometry_pass
+ * (visibility buffer, vertex cache), pbrcu_ibl_prefilter_ggx / pbrcu_ibl_irradiance (the texture copy of
+ * the source chain), the *_batched entries (camera table) and the *_host entries (staging planes).  Calls
+ * of these on DIFFERENT streams of one context must be ordered by the caller (an event), or use one
+ * context per stream -- contexts are cheap (no device memory until a scratch is first needed).
  */
 #ifndef PBRCU_H
 #define PBRCU_H
@@ -77,6 +85,10 @@ int pbrcu_host_free(void* ptr);
 int pbrcu_memcpy_h2d(void* dst, const void* src, size_t bytes, pbrcu_stream s);
 int pbrcu_memcpy_d2h(void* dst, const void* src, size_t bytes, pbrcu_stream s);
 int pbrcu_memset(void* dst, int value, size_t bytes, pbrcu_stream s);
+/* pitched forms: `height` rows of `width_bytes` bytes, rows dst_pitch (src_pitch) bytes apart -- one call per image */
+int pbrcu_memset_2d(void* dst, size_t dst_pitch, int value, size_t width_bytes, size_t height, pbrcu_stream s);
+int pbrcu_memcpy_h2d_2d(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes,
+                        size_t height, pbrcu_stream s);
 int pbrcu_stream_create(pbrcu_stream* out);
 int pbrcu_stream_destroy(pbrcu_stream s);
 int pbrcu_stream_synchronize(pbrcu_stream s);

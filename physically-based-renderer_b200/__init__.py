@@ -97,6 +97,8 @@ _SIGNATURES = {
     "pbrcu_memcpy_h2d": (_i, [_vp, _vp, _sz, _vp]),
     "pbrcu_memcpy_d2h": (_i, [_vp, _vp, _sz, _vp]),
     "pbrcu_memset": (_i, [_vp, _i, _sz, _vp]),
+    "pbrcu_memset_2d": (_i, [_vp, _sz, _i, _sz, _sz, _vp]),
+    "pbrcu_memcpy_h2d_2d": (_i, [_vp, _sz, _vp, _sz, _sz, _sz, _vp]),
     "pbrcu_stream_create": (_i, [C.POINTER(_vp)]),
     "pbrcu_stream_destroy": (_i, [_vp]),
     "pbrcu_stream_synchronize": (_i, [_vp]),

@@ -128,6 +128,22 @@ extern "C" int pbrcu_memset(void* dst, int value, size_t bytes, pbrcu_stream s) 
   PBRCU_CUDA(cudaMemsetAsync(dst, value, bytes, static_cast<cudaStream_t>(s)));
   return PBRCU_OK;
 }
+extern "C" int pbrcu_memset_2d(void* dst, size_t dst_pitch, int value, size_t width_bytes, size_t height, pbrcu_stream s) {
+  PBRCU_REQUIRE(dst_pitch >= width_bytes, "pitch smaller than a row");
+  if (width_bytes == 0 || height == 0) return PBRCU_OK;
+  PBRCU_CUDA(cudaMemset2DAsync(dst, dst_pitch, value, width_bytes, height, static_cast<cudaStream_t>(s)));
+  return PBRCU_OK;
+}
+extern "C" int pbrcu_memcpy_h2d_2d(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width_bytes, size_t height,
+                                   pbrcu_stream s) {
+  PBRCU_REQUIRE(dst_pitch >= width_bytes && src_pitch >= width_bytes, "pitch smaller than a row");
+  if (width_bytes == 0 || height == 0) return PBRCU_OK;
+  if (dst_pitch == width_bytes && src_pitch == width_bytes)  // tightly packed on both sides: one linear copy
+    PBRCU_CUDA(cudaMemcpyAsync(dst, src, width_bytes * height, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(s)));
+  else
+    PBRCU_CUDA(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width_bytes, height, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(s)));
+  return PBRCU_OK;
+}
 extern "C" int pbrcu_stream_create(pbrcu_stream* out) {
   PBRCU_REQUIRE(out, "out is NULL");
   cudaStream_t st;
@@ -223,7 +239,11 @@ extern "C" int pbrcu_gbuffer_alloc(pbrcu_ctx* ctx, uint32_t w, uint32_t h, int t
     pbrcu_gbuffer_free(ctx, out);
     return rc;
   }
-  return pbrcu_gbuffer_clear(out, nullptr);
+  // the clear must have landed before the call returns: streams from pbrcu_stream_create are non-blocking and do not
+  // order themselves against the legacy stream, so a clear still in flight could wipe the caller's first upload or pass
+  if ((rc = pbrcu_gbuffer_clear(out, nullptr))) return rc;
+  PBRCU_CUDA(cudaStreamSynchronize(nullptr));
+  return PBRCU_OK;
 }
 
 extern "C" int pbrcu_gbuffer_free(pbrcu_ctx* ctx, pbrcu_gbuffer* g) {
@@ -244,7 +264,8 @@ extern "C" int pbrcu_image_alloc(pbrcu_ctx* ctx, uint32_t w, uint32_t h, uint32_
   *pitch = align_up(size_t(w) * texel_bytes, 128);
   int rc = pbrcu_malloc(ctx, *pitch * h, out);
   if (rc) return rc;
-  PBRCU_CUDA(cudaMemsetAsync(*out, 0, *pitch * h, nullptr));  // render targets start cleared to 0
+  PBRCU_CUDA(cudaMemsetAsync(*out, 0, *pitch * h, nullptr));  // render targets start cleared to 0 ...
+  PBRCU_CUDA(cudaStreamSynchronize(nullptr));                 // ... before the caller's (non-blocking) streams touch them
   return PBRCU_OK;
 }
 

@@ -250,15 +250,6 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
 // Registers for both come from deferring everything only the ambient term needs (tap weights, c_diff, occlusion,
 // emissive, alpha) to shared memory: a small per-thread stash, and the staged tile itself, which stays valid for the
 // whole iteration.  Unlit and outside pixels leave the iteration early instead of carrying neutral values through it.
-__device__ __forceinline__ Quad6 ldg_rec256(const uint4* p) {
-  Quad6 q;
-  uint32_t pad0, pad1;
-  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=r"(q.w[0]), "=r"(q.w[1]), "=r"(q.w[2]), "=r"(q.w[3]), "=r"(q.w[4]), "=r"(q.w[5]), "=r"(pad0), "=r"(pad1)
-               : "l"(p));
-  return q;
-}
-
 // AMBTEX: the two SMOOTH maps of the ambient term -- irradiance (a cosine convolution) and the split-sum LUT -- come from the
 // otherwise idle texture unit: one TEX each (face selection and bilinear in hardware) instead of face / tap arithmetic, a
 // scattered 256-bit load and a 24-instruction filter.  The unit's 8-bit weights cost at most 2/512 of the footprint's value

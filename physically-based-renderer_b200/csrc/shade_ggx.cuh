@@ -134,6 +134,16 @@ __device__ __forceinline__ IblTaps make_ibl_taps(const ShadeParams& p, float3 N,
   return t;
 }
 
+// one 256-bit load of a cube-map record (8 destination registers, 6 in use)
+__device__ __forceinline__ Quad6 ldg_rec256(const uint4* p) {
+  Quad6 q;
+  uint32_t pad0, pad1;
+  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(q.w[0]), "=r"(q.w[1]), "=r"(q.w[2]), "=r"(q.w[3]), "=r"(q.w[4]), "=r"(q.w[5]), "=r"(pad0), "=r"(pad1)
+               : "l"(p));
+  return q;
+}
+
 // ---- cp.async staging of one pixel's five texels into this thread's shared-memory slots ----
 __device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(uint32_t(__cvta_generic_to_shared(smem))), "l"(gmem) : "memory");

@@ -50,6 +50,7 @@ void node(pbr::gltf::Document const& doc, std::size_t index, int depth) {
     std::vector<std::uint16_t> idx;
     if (prim.indices) doc.iterateIndices(*prim.indices, [&](std::uint16_t i) { idx.push_back(i); });
     else for (std::size_t i = 0; i < v.size(); ++i) idx.push_back(std::uint16_t(i));
+    pbr::gltf::Document::requireIndicesBelow(idx, v.size());  // as gltf::Asset::loadPrimitive does
     std::printf("%*sprim vertices %zu indices %zu vhash %016" PRIx64 " ihash %016" PRIx64 " material %zu\n", depth * 2 + 2, "", v.size(), idx.size(),
                 fnv(v.data(), v.size() * sizeof(pbr::MeshVertex)), fnv(idx.data(), idx.size() * 2), prim.material.value());
     auto const& m = doc.materials.at(prim.material.value());

@@ -147,3 +147,47 @@ def test_errors_are_reported(tool, tmp_path):
     rc, _, err = run(tool, tmp_path / "no_tangent.glb")
     assert rc == 2 and "Primitive does not have TANGENT attribute" in err
     assert run(tool, tmp_path / "missing.glb")[0] == 2
+
+
+def test_hostile_assets_are_rejected(tool, tmp_path):
+    """Malformed files must fail in the parser, not in the rasteriser: an index past the primitive's vertices (K10 would read
+    another draw's vertex-cache slots), an accessor whose count * stride wraps size_t, a node graph with a cycle."""
+    import json as js
+    import struct
+
+    def variant(name, edit):
+        b, _ = build_asset()
+        edit(b)
+        for fname, data in b.files.items():
+            (tmp_path / fname).write_bytes(data)
+        path = tmp_path / name
+        b.write_gltf(path, buffer="file")
+        return run(tool, path)
+
+    def bad_index(b):  # patch the first index of the first indexed primitive to 65535
+        doc = b.doc
+        prim = next(p for m in doc["meshes"] for p in m["primitives"] if "indices" in p)
+        acc = doc["accessors"][prim["indices"]]
+        bv = doc["bufferViews"][acc["bufferView"]]
+        off = bv.get("byteOffset", 0) + acc.get("byteOffset", 0)
+        size = {5121: 1, 5123: 2, 5125: 4}[acc["componentType"]]
+        b.bin[off:off + size] = b"\xff" * size
+
+    rc, _, err = variant("bad_index.gltf", bad_index)
+    assert rc == 2 and "addresses a vertex past" in err, err
+
+    def huge_count(b):
+        acc = b.doc["accessors"][0]
+        acc["count"] = (1 << 64) // 12 + 2  # (count - 1) * stride wraps to a small number
+
+    rc, _, err = variant("huge_count.gltf", huge_count)
+    assert rc == 2 and "pbr::gltf" in err, err
+
+    def cycle(b):
+        nodes = b.doc["nodes"]
+        parent = next(i for i, n in enumerate(nodes) if n.get("children"))
+        child = nodes[parent]["children"][0]
+        nodes[child].setdefault("children", []).append(parent)
+
+    rc, _, err = variant("cycle.gltf", cycle)
+    assert rc == 2 and ("cycle" in err or "more than one parent" in err), err

@@ -208,3 +208,23 @@ def test_clip_cache_overflow_falls_back(pbr, dev, oracle, monkeypatch):
     for cap in ("1", "0"):
         monkeypatch.setenv("PBRCU_RASTER_CLIP_CAP", cap)
         assert_same(device_pass(pbr, dev, draws, view, proj, 200, 112), want, f"clip cap {cap}")
+
+
+def test_chunk_queue_overflow_falls_back(pbr, dev, oracle, monkeypatch):
+    """Screen-sized triangles hand their 64 x 32 chunks to the chunk queue.  With the queue forced to overflow (capacity 0,
+    one slot, part of a reservation, exactly one triangle's chunks) the producers that do not fit keep their piece with the
+    warp loop, their reserved slots carry the skip sentinel, and the consumer never reads a slot nobody wrote: same bits."""
+    W, H = 320, 200
+    view, proj = camera(aspect=W / H)
+    g = 40.0
+    quad = np.array([mesh_vertex((-g, -g, 6.0), (0, 0, -1), (1, 0, 0, 1), (0, 0)), mesh_vertex((g, -g, 6.0), (0, 0, -1), (1, 0, 0, 1), (16, 0)),
+                     mesh_vertex((g, g, 6.0), (0, 0, -1), (1, 0, 0, 1), (16, 16)), mesh_vertex((-g, g, 6.0), (0, 0, -1), (1, 0, 0, 1), (0, 16))], np.float32)
+    idx = np.array([0, 1, 2, 0, 2, 3, 0, 2, 1, 0, 3, 2], np.uint16)
+    walls = [make_draw(quad, idx, model_push_constant((0.3 * k, -0.2 * k, float(k)), (1, 1, 1), (0, 0, 1), 0.1 * k), color=(0.9, 0.5 + 0.1 * k, 0.4, 1.0),
+                       color_tex=checker_texture(64, 64, 9 + k)) for k in range(3)]
+    want = oracle.geometry_pass(walls, view, proj, W, H, extended=True)
+    assert (want["prim"] != EMPTY).mean() > 0.9
+    assert_same(device_pass(pbr, dev, walls, view, proj, W, H), want, "full queue")
+    for cap in ("0", "1", "17", "35", "36", "71"):
+        monkeypatch.setenv("PBRCU_RASTER_QUEUE_CAP", cap)
+        assert_same(device_pass(pbr, dev, walls, view, proj, W, H), want, f"chunk queue cap {cap}")
