@@ -10,6 +10,8 @@
 // NEXT tile are staged into shared memory with cp.async while the current tile is shaded, so the DRAM
 // latency of the streaming reads never sits on a warp's critical path; the tile's light list is staged
 // in shared memory; the IBL footprint records of a pixel are prefetched into L1 before its light loop.
+#include <cstdlib>
+
 #include "shade_ggx.cuh"
 
 namespace pbrcu {
@@ -613,7 +615,11 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   // ---- one light list the HOST holds (the headline frame, the batched views, the facade): lights in the kernel's
   // parameter block, IBL by texture gathers (shade_ggx_cl.cu) ----
   const bool host_lights = n_lights == 0 || is_host_pointer(lights_dev);
-  if (!tex && p.tile_counts == nullptr && n_lights <= uint32_t(kClMaxLights) && host_lights && (!p.has_ibl || (ibl->accel && ibl->accel->g_pref.tex))) {
+  // (measured SLOWER than the record kernel on the bench frame, 218 vs 169 us -- profiles/r02_k3_variants.txt -- so it is opt-in:
+  // PBRCU_K3_CL=1)
+  const char* cl_env = getenv("PBRCU_K3_CL");
+  const bool use_cl = cl_env && atoi(cl_env) != 0;
+  if (use_cl && !tex && p.tile_counts == nullptr && n_lights <= uint32_t(kClMaxLights) && host_lights && (!p.has_ibl || (ibl->accel && ibl->accel->g_pref.tex))) {
     const int amb = !p.has_ibl ? 0 : (p.t_irr && p.t_lut && !ctx->exact_ibl_filter) ? 1 : 2;
     return launch_shade_cl(p, lights_dev, n_lights, ibl ? ibl->accel : nullptr, amb, n_views > 1 ? LIST_ONE_BATCHED : LIST_ONE, ctx->sm_count, st);
   }

@@ -169,9 +169,9 @@ def test_shade_matches_oracle(pbr, dev, oracle, w, h, nl, use_ibl):
     if use_ibl:
         ibl2 = make_ibl_struct(pbr, host, bufs, dev, accel=True)
         n_cube = oracle.chain_texels(host["pref_res"], host["pref_mips"]) + host["irr"].size // 4
-        # 32-byte footprint records of the three maps + the flagged RGBA16F texture copies of the two cubes
-        # ... and the LUT as a float2 texture
-        assert dev.lib.ibl_accel_bytes(ibl2.accel) == 32 * (n_cube + host["lut"].size // 2) + 8 * n_cube + 8 * (host["lut"].size // 2)
+        # at least: 32-byte footprint records of the three maps + the flagged RGBA16F texture copies of the two cubes + the LUT
+        # as a float2 texture (+ the gather atlases: every face of every level with a one-texel gutter)
+        assert dev.lib.ibl_accel_bytes(ibl2.accel) >= 32 * (n_cube + host["lut"].size // 2) + 8 * n_cube + 8 * (host["lut"].size // 2)
         out2 = dev.alloc(w * h * 8)
         # opt-in: texture-unit fetches (8-bit weights), fp32-weight records where the contrast flag is set
         dev.lib.shade_set_texture_unit(dev.ctx, 1)
@@ -630,3 +630,44 @@ def test_shade_frame_host_equals_the_device_path(pbr, dev, oracle, w, h, bands):
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
     for b in (out, ld, *bufs):
         b.free()
+
+
+@pytest.mark.parametrize("nl", [0, 1, 3, 4, 7, 16])
+def test_shade_host_light_list_and_the_gather_kernel(pbr, dev, oracle, nl, monkeypatch):
+    """Lights passed as a HOST array (what the facade and pbrcu_shade_frame_host do): the default path uploads them into
+    the context's list and must equal the device-list call bit for bit; with PBRCU_K3_CL=1 the list travels in the kernel's
+    parameter block and the IBL taps are tld4 gathers (shade_ggx_cl.cu) -- checked against the oracle in both filter modes,
+    and the exact mode against the plain four-load path within one fp16 ulp (different contraction order in the lights)."""
+    host, bufs = build_ibl(dev, oracle)
+    w, h = 83, 41
+    g = synth_gbuffer(w, h, seed=300 + nl, tier_b=True)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    lights = synth_lights(max(nl, 1), seed=30 + nl)[:nl]
+    ld = dev.upload(lights) if nl else None
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    cam = (0.5, -1.0, 12.0)
+    out = dev.alloc(w * h * 8)
+
+    def run(ptr):
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ptr, nl, None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
+        dev.sync()
+        return out.download((h, w, 4), np.uint16)
+
+    host_ptr = lights.ctypes.data if nl else None
+    _, want = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, lights, host)
+    peak = float(max(f16(want).max(), 1.0))
+    for exact in (0, 1):
+        dev.lib.ibl_set_exact_filtering(dev.ctx, exact)
+        monkeypatch.delenv("PBRCU_K3_CL", raising=False)
+        from_dev = run(ld.ptr if ld else None)
+        assert np.array_equal(run(host_ptr), from_dev), "host light list != device light list"
+        monkeypatch.setenv("PBRCU_K3_CL", "1")
+        got = run(host_ptr)
+        assert_hdr_parity(got, want, peak=peak, rel_tol=REL, what=f"gather kernel nl={nl} exact={exact}")
+        assert (got[g["bg"]] == 0).all()
+        if exact:
+            ulps = np.abs(got.view(np.int16).astype(int) - from_dev.view(np.int16).astype(int))
+            assert ulps.max() <= 1, f"gather kernel (exact) differs from the record kernel by {ulps.max()} fp16 ulps"
+    monkeypatch.delenv("PBRCU_K3_CL", raising=False)
+    dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
