@@ -221,6 +221,19 @@ int pbrcu_shade_ggx_ibl_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t 
                                 uint32_t n_views, const float* cam_pos_xyz, const pbrcu_light* lights_dev,
                                 uint32_t n_lights, const pbrcu_ibl* ibl, void* out_rgba16f, size_t out_pitch,
                                 size_t out_view_stride, pbrcu_stream s);
+/* pbrcu_shade_ggx_ibl_batched for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments and
+ * bit-identical results; the per-view camera table lives in a file-scope device array instead of context scratch, so the
+ * call makes no cudaMalloc / cudaFree and calls no allocating library routine.  Limits: n_views <= PBRCU_STATIC_MAX_VIEWS
+ * (beyond it: PBRCU_ERR_INVALID with a message), lights_dev must be DEVICE memory (a host list would need an upload
+ * buffer), at most 128 lights, no tile lists.  The array (48 KB) is held by every GPU that loads the library until exit and
+ * is shared by ALL calls on a device: each call overwrites the entries it uses, and calls that overlap on the GPU
+ * (different streams or contexts of one device) race on it -- order them with events or use the allocating entry point. */
+#define PBRCU_STATIC_MAX_VIEWS 4096
+int pbrcu_shade_ggx_ibl_batched_static(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
+                                       uint32_t n_views, const float* cam_pos_xyz, const pbrcu_light* lights_dev,
+                                       uint32_t n_lights, const pbrcu_ibl* ibl, void* out_rgba16f, size_t out_pitch,
+                                       size_t out_view_stride, pbrcu_stream s);
 /* K3c: per 16x16 tile, the lights whose range sphere meets the tile's world-space position AABB */
 int pbrcu_light_tiles_alloc(pbrcu_ctx* ctx, uint32_t width, uint32_t height, uint32_t max_per_tile,
                             pbrcu_light_tiles* out);

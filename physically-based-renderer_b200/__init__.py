@@ -122,6 +122,7 @@ _SIGNATURES = {
     "pbrcu_shade_ggx_ibl_multicast": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, _vp]),
     "pbrcu_shade_ggx_ibl_replicated": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, C.POINTER(_vp), _u32, _vp]),
     "pbrcu_shade_ggx_ibl_batched": (_i, [_vp, _PG, _sz, _sz, _u32, _f3, _vp, _u32, _PI, _vp, _sz, _sz, _vp]),
+    "pbrcu_shade_ggx_ibl_batched_static": (_i, [_vp, _PG, _sz, _sz, _u32, _f3, _vp, _u32, _PI, _vp, _sz, _sz, _vp]),
     "pbrcu_shade_frame_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _f3, _vp, _u32, _PI, _vp, _u32, _vp]),
     "pbrcu_ibl_accel_build": (_i, [_vp, _PI, C.POINTER(_vp), _vp]),
     "pbrcu_ibl_accel_free": (_i, [_vp, _vp]),

@@ -11,6 +11,7 @@
 // latency of the streaming reads never sits on a warp's critical path; the tile's light list is staged
 // in shared memory; the IBL footprint records of a pixel are prefetched into L1 before its light loop.
 #include <cstdlib>
+#include <mutex>
 
 #include "shade_ggx.cuh"
 
@@ -560,7 +561,7 @@ static void launch_shade(const ShadeParams& p, int lists, uint32_t grid, cudaStr
 static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_dev, uint32_t n_lights,
                         const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch,
                         uint32_t n_views, size_t view_stride8, size_t view_stride4, size_t out_view_stride, pbrcu_stream s,
-                        void* const* replicas = nullptr, uint32_t n_replicas = 0, bool multicast = false) {
+                        void* const* replicas = nullptr, uint32_t n_replicas = 0, bool multicast = false, const float* cams_table = nullptr) {
   PBRCU_REQUIRE(ctx && g && cam_pos && out_rgba16f, "NULL argument");
   PBRCU_REQUIRE(n_replicas <= PBRCU_MAX_REPLICAS && (n_replicas == 0 || replicas), "too many replicas or replicas NULL");
   for (uint32_t k = 0; k < n_replicas; ++k) PBRCU_REQUIRE(replicas[k] && reinterpret_cast<uintptr_t>(replicas[k]) % 8 == 0, "replica NULL or not 8-byte aligned");
@@ -583,7 +584,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   p.tx0 = rect.x0 / kTile; p.ty0 = rect.y0 / kTile;
   p.cx = cam_pos[0]; p.cy = cam_pos[1]; p.cz = cam_pos[2];
   p.n_views = n_views; p.view_stride8 = view_stride8; p.view_stride4 = view_stride4; p.out_view_stride = out_view_stride;
-  p.cams = ctx->cams_dev;
+  p.cams = cams_table ? cams_table : ctx->cams_dev;
   p.lights = lights_dev; p.n_lights = n_lights;
   if (tiles) {
     PBRCU_REQUIRE(tiles->counts && tiles->indices, "light tiles not allocated");
@@ -698,4 +699,60 @@ extern "C" int pbrcu_shade_ggx_ibl_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* 
   PBRCU_CUDA(cudaMemcpyAsync(ctx->cams_dev, cam_pos_xyz, size_t(n_views) * 3 * sizeof(float), cudaMemcpyHostToDevice, static_cast<cudaStream_t>(s)));
   return shade_common(ctx, g0, cam_pos_xyz, lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, 0, 0, 0}, out_rgba16f, out_pitch, n_views, view_stride8,
                       view_stride4, out_view_stride, s);
+}
+
+// ---- pbrcu_shade_ggx_ibl_batched_static: the batched launch for callers that must not allocate ----
+// The batched kernel reads one camera position per view from a table in device memory.  pbrcu_shade_ggx_ibl_batched keeps
+// that table in context scratch grown with cudaMalloc; here it lives in a file-scope device array of a fixed, modest size
+// (PBRCU_STATIC_MAX_VIEWS views x 3 floats = 48 KB, held by every GPU that loads the library until exit).  Every call
+// shares the array and overwrites the entries it uses (nothing in it has to start at zero); two calls that overlap on
+// the GPU -- different streams, or different contexts of one device -- race on it.
+static __device__ __align__(256) float g_static_cams[3 * PBRCU_STATIC_MAX_VIEWS];
+
+// In host code `g_static_cams` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+static int static_cams_address(pbrcu_ctx* ctx, float** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex lock;
+  static float* address[kMaxDevices] = {};
+  PBRCU_REQUIRE(ctx->device >= 0 && ctx->device < kMaxDevices, "device ordinal out of range for the static scratch");
+  std::lock_guard<std::mutex> hold(lock);
+  if (!address[ctx->device]) {
+    int current = -1;
+    PBRCU_CUDA(cudaGetDevice(&current));
+    if (current != ctx->device) PBRCU_CUDA(cudaSetDevice(ctx->device));
+    float* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_static_cams);
+    if (current != ctx->device) cudaSetDevice(current);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_cams)");
+    PBRCU_REQUIRE(ptr != nullptr, "static scratch has no device address");
+    address[ctx->device] = ptr;
+  }
+  *out = address[ctx->device];
+  return PBRCU_OK;
+}
+
+extern "C" int pbrcu_shade_ggx_ibl_batched_static(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
+                                                  uint32_t n_views, const float* cam_pos_xyz, const pbrcu_light* lights_dev, uint32_t n_lights,
+                                                  const pbrcu_ibl* ibl, void* out_rgba16f, size_t out_pitch, size_t out_view_stride, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && g0 && cam_pos_xyz && out_rgba16f, "NULL argument");
+  PBRCU_REQUIRE(n_views >= 1, "n_views must be at least 1");
+  if (n_views > PBRCU_STATIC_MAX_VIEWS) {
+    set_error("invalid argument: n_views = %u exceeds PBRCU_STATIC_MAX_VIEWS = %u, the size of the static camera table "
+              "(use pbrcu_shade_ggx_ibl_batched, or split the views over several calls)", n_views, unsigned(PBRCU_STATIC_MAX_VIEWS));
+    return PBRCU_ERR_INVALID;
+  }
+  // a host light list would be uploaded into context scratch that may have to grow: this entry point allocates nothing
+  PBRCU_REQUIRE(n_lights == 0 || (lights_dev && !is_host_pointer(lights_dev)), "lights must be a DEVICE array for the no-allocation entry point");
+  PBRCU_REQUIRE(view_stride8 >= g0->pitch8 * g0->height && view_stride4 >= g0->pitch4 * g0->height && out_view_stride >= out_pitch * g0->height,
+                "view stride smaller than one view");
+  PBRCU_REQUIRE(view_stride8 % 8 == 0 && view_stride4 % 4 == 0 && out_view_stride % 8 == 0, "view strides must keep texels aligned");
+  PBRCU_REQUIRE(n_lights <= uint32_t(kLightChunk), "batched shading takes at most 128 lights");
+  float* cams = nullptr;
+  if (int rc = static_cams_address(ctx, &cams)) return rc;
+  if (n_views == 1)  // a single view takes its camera from the kernel parameters
+    return shade_common(ctx, g0, cam_pos_xyz, lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, 0, 0, 0}, out_rgba16f, out_pitch, 1, 0, 0, 0, s);
+  PBRCU_CUDA(cudaMemcpyAsync(cams, cam_pos_xyz, size_t(n_views) * 3 * sizeof(float), cudaMemcpyHostToDevice, static_cast<cudaStream_t>(s)));
+  return shade_common(ctx, g0, cam_pos_xyz, lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, 0, 0, 0}, out_rgba16f, out_pitch, n_views, view_stride8,
+                      view_stride4, out_view_stride, s, nullptr, 0, false, cams);
 }
