@@ -166,8 +166,11 @@ typedef struct {
 size_t pbrcu_cube_chain_texels(uint32_t base_res, uint32_t nmips);
 size_t pbrcu_cube_mip_offset(uint32_t base_res, uint32_t mip); /* texels */
 
-/* K3: lights = device array of n_lights pbrcu_light; tiles may be NULL (every pixel loops all
- * lights); ibl may be NULL (direct light + emissive only). */
+/* K3: lights = array of n_lights pbrcu_light in DEVICE or HOST memory; tiles may be NULL (every pixel loops all
+ * lights); ibl may be NULL (direct light + emissive only).  A HOST list of at most 32 lights without tile lists -- the
+ * usual frame: a handful of scene lights -- is read during the call and travels in the kernel's parameter block (no
+ * upload, no staging: the fastest path, csrc/shade_ggx_cl.cu); any other host list is uploaded into context scratch
+ * first.  The same holds for the _replicated, _multicast and _batched forms. */
 int pbrcu_shade_ggx_ibl(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3],
                         const pbrcu_light* lights_dev, uint32_t n_lights,
                         const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,

@@ -203,3 +203,4 @@ WHOLE = Rect(0, 0, 0, 0)
 
 from .device import Device, DeviceBuffer  # noqa: E402  (numpy-level conveniences for tests / bench)
 from . import partition  # noqa: E402
+from . import synth  # noqa: E402  (seeded synthetic inputs for tests / bench)

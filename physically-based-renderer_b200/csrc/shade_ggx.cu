@@ -616,12 +616,14 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   // ---- one light list the HOST holds (the headline frame, the batched views, the facade): lights in the kernel's
   // parameter block, IBL by texture gathers (shade_ggx_cl.cu) ----
   const bool host_lights = n_lights == 0 || is_host_pointer(lights_dev);
-  // (measured SLOWER than the record kernel on the bench frame, 218 vs 169 us -- profiles/r02_k3_variants.txt -- so it is opt-in:
-  // PBRCU_K3_CL=1)
+  // PBRCU_K3_CL: 0 = never (upload the list, shade_ggx_one_kernel), 1 = IBL taps by tld4 gathers (measured slower: 218 vs 169 us
+  // on the bench frame), 2 or unset = footprint records (158.6 us) -- profiles/r02_k3_variants_*.txt
   const char* cl_env = getenv("PBRCU_K3_CL");
-  const bool use_cl = cl_env && atoi(cl_env) != 0;
-  if (use_cl && !tex && p.tile_counts == nullptr && n_lights <= uint32_t(kClMaxLights) && host_lights && (!p.has_ibl || (ibl->accel && ibl->accel->g_pref.tex))) {
-    const int amb = !p.has_ibl ? 0 : (p.t_irr && p.t_lut && !ctx->exact_ibl_filter) ? 1 : 2;
+  const int cl_mode = cl_env ? atoi(cl_env) : 2;
+  const bool use_cl = cl_mode != 0;
+  if (use_cl && !tex && p.tile_counts == nullptr && n_lights <= uint32_t(kClMaxLights) && host_lights && (!p.has_ibl || (p.q_pref && ibl->accel->g_pref.tex))) {
+    int amb = !p.has_ibl ? 0 : (p.t_irr && p.t_lut && !ctx->exact_ibl_filter) ? 1 : 2;
+    if (amb != 0 && cl_mode != 1) amb += 2;  // footprint records instead of gathers
     return launch_shade_cl(p, lights_dev, n_lights, ibl ? ibl->accel : nullptr, amb, n_views > 1 ? LIST_ONE_BATCHED : LIST_ONE, ctx->sm_count, st);
   }
   if (n_lights != 0 && host_lights) {  // the kernels below read the list from device memory

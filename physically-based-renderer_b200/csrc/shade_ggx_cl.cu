@@ -117,10 +117,11 @@ __device__ __forceinline__ void cl_light(const LightPixel& s, const ClLight& L, 
 template <int NL, int AMB, bool BATCHED, bool PEERS, bool BRANCH, int CTAS, bool LATE = false>
 __global__ void __launch_bounds__(kShadeThreads, CTAS) shade_ggx_cl_kernel(const __grid_constant__ ShadeClParams q) {
   const ShadeParams& p = q.p;
+  constexpr bool REC = AMB >= 3, AMBTEX = AMB == 1 || AMB == 3;  // 3 / 4: modes 1 / 2 with footprint records in place of gathers
   __shared__ TileStage s_tile[2];
   __shared__ float4 s_lv[17];
-  __shared__ float4 s_amb[AMB == 2 ? 3 : 2][kShadeThreads];  // {p0_tx, p0_ty, p1_tx, p1_ty}, {lod_f, cdr, cdg, cdb}, {irr_tx, irr_ty, lut_tx, lut_ty}
-  if (AMB != 0 && threadIdx.x < 17) s_lv[threadIdx.x] = q.lv[threadIdx.x];
+  __shared__ float4 s_amb[AMBTEX ? 2 : 3][kShadeThreads];  // {p0_tx, p0_ty, p1_tx, p1_ty}, {lod_f, cdr, cdg, cdb}, {irr_tx, irr_ty, lut_tx, lut_ty}
+  if (AMB != 0 && !REC && threadIdx.x < 17) s_lv[threadIdx.x] = q.lv[threadIdx.x];
 
   const uint32_t nitems = 2 * p.ntiles;  // per view
   uint32_t tile = blockIdx.x, view = 0;
@@ -195,9 +196,26 @@ __global__ void __launch_bounds__(kShadeThreads, CTAS) shade_ggx_cl_kernel(const
 
     // ---- ambient set-up: every fetch is issued here and consumed after the lights, which cover its latency ----
     float4 p0r, p0g, p0b, p1r, p1g, p1b, ir, ig, ib, la, lb;
+    Quad6 rq0, rq1, rqi;
+    Quad8 rql;
     float4 tirr = make_float4(0.f, 0.f, 0.f, 0.f);
     float2 tlut = make_float2(0.f, 0.f);
-    if (AMB != 0) {
+    if (REC) {  // footprint records: one 256-bit load per bilinear tap, fp32 weights (ibl_quads.cuh)
+      const float3 Rv = make_float3(2.0f * NoVraw * s.N.x - s.V.x, 2.0f * NoVraw * s.N.y - s.V.y, 2.0f * NoVraw * s.N.z - s.V.z);
+      const IblTaps taps = make_ibl_taps(p, s.N, Rv, s.NoV, rough);  // (the taps a mode does not use are dead code)
+      rq0 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p0));
+      rq1 = ldg_rec256(p.q_pref + 2 * size_t(taps.i_p1));
+      s_amb[0][threadIdx.x] = make_float4(taps.p0_tx, taps.p0_ty, taps.p1_tx, taps.p1_ty);
+      reinterpret_cast<float*>(&s_amb[1][threadIdx.x])[0] = taps.lod_f;
+      if (AMBTEX) {
+        tirr = texCubemapLod<float4>(p.t_irr, s.N.x * 1.00000095f, s.N.y * 1.00000048f, s.N.z, 0.0f);  // (tilt: see below)
+        tlut = tex2D<float2>(p.t_lut, s.NoV, rough);
+      } else {
+        rqi = ldg_rec256(p.q_irr + 2 * size_t(taps.i_irr));
+        rql = ldg_quad(p.q_lut + 2 * size_t(taps.i_lut));
+        s_amb[2][threadIdx.x] = make_float4(taps.irr_tx, taps.irr_ty, taps.lut_tx, taps.lut_ty);
+      }
+    } else if (AMB != 0) {
       const float3 Rv = make_float3(2.0f * NoVraw * s.N.x - s.V.x, 2.0f * NoVraw * s.N.y - s.V.y, 2.0f * NoVraw * s.N.z - s.V.z);
       float facef, u, v;
       cube_dir_to_facef_uv(Rv, facef, u, v);
@@ -212,7 +230,7 @@ __global__ void __launch_bounds__(kShadeThreads, CTAS) shade_ggx_cl_kernel(const
       p1r = tex2Dgather<float4>(q.g_pref, c1x, c1y, 0); p1g = tex2Dgather<float4>(q.g_pref, c1x, c1y, 1); p1b = tex2Dgather<float4>(q.g_pref, c1x, c1y, 2);
       s_amb[0][threadIdx.x] = make_float4(t0.tx, t0.ty, t1.tx, t1.ty);
       reinterpret_cast<float*>(&s_amb[1][threadIdx.x])[0] = lod - l0f;
-      if (AMB == 1) {
+      if (AMBTEX) {
         // the unit's own face selection breaks exact ties of the major axis (fp16 normals do produce them) its own way, and
         // without seamless filtering the two faces give different edge texels: tilt the direction by 2^-20 so that ties
         // go X, then Y, then Z like cube_dir_to_face_uv (moves the tap by 1e-6 of the face)
@@ -233,20 +251,44 @@ __global__ void __launch_bounds__(kShadeThreads, CTAS) shade_ggx_cl_kernel(const
     if (NL >= 0) {
 #pragma unroll
       for (int l = 0; l < NL; ++l) cl_light<BRANCH>(s, q.lights[l], dr, dg, db);
-    } else {
-      for (uint32_t l = 0; l < q.n_lights; ++l) cl_light<BRANCH>(s, q.lights[l], dr, dg, db);
+    } else {  // run-time count, padded to a multiple of four: four independent chains per iteration
+      for (uint32_t l = 0; l < q.n_lights; l += 4) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) cl_light<BRANCH>(s, q.lights[l + k], dr, dg, db);
+      }
     }
 
     // ---- ambient: split-sum image-based lighting (Karis 2013) ----
     float ar = 0.f, ag = 0.f, ab = 0.f;
     if (AMB != 0 && (!LATE || q.pad == 0)) {  // (LATE: an opaque, always-true test keeps ptxas from moving the filter -- and the wait for its fetches -- in front of the lights)
       const float4 w0 = s_amb[0][threadIdx.x], w1 = s_amb[1][threadIdx.x];
-      RGB pre{bilerp4(p0r, w0.x, w0.y), bilerp4(p0g, w0.x, w0.y), bilerp4(p0b, w0.x, w0.y)};
-      const RGB pr1{bilerp4(p1r, w0.z, w0.w), bilerp4(p1g, w0.z, w0.w), bilerp4(p1b, w0.z, w0.w)};
+      RGB pre, pr1;
+      if (REC) {
+        pre = quad_bilinear_rgb(rq0, w0.x, w0.y);
+        pr1 = quad_bilinear_rgb(rq1, w0.z, w0.w);
+      } else {
+        pre = RGB{bilerp4(p0r, w0.x, w0.y), bilerp4(p0g, w0.x, w0.y), bilerp4(p0b, w0.x, w0.y)};
+        pr1 = RGB{bilerp4(p1r, w0.z, w0.w), bilerp4(p1g, w0.z, w0.w), bilerp4(p1b, w0.z, w0.w)};
+      }
       pre.r = lerpf(pre.r, pr1.r, w1.x); pre.g = lerpf(pre.g, pr1.g, w1.x); pre.b = lerpf(pre.b, pr1.b, w1.x);
       RGB irr;
       float2 sb;
-      if (AMB == 1) {
+      if (AMBTEX && REC) {
+        irr = RGB{tirr.x, tirr.y, tirr.z};
+        sb = tlut;
+        if (tirr.w > 0.0f) {  // a flagged texel took part in the fetch: redo this tap with fp32 weights from its record
+          int face;
+          float u, v;
+          cube_dir_to_face_uv(s.N, face, u, v);
+          const int ires = int(p.irr.base_res);
+          const Tap a = make_tap(u, v, ires);
+          irr = quad_bilinear_rgb(ldg_rec256(p.q_irr + 2 * size_t(face * ires * ires + a.idx)), a.tx, a.ty);
+        }
+      } else if (REC) {
+        const float4 w2 = s_amb[2][threadIdx.x];
+        irr = quad_bilinear_rgb(rqi, w2.x, w2.y);
+        sb = quad_bilinear_lut(rql, w2.z, w2.w);
+      } else if (AMBTEX) {
         irr = RGB{tirr.x, tirr.y, tirr.z};
         sb = tlut;
         if (tirr.w > 0.0f) {  // a flagged texel took part in the fetch: redo this tap with fp32 weights
@@ -290,13 +332,15 @@ static void launch_cl_modes(const ShadeClParams& q, int lists, bool peers, uint3
 
 template <int NL>
 static void launch_cl_amb(const ShadeClParams& q, int amb, int lists, bool peers, uint32_t grid, cudaStream_t st) {
-  if (amb == 0) launch_cl_modes<NL, 0, true, kClCtasPerSm>(q, lists, peers, grid, st);
-  else if (amb == 1) launch_cl_modes<NL, 1, true, kClCtasPerSm>(q, lists, peers, grid, st);
-  else launch_cl_modes<NL, 2, true, kClCtasPerSm>(q, lists, peers, grid, st);
+  if (amb == 0) launch_cl_modes<NL, 0, false, kClCtasPerSm>(q, lists, peers, grid, st);
+  else if (amb == 1) launch_cl_modes<NL, 1, false, kClCtasPerSm>(q, lists, peers, grid, st);
+  else if (amb == 2) launch_cl_modes<NL, 2, false, kClCtasPerSm>(q, lists, peers, grid, st);
+  else if (amb == 3) launch_cl_modes<NL, 3, false, kClCtasPerSm>(q, lists, peers, grid, st);
+  else launch_cl_modes<NL, 4, false, kClCtasPerSm>(q, lists, peers, grid, st);
 }
 
 // p: the parameters shade_common filled (rect, planes, textures, views, replicas); lights: HOST array.
-// amb: 0 no IBL, 1 default, 2 exact.  Returns the persistent grid's CTAs per SM through *ctas_per_sm.
+// amb: 0 no IBL; 1 / 2 gathers (default / exact filtering); 3 / 4 footprint records (default / exact).
 int launch_shade_cl(const ShadeParams& p, const pbrcu_light* lights_host, uint32_t n_lights, const pbrcu_ibl_accel* accel, int amb, int lists,
                     int sm_count, cudaStream_t st) {
   ShadeClParams q{};
@@ -308,7 +352,7 @@ int launch_shade_cl(const ShadeParams& p, const pbrcu_light* lights_host, uint32
     q.lut_res = float(accel->lut_res);
     q.nm1 = float(accel->pref_mips - 1);
   }
-  const uint32_t n_eval = n_lights == 0 ? 0 : n_lights <= 2 ? 2 : n_lights <= 4 ? 4 : n_lights;
+  const uint32_t n_eval = n_lights == 0 ? 0 : n_lights <= 2 ? 2 : (n_lights + 3) & ~3u;
   q.n_lights = n_eval;
   for (uint32_t l = 0; l < n_eval; ++l) {
     ClLight& c = q.lights[l];
@@ -328,15 +372,21 @@ int launch_shade_cl(const ShadeParams& p, const pbrcu_light* lights_host, uint32
     const int v = atoi(e);
     if (n_eval == 4 && lists == LIST_ONE && !peers && amb != 0 && v > 0) {
       const uint32_t g4 = uint32_t(std::min<uint64_t>(items, uint64_t(sm_count) * 4)), g6 = uint32_t(std::min<uint64_t>(items, uint64_t(sm_count) * 6));
+#define PBRCU_EXP1(A, BR, CT, LT, G) shade_ggx_cl_kernel<4, A, false, false, BR, CT, LT><<<G, kShadeThreads, 0, st>>>(q)
 #define PBRCU_EXP(BR, CT, LT, G) \
-  (amb == 1 ? shade_ggx_cl_kernel<4, 1, false, false, BR, CT, LT><<<G, kShadeThreads, 0, st>>>(q) : shade_ggx_cl_kernel<4, 2, false, false, BR, CT, LT><<<G, kShadeThreads, 0, st>>>(q))
-      if (v == 1) PBRCU_EXP(false, 5, false, grid);
+  (amb == 1 ? PBRCU_EXP1(1, BR, CT, LT, G) : amb == 2 ? PBRCU_EXP1(2, BR, CT, LT, G) : amb == 3 ? PBRCU_EXP1(3, BR, CT, LT, G) : PBRCU_EXP1(4, BR, CT, LT, G))
+      if (v == 1) PBRCU_EXP(true, 5, false, grid);
       else if (v == 2) PBRCU_EXP(true, 4, false, g4);
       else if (v == 3) PBRCU_EXP(true, 6, false, g6);
       else if (v == 4) PBRCU_EXP(true, 4, true, g4);
       else if (v == 5) PBRCU_EXP(true, 5, true, grid);
+      else if (v == 6) PBRCU_EXP(false, 6, false, g6);
+      else if (v == 7) PBRCU_EXP(false, 5, true, grid);
+      else if (v == 8) PBRCU_EXP(false, 6, true, g6);
+      else if (v == 9) PBRCU_EXP(false, 4, false, g4);
       else PBRCU_EXP(true, 5, false, grid);
 #undef PBRCU_EXP
+#undef PBRCU_EXP1
       return launch_check("shade_ggx_cl_kernel (experiment)");
     }
   }

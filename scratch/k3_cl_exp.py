@@ -36,17 +36,20 @@ def diff(out, ref):
             f"nan {int(f1.isnan().sum())}/{int(f0.isnan().sum())}")
 
 refs = {}
+names = {0: "branch ctas5", 1: "nobranch ctas5", 2: "branch ctas4", 3: "branch ctas6", 4: "branch ctas4 late", 5: "branch ctas5 late", 6: "nobranch ctas6", 7: "nobranch ctas5 late", 8: "nobranch ctas6 late", 9: "nobranch ctas4"}
 for exact in (0, 1):
     lib.ibl_set_exact_filtering(ctx, exact)
-    os.environ.pop("PBRCU_K3_EXP", None)
+    os.environ.pop("PBRCU_K3_EXP", None); os.environ.pop("PBRCU_K3_CL", None)
     refs[exact], us = run(scene.lights.data_ptr())
-    print(f"exact={exact} OLD (device lights, records): {us:.1f} us/frame {bench.W4K*bench.H4K/us/1e3:.2f} Gpix/s", flush=True)
-    for v in (0, 1, 2, 3, 4, 5):
-        os.environ["PBRCU_K3_EXP"] = str(v)
-        out, us = run(host_lights.ctypes.data)
-        name = {0: "branch ctas5", 1: "nobranch ctas5", 2: "branch ctas4", 3: "branch ctas6", 4: "branch ctas4 late", 5: "branch ctas5 late"}[v]
-        print(f"exact={exact} NEW v{v} ({name}): {us:.1f} us/frame {bench.W4K*bench.H4K/us/1e3:.2f} Gpix/s  vs old: {diff(out, refs[exact])}", flush=True)
+    print(f"exact={exact} OLD (device lights, records, shade_ggx_one_kernel): {us:.1f} us/frame {bench.W4K*bench.H4K/us/1e3:.2f} Gpix/s", flush=True)
+    for cl, what in ((2, "records"),):
+        os.environ["PBRCU_K3_CL"] = str(cl)
+        for v in (0, 1, 6, 7, 8, 9):
+            os.environ["PBRCU_K3_EXP"] = str(v)
+            out, us = run(host_lights.ctypes.data)
+            print(f"exact={exact} CL {what} v{v} ({names[v]}): {us:.1f} us/frame {bench.W4K*bench.H4K/us/1e3:.2f} Gpix/s  vs old: {diff(out, refs[exact])}", flush=True)
 os.environ.pop("PBRCU_K3_EXP", None)
+os.environ["PBRCU_K3_CL"] = "2"
 lib.ibl_set_exact_filtering(ctx, 0)
 # no IBL, and the run-time light count form
 for nl in (0, 1, 3, 4, 7, 16):

@@ -617,7 +617,8 @@ def test_shade_frame_host_equals_the_device_path(pbr, dev, oracle, w, h, bands):
     cam = pbr.f3(0.5, -1.0, 12.0)
     gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
     out = dev.alloc(w * h * 8)
-    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), cam, ld.ptr, nl, None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
+    # (the same HOST light list: both calls then take the parameter-block kernel)
+    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), cam, lights.ctypes.data, nl, None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
     dev.sync()
     want = out.download((h, w, 4), np.uint16)
     planes = {k: np.ascontiguousarray(g[k]) for k in ("pos", "nrm", "alb", "orm", "emi")}
@@ -633,11 +634,11 @@ def test_shade_frame_host_equals_the_device_path(pbr, dev, oracle, w, h, bands):
 
 
 @pytest.mark.parametrize("nl", [0, 1, 3, 4, 7, 16])
-def test_shade_host_light_list_and_the_gather_kernel(pbr, dev, oracle, nl, monkeypatch):
-    """Lights passed as a HOST array (what the facade and pbrcu_shade_frame_host do): the default path uploads them into
-    the context's list and must equal the device-list call bit for bit; with PBRCU_K3_CL=1 the list travels in the kernel's
-    parameter block and the IBL taps are tld4 gathers (shade_ggx_cl.cu) -- checked against the oracle in both filter modes,
-    and the exact mode against the plain four-load path within one fp16 ulp (different contraction order in the lights)."""
+def test_shade_host_light_list_kernels(pbr, dev, oracle, nl, monkeypatch):
+    """Lights passed as a HOST array (what the facade, the bench and pbrcu_shade_frame_host do) travel in the kernel's parameter
+    block (shade_ggx_cl.cu).  Default: IBL taps from the footprint records; PBRCU_K3_CL=1: tld4 gathers; PBRCU_K3_CL=0: the list
+    is uploaded and the device-list kernel runs, bit for bit.  Every mode against the oracle in both filter modes; the exact
+    modes against the device-list kernel within one fp16 ulp (the lights are summed in another contraction order)."""
     host, bufs = build_ibl(dev, oracle)
     w, h = 83, 41
     g = synth_gbuffer(w, h, seed=300 + nl, tier_b=True)
@@ -648,8 +649,8 @@ def test_shade_host_light_list_and_the_gather_kernel(pbr, dev, oracle, nl, monke
     cam = (0.5, -1.0, 12.0)
     out = dev.alloc(w * h * 8)
 
-    def run(ptr):
-        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ptr, nl, None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
+    def run(ptr, use_ibl=True):
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ptr, nl, None, C.byref(ibl) if use_ibl else None, pbr.WHOLE, out.ptr, w * 8, None)
         dev.sync()
         return out.download((h, w, 4), np.uint16)
 
@@ -660,14 +661,22 @@ def test_shade_host_light_list_and_the_gather_kernel(pbr, dev, oracle, nl, monke
         dev.lib.ibl_set_exact_filtering(dev.ctx, exact)
         monkeypatch.delenv("PBRCU_K3_CL", raising=False)
         from_dev = run(ld.ptr if ld else None)
-        assert np.array_equal(run(host_ptr), from_dev), "host light list != device light list"
-        monkeypatch.setenv("PBRCU_K3_CL", "1")
-        got = run(host_ptr)
-        assert_hdr_parity(got, want, peak=peak, rel_tol=REL, what=f"gather kernel nl={nl} exact={exact}")
-        assert (got[g["bg"]] == 0).all()
-        if exact:
-            ulps = np.abs(got.view(np.int16).astype(int) - from_dev.view(np.int16).astype(int))
-            assert ulps.max() <= 1, f"gather kernel (exact) differs from the record kernel by {ulps.max()} fp16 ulps"
+        monkeypatch.setenv("PBRCU_K3_CL", "0")
+        assert np.array_equal(run(host_ptr), from_dev), "uploaded host light list != device light list"
+        for mode in (None, "1"):
+            if mode is None:
+                monkeypatch.delenv("PBRCU_K3_CL", raising=False)
+            else:
+                monkeypatch.setenv("PBRCU_K3_CL", mode)
+            got = run(host_ptr)
+            assert_hdr_parity(got, want, peak=peak, rel_tol=REL, what=f"parameter-block kernel nl={nl} exact={exact} mode={mode}")
+            assert (got[g["bg"]] == 0).all()
+            if exact:
+                ulps = np.abs(got.view(np.int16).astype(int) - from_dev.view(np.int16).astype(int))
+                assert ulps.max() <= 1, f"mode {mode} (exact) differs from the device-list kernel by {ulps.max()} fp16 ulps"
     monkeypatch.delenv("PBRCU_K3_CL", raising=False)
     dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+    # no IBL at all
+    _, want0 = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, lights, None)
+    assert_hdr_parity(run(host_ptr, use_ibl=False), want0, peak=float(max(f16(want0).max(), 1.0)), rel_tol=REL, what=f"parameter-block kernel nl={nl}, no IBL")
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
