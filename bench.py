@@ -57,6 +57,22 @@ def config_block(n_gpus):
     return {"workload": WORKLOAD, "l2": "inputs larger than L2 (365 MB per frame) and 3 rotating buffer sets", "parallelism": f"frames x{n_gpus}"}
 
 
+def roof(bound, achieved, peak, unit, note=None):
+    """One roofline entry: achieved / peak of whatever bounds the kernel."""
+    r = {"bound": bound, "achieved": round(achieved, 2), "peak": round(peak, 2), "unit": unit, "frac": round(achieved / peak, 4) if peak else None}
+    if note:
+        r["note"] = note
+    return r
+
+
+def fp32_peak_tflops(sm_count, mhz=1965.0):
+    return sm_count * 128 * 2 * mhz * 1e6 / 1e12  # FMA = 2 flop, 128 lanes per SM
+
+
+def tex_peak_gfetch(sm_count, mhz=1965.0):
+    return sm_count * 2.0 * mhz * 1e6 / 1e9  # RGBA16F (64-bit texel) trilinear fetches: 2 per clock per SM (scratch/ubench.cu)
+
+
 def measured_peak_gbs():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -210,6 +226,21 @@ class Scene:
         b.record()
         torch.cuda.synchronize()
         self.ibl_ms["accel_build"] = round(a.elapsed_time(b), 4)
+        peak, _ = measured_peak_gbs()
+        sms = dev.sm_count
+        lvl_texels = lambda m: 6 * (CUBE_RES >> m) ** 2
+        k7_fetches = sum(lvl_texels(m) for m in range(1, CUBE_MIPS)) * IBL_SAMPLES
+        ms_of = lambda k: self.ibl_ms[k] * 1e-3
+        self.ibl_roofline = {
+            "equirect_to_cube": roof("hbm", (ENV_W * ENV_H * 16 + lvl_texels(0) * 8) / ms_of("equirect_to_cube") / 1e9, peak, "GB/s"),
+            "cube_mipgen": roof("hbm", (chain_bytes + chain_bytes - lvl_texels(0) * 8) / ms_of("cube_mipgen") / 1e9, peak, "GB/s", "reads every level but the last, writes every level but the first"),
+            "prefilter_ggx": roof("texture fetch rate", k7_fetches / ms_of("prefilter_ggx") / 1e9, tex_peak_gfetch(sms), "G trilinear RGBA16F fetches/s",
+                                  "levels 1..11 x 1024 samples, one hardware trilinear cube fetch each; level 0 is a copy; the time includes the flagged texture upload"),
+            "irradiance": roof("texture fetch rate", 6 * IRR_RES * IRR_RES * IBL_SAMPLES / ms_of("irradiance") / 1e9, tex_peak_gfetch(sms), "G trilinear RGBA16F fetches/s",
+                               "24,576 texels: a single partial wave, latency-bound; the time includes the flagged texture upload"),
+            "brdf_lut": roof("fp32", LUT_RES * LUT_RES * IBL_SAMPLES * 40 / ms_of("brdf_lut") / 1e12, fp32_peak_tflops(sms), "TFLOP/s",
+                             "40 flop per sample (SURVEY 8(d)); deterministic math: no FMA contraction, correctly rounded sqrt / div"),
+        }
         s.accel = self.accel
         self.ibl = s
 
@@ -283,12 +314,22 @@ def extra_configs(scene, torch, dist, world, rank):
     gathered = None
     if world > 1:
         # north_star: "NCCL over NVLink is used only to gather the finished tiles": the same step followed by the exchange that
-        # leaves the whole HDR frame on every rank (one NCCL broadcast per band -- the cost-balanced bands differ in height)
-        def step8k_gather(i):
-            step8k(i)
+        # leaves the whole HDR frame on every rank
+        # ONE collective: every rank shades its band straight into its slot of a padded gather buffer (slots of the tallest band's
+        # size -- the cost-balanced bands differ in height), one in-place ncclAllGather, then the bands are unpacked into the frame
+        rb = W8 * 8
+        slot = max(e - b for b, e in bands_all) * rb
+        stage_all = scene.buf(world * slot)
+
+        def step8k_gather(_):
+            if y1 > y0:
+                lib.cluster_lights(ctx, C.byref(band.gbuffer), lights.data_ptr(), NL, C.byref(band.tiles), scene.stream())
+                lib.shade_ggx_ibl(ctx, C.byref(band.gbuffer), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(band.tiles), C.byref(scene.ibl), pbr.WHOLE,
+                                  stage_all.data_ptr() + rank * slot, rb, scene.stream())
+            dist.all_gather_into_tensor(stage_all, stage_all[rank * slot:(rank + 1) * slot])
             for r, (b, e) in enumerate(bands_all):
                 if e > b:
-                    dist.broadcast(hdr[b * W8 * 8:e * W8 * 8], src=r)
+                    hdr[b * rb:e * rb].copy_(stage_all[r * slot:r * slot + (e - b) * rb], non_blocking=True)
 
         ms_g = timed(torch, dist, step8k_gather, 5, 3)
         # the same frame with the gather fused into K3's stores: every rank's frame lives in symmetric memory, each rank
@@ -354,7 +395,33 @@ def extra_configs(scene, torch, dist, world, rank):
     host_counts = np.empty(max(band.tiles.tiles_x * band.tiles.tiles_y, 1), np.uint32)
     lib.memcpy_d2h(host_counts.ctypes.data, band.tiles.counts, band.tiles.tiles_x * band.tiles.tiles_y * 4, scene.stream())
     torch.cuda.synchronize()
+    # (light, pixel) pairs the frame evaluates: every pixel of a tile loops its tile's list (90 flop per pair + 120 per pixel)
+    pairs = torch.tensor([float(host_counts[:band.tiles.tiles_x * band.tiles.tiles_y].astype(np.float64).sum()) * 256.0], dtype=torch.float64, device=hdr.device)
+    if dist is not None:
+        dist.all_reduce(pairs)
+    t8 = ms / 5 * 1e-3
+    peak_hbm, _ = measured_peak_gbs()
+    flop = float(pairs.item()) * 90.0 + W8 * H8 * 120.0
+    # the same frame unsharded on this GPU alone (no barrier): the N = 1 time the strong-scaling efficiency refers to
+    ms_whole = ms / 5
+    if world > 1:
+        tiles1 = pbr.LightTiles()
+        lib.light_tiles_alloc(ctx, W8, H8, NL, C.byref(tiles1))
+        whole = scene.buf(W8 * H8 * 8)
+
+        def step_whole(_):
+            lib.cluster_lights(ctx, C.byref(g), lights.data_ptr(), NL, C.byref(tiles1), scene.stream())
+            lib.shade_ggx_ibl(ctx, C.byref(g), pbr.f3(*CAM), lights.data_ptr(), NL, C.byref(tiles1), C.byref(scene.ibl), pbr.WHOLE, whole.data_ptr(), W8 * 8, scene.stream())
+
+        ms_whole = timed(torch, None, step_whole, 5, 3) / 5
+        lib.light_tiles_free(ctx, C.byref(tiles1))
+        scene.keep = [t for t in scene.keep if t is not whole]
+        del whole
     out["config3_8k_256_lights"] = {"mpix_s": round(W8 * H8 * 5 / (ms * 1e-3) / 1e6, 1), "ms_per_frame": round(ms / 5, 4),
+                                    "ms_per_frame_unsharded_on_one_gpu": round(ms_whole, 4),
+                                    "roofline": roof("fp32", flop / t8 / 1e12, fp32_peak_tflops(dev.sm_count) * world, "TFLOP/s",
+                                                     f"{pairs.item():.4g} (light, pixel) pairs x 90 flop + 120 flop per pixel over {world} GPU(s); peak = SMs x 128 lanes x 2 x 1.965 GHz"),
+                                    "roofline_hbm": roof("hbm", (B_PER_PX_K3 + 16) * W8 * H8 / t8 / 1e9, peak_hbm * world, "GB/s", "44 B/px K3 + 16 B/px K3c (positions + normals re-read)"),
                                     "rows_per_rank": y1 - y0, "mean_lights_per_tile": round(float(host_counts.mean()), 2),
                                     "max_lights_per_tile": int(host_counts.max()), "scaling": "strong (cost-balanced row bands from the previous frame's light lists, no exchange)",
                                     "what": "pbrcu_cluster_lights + pbrcu_shade_ggx_ibl on the rank's row band, 256 point lights range U[2,6], IBL"}
@@ -394,6 +461,7 @@ def extra_configs(scene, torch, dist, world, rank):
 
     ms = timed(torch, dist, step_views, 3, 3)
     out["config4_256_views_1080p"] = {"mpix_s": round(NV * WV * HV * 3 / (ms * 1e-3) / 1e6, 1), "ms_per_pass": round(ms / 3, 3),
+                                      "roofline": roof("hbm", B_PER_PX_K3 * NV * WV * HV / (ms / 3 * 1e-3) / 1e9, measured_peak_gbs()[0] * world, "GB/s", "44 B/px, all views, all ranks"),
                                       "views_per_rank": nv, "scaling": "strong (view blocks, no exchange)",
                                       "what": "pbrcu_shade_ggx_ibl_batched: the rank's views in one launch, 4 point lights + IBL"}
     out["geometry_pass_1080p"] = geometry_bench(scene, torch, dist, world, rank)
@@ -513,10 +581,43 @@ def geometry_bench(scene, torch, dist, world, rank):
     ms_geo = timed(torch, dist, geo, 16, 4) / 16
     ms_frame = timed(torch, dist, frame, 16, 4) / 16
     covered = float((planes["normals"].view(torch.int16).view(-1, 4)[:, :3] != 0).any(dim=1).float().mean())
-    return {"triangles": n_tris, "draws": n_draws, "ms_geometry_pass": round(ms_geo, 4), "mtri_s": round(n_tris / (ms_geo * 1e-3) / 1e6, 1),
+    return {"roofline": roof("hbm (traffic floor; the pass is latency-bound: dependent gathers key -> record -> vertices -> texel)",
+                             (W * H * (28 + 12 + 16) + n_tris * (16 + 48)) / (ms_geo * 1e-3) / 1e9, measured_peak_gbs()[0], "GB/s",
+                             "per pixel 28 B of planes + 12 B of ORM / emissive written, 8 B visibility word written and read; per triangle a 48 B set-up + 16 B record"),
+            "triangles": n_tris, "draws": n_draws, "ms_geometry_pass": round(ms_geo, 4), "mtri_s": round(n_tris / (ms_geo * 1e-3) / 1e6, 1),
             "ms_frame_geometry_plus_ggx_shading": round(ms_frame, 4), "frame_mpix_s": round(W * H / (ms_frame * 1e-3) / 1e6, 1),
             "covered_fraction_last_view": round(covered, 3),
             "what": "pbrcu_geometry_pass (setup, cover, chunk queue, resolve) per view; then + pbrcu_shade_ggx_ibl on the rasterised G-buffer"}
+
+
+def strong_scaling_block(extra, scene, world):
+    """Fixed total work over N GPUs: time at N, time on one GPU and efficiency = t1 / (N tN).  The headline `value` is N
+    independent frames (weak scaling, no data shared), so its scaling says nothing about these designs.  t1: measured in
+    this run where the unsharded work fits beside the sharded one (8K frame, prefilter), else the committed N = 1 line."""
+    if not extra:
+        return None
+    cached = {}
+    try:
+        cached = json.loads((ROOT / "profiles" / "r02_bench_n1.json").read_text().strip().splitlines()[-1])["other_configs"]
+    except Exception:
+        pass
+    c3, c4, pf = extra["config3_8k_256_lights"], extra["config4_256_views_1080p"], extra["config2_prefilter_sharded"]
+
+    def entry(t1, tn, src):
+        return {"n_gpus": world, "ms": tn, "ms_one_gpu": t1, "efficiency": (round(t1 / (world * tn), 3) if t1 and tn else None), "ms_one_gpu_source": src}
+
+    t1_views = c4["ms_per_pass"] if world == 1 else cached.get("config4_256_views_1080p", {}).get("ms_per_pass")
+    out = {"256_views_1080p": entry(t1_views, c4["ms_per_pass"], "this run" if world == 1 else "profiles/r02_bench_n1.json"),
+           "8k_256_lights_sharded": entry(c3["ms_per_frame_unsharded_on_one_gpu"], c3["ms_per_frame"], "this run (same frame unsharded on this GPU)"),
+           "prefilter_sharded": entry(scene.ibl_ms["prefilter_ggx"], pf["ms_prefilter_shard_only"], "this run (ibl_precompute_ms.prefilter_ggx)")}
+    for key, name in (("ms_per_frame_with_gather", "8k_256_lights_sharded_nccl_gather"), ("ms_per_frame_fused_gather", "8k_256_lights_sharded_fused_gather_p2p"),
+                      ("ms_per_frame_multicast_gather", "8k_256_lights_sharded_fused_gather_multicast")):
+        if key in c3:
+            out[name] = entry(c3["ms_per_frame_unsharded_on_one_gpu"], c3[key], "this run (same frame unsharded on this GPU)")
+    for key, name in (("ms_prefilter_and_gather", "prefilter_sharded_nccl_gather"), ("ms_prefilter_fused_gather", "prefilter_sharded_fused_gather")):
+        if key in pf and world > 1:
+            out[name] = entry(scene.ibl_ms["prefilter_ggx"], pf[key], "this run (ibl_precompute_ms.prefilter_ggx)")
+    return out
 
 
 def timed(torch, dist, fn, steps, warmup):
@@ -676,6 +777,22 @@ def main_ours(args):
                            out.data_ptr(), ldr_host.data_ptr(), scene.stream())
 
     ms_a_e2e = timed(torch, dist, step_a_host, e2e_steps, 3)
+    # the floor of the e2e step on this box: every rank moves one frame's bytes both ways AT THE SAME TIME (pinned memory, two
+    # streams per rank, no kernels) -- what the PCIe links and the host's memory system deliver to N GPUs at once
+    dev_in = scene.buf(px_step * 36)
+    host_in = torch.empty(px_step * 36, dtype=torch.uint8, pin_memory=True)
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def step_copy(_):
+        cur = torch.cuda.current_stream()
+        s_in.wait_stream(cur); s_out.wait_stream(cur)
+        with torch.cuda.stream(s_in):
+            dev_in.copy_(host_in, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            out.copy_(scene.outs[0], non_blocking=True)
+        cur.wait_stream(s_in); cur.wait_stream(s_out)
+
+    ms_floor = timed(torch, dist, step_copy, e2e_steps, 3) / e2e_steps
     clocks = sampler.stop()
 
     extra = None if args.no_extra else extra_configs(scene, torch, dist, world, rank)
@@ -697,7 +814,8 @@ def main_ours(args):
                          "kernel": K3_KERNEL, "algorithmic_bytes_per_px": B_PER_PX_K3},
             "e2e": {"value": round(e2e_value, 1), "unit": "Mpix/s", "h2d_bytes_per_step": px_step * 36,
                     "d2h_bytes_per_step": px_step * 8, "steps": e2e_steps, "api": "pbrcu_shade_frame_host (pinned host planes, 4 pipelined row bands, tapered 8:4:2:1)",
-                    "host_placement": host_placement},
+                    "host_placement": host_placement, "ms_per_step": round(ms_e2e / e2e_steps, 4), "floor_ms": round(ms_floor, 4),
+                    "floor": f"{world} rank(s) copying 299 MB in and 66 MB out concurrently from / to pinned memory, no kernels (max over ranks)"},
             "gpu_launches": args.steps,
             "clocks": clocks,
             "cpu_baseline": cpu,
@@ -710,7 +828,9 @@ def main_ours(args):
                        "frame_host_mpix_s": round(world * px_step * e2e_steps / (ms_a_e2e * 1e-3) / 1e6, 1),
                        "frame_host": "pbrcu_frame_host: three pinned host planes in (24 B/px), lighting + ACES tonemap, HDR and LDR frames out (12 B/px), 4 tapered row bands"},
             "other_configs": extra,
+            "strong_scaling": strong_scaling_block(extra, scene, world),
             "ibl_precompute_ms": scene.ibl_ms,
+            "ibl_precompute_roofline": scene.ibl_roofline,
             "prefilter_error": scene.prefilter_error,
         }
         print(json.dumps(line))
