@@ -189,6 +189,29 @@ class Scene:
             b.record()
             torch.cuda.synchronize()
             self.ibl_ms[name] = round(a.elapsed_time(b), 4)
+        # the same two convolutions from a PREPARED source (pbrcu_ibl_source: the flagged texture copy built once for both, as a
+        # precompute that runs K6 and K7 from one environment does); results must equal the plain entry points' bit for bit
+        self.source = C.c_void_p()
+        check_pref, check_irr = buf(chain_bytes), buf(6 * IRR_RES * IRR_RES * 8)
+        prepared = [
+            ("source_prepare", lambda: (lib.ibl_source_free(ctx, self.source), lib.ibl_source_create(ctx, self.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, self.stream(), C.byref(self.source)))),
+            ("prefilter_ggx_prepared", lambda: lib.ibl_prefilter_ggx_prepared(ctx, self.source, IBL_SAMPLES, check_pref.data_ptr(), 0, CUBE_MIPS - 1, 0, 1, None, 0, self.stream())),
+            ("irradiance_prepared", lambda: lib.ibl_irradiance_prepared(ctx, self.source, IRR_RES, IBL_SAMPLES, check_irr.data_ptr(), self.stream())),
+        ]
+        for name, fn in prepared:
+            fn()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            self.ibl_ms[name] = round(a.elapsed_time(b), 4)
+        self.ibl_ms["prepared_equals_plain"] = bool(torch.equal(check_pref, self.pref) and torch.equal(check_irr, self.irr))
+        self.ibl_ms["precompute_total_prepared"] = round(sum(self.ibl_ms[k] for k in ("hammersley", "equirect_to_cube", "cube_mipgen", "source_prepare",
+                                                                                    "prefilter_ggx_prepared", "irradiance_prepared", "brdf_lut")), 4)
+        self.keep = [t for t in self.keep if t is not check_pref and t is not check_irr]
+        del check_pref, check_irr
         # the same prefilter with software fp32-weight filtering (pbrcu_ibl_set_exact_filtering): time, and
         # how far the texture-unit result is from it
         exact = buf(chain_bytes)
@@ -234,10 +257,10 @@ class Scene:
         self.ibl_roofline = {
             "equirect_to_cube": roof("hbm", (ENV_W * ENV_H * 16 + lvl_texels(0) * 8) / ms_of("equirect_to_cube") / 1e9, peak, "GB/s"),
             "cube_mipgen": roof("hbm", (chain_bytes + chain_bytes - lvl_texels(0) * 8) / ms_of("cube_mipgen") / 1e9, peak, "GB/s", "reads every level but the last, writes every level but the first"),
-            "prefilter_ggx": roof("texture fetch rate", k7_fetches / ms_of("prefilter_ggx") / 1e9, tex_peak_gfetch(sms), "G trilinear RGBA16F fetches/s",
-                                  "levels 1..11 x 1024 samples, one hardware trilinear cube fetch each; level 0 is a copy; the time includes the flagged texture upload"),
-            "irradiance": roof("texture fetch rate", 6 * IRR_RES * IRR_RES * IBL_SAMPLES / ms_of("irradiance") / 1e9, tex_peak_gfetch(sms), "G trilinear RGBA16F fetches/s",
-                               "24,576 texels: a single partial wave, latency-bound; the time includes the flagged texture upload"),
+            "prefilter_ggx": roof("texture fetch rate", k7_fetches / ms_of("prefilter_ggx_prepared") / 1e9, tex_peak_gfetch(sms), "G trilinear RGBA16F fetches/s",
+                                  "levels 1..11 x 1024 samples, one hardware trilinear cube fetch each; level 0 is a copy; prepared source (prefilter_ggx_prepared)"),
+            "irradiance": roof("texture fetch rate", 6 * IRR_RES * IRR_RES * IBL_SAMPLES / ms_of("irradiance_prepared") / 1e9, tex_peak_gfetch(sms), "G trilinear RGBA16F fetches/s",
+                               "24,576 texels: a single partial wave, latency-bound; prepared source (irradiance_prepared)"),
             "brdf_lut": roof("fp32", LUT_RES * LUT_RES * IBL_SAMPLES * 40 / ms_of("brdf_lut") / 1e12, fp32_peak_tflops(sms), "TFLOP/s",
                              "40 flop per sample (SURVEY 8(d)); deterministic math: no FMA contraction, correctly rounded sqrt / div"),
         }
@@ -472,7 +495,8 @@ def extra_configs(scene, torch, dist, world, rank):
 def prefilter_sharded(scene, torch, dist, world, rank):
     """BASELINE configs[2]'s prefilter (2048^2, 12 mips, 1024 spp) over the ranks: every rank convolves its row
     block of every level (pbrcu_ibl_prefilter_ggx shard/nshards) from its own replica of the source chain, then
-    the finished chain is all-gathered over NCCL so every GPU can shade with it.  Strong
+    the finished chain is all-gathered over NCCL so every GPU can shade with it.  The source is PREPARED once
+    (pbrcu_ibl_source, outside the timed region like the source chain itself: it is the same on every rank).  Strong
     scaling; the gather is inside the timed region, and the gathered chain is checked against the unsharded one."""
     from pbr_b200.partition import gather_chain
     lib, ctx = scene.dev.lib, scene.dev.ctx
@@ -480,8 +504,8 @@ def prefilter_sharded(scene, torch, dist, world, rank):
 
     def conv(_):
         # level 0 (a copy of the source level, which every rank holds) whole on every rank; levels 1.. by row blocks
-        lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, dst.data_ptr(), 0, 0, 0, 1, scene.stream())
-        lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, dst.data_ptr(), 1, CUBE_MIPS - 1, rank, world, scene.stream())
+        lib.ibl_prefilter_ggx_prepared(ctx, scene.source, IBL_SAMPLES, dst.data_ptr(), 0, 0, 0, 1, None, 0, scene.stream())
+        lib.ibl_prefilter_ggx_prepared(ctx, scene.source, IBL_SAMPLES, dst.data_ptr(), 1, CUBE_MIPS - 1, rank, world, None, 0, scene.stream())
 
     def step(i):
         conv(i)
@@ -501,9 +525,8 @@ def prefilter_sharded(scene, torch, dist, world, rank):
             reps, nrep = pf.replica_array(0)
 
             def step_fused(_):
-                lib.ibl_prefilter_ggx(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, pf.local.data_ptr(), 0, 0, 0, 1, scene.stream())
-                lib.ibl_prefilter_ggx_replicated(ctx, scene.src_chain.data_ptr(), CUBE_RES, CUBE_MIPS, IBL_SAMPLES, pf.local.data_ptr(), 1, CUBE_MIPS - 1,
-                                                 rank, world, reps, nrep, scene.stream())
+                lib.ibl_prefilter_ggx_prepared(ctx, scene.source, IBL_SAMPLES, pf.local.data_ptr(), 0, 0, 0, 1, None, 0, scene.stream())
+                lib.ibl_prefilter_ggx_prepared(ctx, scene.source, IBL_SAMPLES, pf.local.data_ptr(), 1, CUBE_MIPS - 1, rank, world, reps, nrep, scene.stream())
                 pf.barrier()
 
             pf.local.zero_()
@@ -609,14 +632,14 @@ def strong_scaling_block(extra, scene, world):
     t1_views = c4["ms_per_pass"] if world == 1 else cached.get("config4_256_views_1080p", {}).get("ms_per_pass")
     out = {"256_views_1080p": entry(t1_views, c4["ms_per_pass"], "this run" if world == 1 else "profiles/r02_bench_n1.json"),
            "8k_256_lights_sharded": entry(c3["ms_per_frame_unsharded_on_one_gpu"], c3["ms_per_frame"], "this run (same frame unsharded on this GPU)"),
-           "prefilter_sharded": entry(scene.ibl_ms["prefilter_ggx"], pf["ms_prefilter_shard_only"], "this run (ibl_precompute_ms.prefilter_ggx)")}
+           "prefilter_sharded": entry(scene.ibl_ms["prefilter_ggx_prepared"], pf["ms_prefilter_shard_only"], "this run (ibl_precompute_ms.prefilter_ggx_prepared)")}
     for key, name in (("ms_per_frame_with_gather", "8k_256_lights_sharded_nccl_gather"), ("ms_per_frame_fused_gather", "8k_256_lights_sharded_fused_gather_p2p"),
                       ("ms_per_frame_multicast_gather", "8k_256_lights_sharded_fused_gather_multicast")):
         if key in c3:
             out[name] = entry(c3["ms_per_frame_unsharded_on_one_gpu"], c3[key], "this run (same frame unsharded on this GPU)")
     for key, name in (("ms_prefilter_and_gather", "prefilter_sharded_nccl_gather"), ("ms_prefilter_fused_gather", "prefilter_sharded_fused_gather")):
         if key in pf and world > 1:
-            out[name] = entry(scene.ibl_ms["prefilter_ggx"], pf[key], "this run (ibl_precompute_ms.prefilter_ggx)")
+            out[name] = entry(scene.ibl_ms["prefilter_ggx_prepared"], pf[key], "this run (ibl_precompute_ms.prefilter_ggx_prepared)")
     return out
 
 

@@ -290,6 +290,22 @@ int pbrcu_ibl_prefilter_ggx_replicated(pbrcu_ctx* ctx, const void* src_chain_dev
                                        uint32_t nmips, uint32_t nsamples, void* dst_chain_dev,
                                        uint32_t first_mip, uint32_t last_mip, uint32_t shard, uint32_t nshards,
                                        void* const* replica_chains, uint32_t n_replicas, pbrcu_stream s);
+/* A PREPARED source for K6 / K7: the texture copy (with contrast flags) the two convolutions sample, built once for every
+ * call that convolves one environment -- the plain entry points above rebuild it inside each call (about 1.3 ms at 2048^2:
+ * 3x3 min / max, flags, copy into the mip-mapped cube array), which is what stops a sharded prefilter from scaling and is
+ * paid twice by a precompute that runs K6 and K7 from the same chain.  The object is a SNAPSHOT of the chain's texels
+ * (rebuild it after they change) and keeps the chain's pointer: the chain must stay alive and unchanged while the object is
+ * used (flagged samples are re-filtered from it with fp32 weights).  Results are bit-identical to the plain entry points.
+ * pbrcu_ibl_prefilter_ggx_prepared takes the replica arguments of pbrcu_ibl_prefilter_ggx_replicated (NULL, 0: none). */
+typedef struct pbrcu_ibl_source pbrcu_ibl_source;
+int pbrcu_ibl_source_create(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips, pbrcu_stream s,
+                            pbrcu_ibl_source** out);
+int pbrcu_ibl_source_free(pbrcu_ctx* ctx, pbrcu_ibl_source* src);
+int pbrcu_ibl_prefilter_ggx_prepared(pbrcu_ctx* ctx, const pbrcu_ibl_source* src, uint32_t nsamples, void* dst_chain_dev,
+                                     uint32_t first_mip, uint32_t last_mip, uint32_t shard, uint32_t nshards,
+                                     void* const* replica_chains, uint32_t n_replicas, pbrcu_stream s);
+int pbrcu_ibl_irradiance_prepared(pbrcu_ctx* ctx, const pbrcu_ibl_source* src, uint32_t res, uint32_t nsamples, void* out_dev,
+                                  pbrcu_stream s);
 /* K6: cosine-weighted irradiance (E/pi), 6*res^2 RGBA16F */
 int pbrcu_ibl_irradiance(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
                          uint32_t res, uint32_t nsamples, void* out_dev, pbrcu_stream s);
@@ -331,6 +347,45 @@ typedef struct {
  * 0xFFFFFFFF.  Scratch (visibility buffer, piece set-ups) lives in the context and grows on demand. */
 int pbrcu_geometry_pass(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float view[16], const float proj[16],
                         const pbrcu_draw* draws, uint32_t n_draws, uint32_t* prim_id_dev, pbrcu_stream s);
+
+/* ---- multi-GPU host: ONE process drives the N GPUs of a box (csrc/mg.cu) ---------------------------------------------
+ * No counterpart in the reference, which renders on one device from one host thread (core/GpuHandle.cpp:77-81,
+ * gltf_viewer/App.cpp:444-483).  A group holds one pbrcu_ctx and one stream per member device with peer access between
+ * every pair (cudaDeviceEnablePeerAccess: memory from pbrcu_malloc on one member is addressable from kernels on another).
+ * The calls ENQUEUE on the members' streams and end with an event barrier: every member's stream waits for all the
+ * others', so work enqueued afterwards on any member's stream sees the whole result; pbrcu_mg_synchronize waits on the host.
+ * Allocate a member's buffers with its device current (pbrcu_mg_set_device) or through pbrcu_mg_ctx(mg, i).
+ * The same device may be listed more than once (members sharing a GPU): used by the tests to run N > 1 on one device. */
+typedef struct pbrcu_mg pbrcu_mg;
+int pbrcu_mg_create(const int* devices, int n, pbrcu_mg** out); /* 1 <= n <= 16 */
+void pbrcu_mg_destroy(pbrcu_mg* mg);
+int pbrcu_mg_size(const pbrcu_mg* mg);
+int pbrcu_mg_device(const pbrcu_mg* mg, int member);
+pbrcu_ctx* pbrcu_mg_ctx(pbrcu_mg* mg, int member);
+pbrcu_stream pbrcu_mg_stream(pbrcu_mg* mg, int member);
+int pbrcu_mg_set_device(pbrcu_mg* mg, int member); /* cudaSetDevice(member's device) */
+int pbrcu_mg_barrier(pbrcu_mg* mg);                /* device-side: every stream waits for all the others (events) */
+int pbrcu_mg_synchronize(pbrcu_mg* mg);            /* host-side: all streams drained */
+/* Row bands [y0, y1) of a frame for n members, cut on PBRCU_TILE boundaries (per-band light clustering == whole-frame
+ * clustering).  tile_row_costs: one estimate per tile row -- e.g. from the previous frame's lists, sum over the row's tiles
+ * of (9 + lights in the tile) -- cuts bands of equal COST; NULL cuts equal numbers of tile rows.  bands_y0y1: 2 n values. */
+int pbrcu_mg_row_bands(uint32_t height, int n, const float* tile_row_costs, uint32_t* bands_y0y1);
+#define PBRCU_MG_GATHER_NONE 0 /* member i's frame holds its own band only */
+#define PBRCU_MG_GATHER_P2P 1  /* fused: K3 stores each finished texel into every member's frame (NVLink P2P stores) */
+#define PBRCU_MG_GATHER_NCCL 2 /* after the shading, one grouped ncclBroadcast per band (libnccl resolved with dlopen) */
+/* One frame: member i clusters (tiles != NULL) and shades rows bands[2i] .. bands[2i+1] of ITS G-buffer g[i] with ITS IBL set
+ * ibl[i] into ITS frame frames[i] (+ the gather).  g, tiles, ibl, frames: arrays of n entries; lights_host: HOST array. */
+int pbrcu_mg_shade_frame(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host,
+                         uint32_t n_lights, const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, const uint32_t* bands_y0y1,
+                         void* const* frames, size_t pitch, int gather);
+/* Batched views: member i shades its block of n_views[i] views (pbrcu_shade_ggx_ibl_batched per member); no exchange. */
+int pbrcu_mg_shade_views(pbrcu_mg* mg, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
+                         const uint32_t* n_views, const float* const* cam_pos_xyz, const pbrcu_light* lights_host,
+                         uint32_t n_lights, const pbrcu_ibl* ibl, void* const* outs, size_t out_pitch, size_t out_view_stride);
+/* GGX prefilter: member i convolves row block i of n of levels 1.. from its prepared source; gather != 0 stores every
+ * finished texel into every member's chain, so all n chains are complete (and bit-identical to the unsharded one). */
+int pbrcu_mg_prefilter(pbrcu_mg* mg, const pbrcu_ibl_source* const* sources, uint32_t nmips, uint32_t nsamples,
+                       void* const* dst_chains, int gather);
 
 /* ---- synthetic inputs for benchmarks (generated on the device; never timed) ------------------ */
 /* kind 0 = gbuf_noise (every texel a hit, no coherence), 1 = gbuf_spheres (ray-cast spheres + plane,

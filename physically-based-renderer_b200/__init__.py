@@ -139,12 +139,29 @@ _SIGNATURES = {
     "pbrcu_geometry_pass": (_i, [_vp, C.POINTER(GBuffer), _vp, _vp, C.POINTER(Draw), C.c_uint32, _vp, _vp]),
     "pbrcu_ibl_prefilter_ggx": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, _vp]),
     "pbrcu_ibl_prefilter_ggx_replicated": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, C.POINTER(_vp), _u32, _vp]),
+    "pbrcu_ibl_source_create": (_i, [_vp, _vp, _u32, _u32, _vp, C.POINTER(_vp)]),
+    "pbrcu_ibl_source_free": (_i, [_vp, _vp]),
+    "pbrcu_ibl_prefilter_ggx_prepared": (_i, [_vp, _vp, _u32, _vp, _u32, _u32, _u32, _u32, C.POINTER(_vp), _u32, _vp]),
+    "pbrcu_ibl_irradiance_prepared": (_i, [_vp, _vp, _u32, _u32, _vp, _vp]),
     "pbrcu_ibl_irradiance": (_i, [_vp, _vp, _u32, _u32, _u32, _u32, _vp, _vp]),
+    "pbrcu_mg_create": (_i, [C.POINTER(C.c_int), _i, C.POINTER(_vp)]),
+    "pbrcu_mg_destroy": (None, [_vp]),
+    "pbrcu_mg_size": (_i, [_vp]),
+    "pbrcu_mg_device": (_i, [_vp, _i]),
+    "pbrcu_mg_ctx": (_vp, [_vp, _i]),
+    "pbrcu_mg_stream": (_vp, [_vp, _i]),
+    "pbrcu_mg_set_device": (_i, [_vp, _i]),
+    "pbrcu_mg_barrier": (_i, [_vp]),
+    "pbrcu_mg_synchronize": (_i, [_vp]),
+    "pbrcu_mg_row_bands": (_i, [_u32, _i, _f3, C.POINTER(_u32)]),
+    "pbrcu_mg_shade_frame": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, C.POINTER(_u32), C.POINTER(_vp), _sz, _i]),
+    "pbrcu_mg_shade_views": (_i, [_vp, _PG, _sz, _sz, C.POINTER(_u32), C.POINTER(_f3), _vp, _u32, _PI, C.POINTER(_vp), _sz, _sz]),
+    "pbrcu_mg_prefilter": (_i, [_vp, C.POINTER(_vp), _u32, _u32, C.POINTER(_vp), _i]),
     "pbrcu_synth_gbuffer": (_i, [_vp, _PG, _i, _u64, _f3, _f3, _vp]),
     "pbrcu_synth_environment": (_i, [_vp, _vp, _u32, _u32, _u64, _vp]),
 }
 
-_NO_STATUS = {"pbrcu_version", "pbrcu_last_error", "pbrcu_ctx_destroy", "pbrcu_ctx_sm_count",
+_NO_STATUS = {"pbrcu_mg_destroy", "pbrcu_mg_size", "pbrcu_mg_device", "pbrcu_mg_ctx", "pbrcu_mg_stream", "pbrcu_version", "pbrcu_last_error", "pbrcu_ctx_destroy", "pbrcu_ctx_sm_count",
               "pbrcu_cube_chain_texels", "pbrcu_cube_mip_offset", "pbrcu_ibl_accel_bytes"}
 
 

@@ -7,6 +7,8 @@
 // builds the table {L_local.xyz, source lod} once in shared memory; per sample a thread then does a
 // 3x3 frame rotation, one exact-weight trilinear cube fetch and 4 FMAs.  G lanes share one texel
 // (samples strided by G, warp-shuffle reduction) so the small mips still fill the machine.
+#include <new>
+
 #include "cube_tex.cuh"
 #include "detmath.cuh"
 
@@ -333,7 +335,8 @@ extern "C" int pbrcu_ibl_set_exact_filtering(pbrcu_ctx* ctx, int exact) {
 
 static int prefilter_common(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips,
                             uint32_t nsamples, void* dst_chain_dev, uint32_t first_mip, uint32_t last_mip,
-                            uint32_t shard, uint32_t nshards, void* const* replicas, uint32_t n_replicas, pbrcu_stream s) {
+                            uint32_t shard, uint32_t nshards, void* const* replicas, uint32_t n_replicas, pbrcu_stream s,
+                            const CubeTex* prepared = nullptr) {
   PBRCU_REQUIRE(ctx && src_chain_dev && dst_chain_dev, "NULL argument");
   PBRCU_REQUIRE(n_replicas <= PBRCU_MAX_REPLICAS && (n_replicas == 0 || replicas), "too many replicas or replicas NULL");
   for (uint32_t k = 0; k < n_replicas; ++k) PBRCU_REQUIRE(replicas[k] && reinterpret_cast<uintptr_t>(replicas[k]) % 8 == 0, "replica NULL or not 8-byte aligned");
@@ -344,7 +347,7 @@ static int prefilter_common(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t 
   PBRCU_REQUIRE(nshards >= 1 && shard < nshards, "shard out of range");
   cudaStream_t st = static_cast<cudaStream_t>(s);
   const bool tex = !ctx->exact_ibl_filter;
-  if (tex && last_mip >= 1)
+  if (tex && last_mip >= 1 && !prepared)  // (a prepared source, pbrcu_ibl_source, carries its own flagged texture copy)
     if (int rc = cube_tex_upload(ctx, &ctx->cube, src_chain_dev, base_res, nmips, 0.25f, true, st)) return rc;
   for (uint32_t m = first_mip; m <= last_mip; ++m) {
     const int res = int(base_res >> m);
@@ -369,7 +372,7 @@ static int prefilter_common(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t 
     p.roughness = float(m) / float(nmips - 1);
     p.row_begin = rb;
     p.row_end = re;
-    p.tex = ctx->cube.tex;
+    p.tex = prepared ? prepared->tex : ctx->cube.tex;
     p.n_replicas = int(n_replicas);
     for (uint32_t k = 0; k < n_replicas; ++k) p.replica_level[k] = static_cast<uint2*>(replicas[k]) + off;
     if (int rc = tex ? launch_conv<CONV_GGX, true>(ctx, p, st) : launch_conv<CONV_GGX, false>(ctx, p, st)) return rc;
@@ -407,5 +410,65 @@ extern "C" int pbrcu_ibl_irradiance(pbrcu_ctx* ctx, const void* src_chain_dev, u
   if (ctx->exact_ibl_filter) return launch_conv<CONV_COSINE, false>(ctx, p, st);
   if (int rc = cube_tex_upload(ctx, &ctx->cube, src_chain_dev, base_res, nmips, 0.25f, true, st)) return rc;
   p.tex = ctx->cube.tex;
+  return launch_conv<CONV_COSINE, true>(ctx, p, st);
+}
+
+// ---- a prepared source: the flagged texture copy K6 / K7 sample, built ONCE for all the calls that convolve one environment ----
+struct pbrcu_ibl_source {
+  pbrcu::CubeTex tex;
+  const void* chain;  // the plain chain (caller-owned): flagged samples are re-filtered from it with fp32 weights
+  uint32_t base_res, nmips;
+};
+
+extern "C" int pbrcu_ibl_source_create(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res, uint32_t nmips, pbrcu_stream s,
+                                       pbrcu_ibl_source** out) {
+  PBRCU_REQUIRE(ctx && src_chain_dev && out, "NULL argument");
+  PBRCU_REQUIRE(base_res > 0 && (base_res & (base_res - 1)) == 0, "base_res must be a power of two");
+  PBRCU_REQUIRE(nmips >= 1 && nmips <= 16 && (base_res >> (nmips - 1)) >= 1, "nmips out of range for base_res");
+  *out = nullptr;
+  pbrcu_ibl_source* src = new (std::nothrow) pbrcu_ibl_source();
+  if (!src) return PBRCU_ERR_NOMEM;
+  src->tex = CubeTex{};
+  src->chain = src_chain_dev; src->base_res = base_res; src->nmips = nmips;
+  if (int rc = cube_tex_upload(ctx, &src->tex, src_chain_dev, base_res, nmips, 0.25f, true, static_cast<cudaStream_t>(s))) {
+    cube_tex_destroy(&src->tex);
+    delete src;
+    return rc;
+  }
+  *out = src;
+  return PBRCU_OK;
+}
+
+extern "C" int pbrcu_ibl_source_free(pbrcu_ctx* ctx, pbrcu_ibl_source* src) {
+  (void)ctx;
+  if (!src) return PBRCU_OK;
+  cube_tex_destroy(&src->tex);
+  delete src;
+  return PBRCU_OK;
+}
+
+extern "C" int pbrcu_ibl_prefilter_ggx_prepared(pbrcu_ctx* ctx, const pbrcu_ibl_source* src, uint32_t nsamples, void* dst_chain_dev,
+                                                uint32_t first_mip, uint32_t last_mip, uint32_t shard, uint32_t nshards,
+                                                void* const* replica_chains, uint32_t n_replicas, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && src, "NULL argument");
+  PBRCU_REQUIRE(src->nmips >= 2, "the source chain needs at least two levels");
+  return prefilter_common(ctx, src->chain, src->base_res, src->nmips, nsamples, dst_chain_dev, first_mip, last_mip, shard, nshards, replica_chains,
+                          n_replicas, s, &src->tex);
+}
+
+extern "C" int pbrcu_ibl_irradiance_prepared(pbrcu_ctx* ctx, const pbrcu_ibl_source* src, uint32_t res, uint32_t nsamples, void* out_dev,
+                                             pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && src && out_dev, "NULL argument");
+  PBRCU_REQUIRE(res > 0 && nsamples > 0 && size_t(nsamples) * 16 <= size_t(ctx->max_smem_optin), "res or nsamples out of range");
+  ConvParams p{};
+  p.src = make_chain(src->chain, src->base_res, src->nmips);
+  p.dst_level = static_cast<uint2*>(out_dev);
+  p.res = int(res);
+  p.nsamples = int(nsamples);
+  p.row_begin = 0;
+  p.row_end = 6 * int(res);
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (ctx->exact_ibl_filter) return launch_conv<CONV_COSINE, false>(ctx, p, st);
+  p.tex = src->tex.tex;
   return launch_conv<CONV_COSINE, true>(ctx, p, st);
 }

@@ -680,3 +680,31 @@ def test_shade_host_light_list_kernels(pbr, dev, oracle, nl, monkeypatch):
     _, want0 = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, lights, None)
     assert_hdr_parity(run(host_ptr, use_ibl=False), want0, peak=float(max(f16(want0).max(), 1.0)), rel_tol=REL, what=f"parameter-block kernel nl={nl}, no IBL")
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+
+
+def test_prepared_source_equals_the_plain_entry_points(dev, oracle):
+    """pbrcu_ibl_source: the flagged texture copy built once; prefilter (whole and as three shards) and irradiance from it must
+    return the bits of the entry points that rebuild it per call -- also after the context's own texture was re-used for
+    another chain in between (the object owns its copy)."""
+    res, nmips, ns, ires = 64, 7, 128, 16
+    env, chain_d, chain = make_env_chain(dev, oracle, res, nmips)
+    want_pref, want_irr = dev.alloc(chain.nbytes), dev.alloc(6 * ires * ires * 8)
+    dev.lib.ibl_prefilter_ggx(dev.ctx, chain_d.ptr, res, nmips, ns, want_pref.ptr, 0, nmips - 1, 0, 1, None)
+    dev.lib.ibl_irradiance(dev.ctx, chain_d.ptr, res, nmips, ires, ns, want_irr.ptr, None)
+    src = C.c_void_p()
+    dev.lib.ibl_source_create(dev.ctx, chain_d.ptr, res, nmips, None, C.byref(src))
+    # another chain through the plain entry point: overwrites the context's texture, must not touch the prepared object
+    _, other_d, other = make_env_chain(dev, oracle, res, nmips, seed=5)
+    scratch = dev.alloc(other.nbytes)
+    dev.lib.ibl_prefilter_ggx(dev.ctx, other_d.ptr, res, nmips, ns, scratch.ptr, 0, nmips - 1, 0, 1, None)
+    got_pref, got_irr, got_shards = dev.alloc(chain.nbytes), dev.alloc(6 * ires * ires * 8), dev.alloc(chain.nbytes)
+    dev.lib.ibl_prefilter_ggx_prepared(dev.ctx, src, ns, got_pref.ptr, 0, nmips - 1, 0, 1, None, 0, None)
+    for k in range(3):
+        dev.lib.ibl_prefilter_ggx_prepared(dev.ctx, src, ns, got_shards.ptr, 0, nmips - 1, k, 3, None, 0, None)
+    dev.lib.ibl_irradiance_prepared(dev.ctx, src, ires, ns, got_irr.ptr, None)
+    dev.sync()
+    w = want_pref.download(chain.shape, np.uint16)
+    assert np.array_equal(got_pref.download(chain.shape, np.uint16), w)
+    assert np.array_equal(got_shards.download(chain.shape, np.uint16), w)
+    assert np.array_equal(got_irr.download((6, ires, ires, 4), np.uint16), want_irr.download((6, ires, ires, 4), np.uint16))
+    dev.lib.ibl_source_free(dev.ctx, src)

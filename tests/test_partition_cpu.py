@@ -134,3 +134,25 @@ def test_bind_host_near_device_on_a_fake_sysfs(pbr, tmp_path):
             assert two["bound"] is True and two["node"] == 1 and os.sched_getaffinity(0) == set(mine[1::2])
     finally:
         os.sched_setaffinity(0, mine)
+
+
+def test_c_row_bands_equal_the_python_partition():
+    """pbrcu_mg_row_bands (the C multi-GPU host's band cuts; touches no CUDA state) == partition.cost_balanced_bands /
+    row_band on random costs, heights that are not tile multiples, more members than tile rows, all-zero costs."""
+    import ctypes as C
+
+    import numpy as np
+    import pbr_b200 as pbr
+    from pbr_b200.partition import cost_balanced_bands, row_band
+    lib = pbr.load()
+    rng = np.random.default_rng(5)
+    for height, n in [(4320, 8), (2160, 4), (1080, 2), (100, 3), (33, 16), (16, 5), (7, 2), (4320, 1)]:
+        rows = (height + 15) // 16
+        out = (C.c_uint32 * (2 * n))()
+        lib.mg_row_bands(height, n, None, out)
+        assert [(out[2 * k], out[2 * k + 1]) for k in range(n)] == [row_band(height, n, r, align=16) for r in range(n)]
+        for costs in (rng.uniform(0, 50, rows).astype(np.float32), np.zeros(rows, np.float32), (rng.uniform(0, 1, rows) ** 8 * 1000).astype(np.float32)):
+            lib.mg_row_bands(height, n, costs.ctypes.data_as(C.POINTER(C.c_float)), out)
+            got = [(out[2 * k], out[2 * k + 1]) for k in range(n)]
+            assert got == cost_balanced_bands(costs.astype(np.float64), height, n), (height, n)
+            assert got[0][0] == 0 and got[-1][1] == height and all(got[k][1] == got[k + 1][0] for k in range(n - 1))
