@@ -643,6 +643,94 @@ def strong_scaling_block(extra, scene, world):
     return out
 
 
+def mg_host_leg(scene, torch, n_dev):
+    """`--mg-host c`: BASELINE configs[3] (7680x4320, 256 clustered lights, row bands) driven by the C multi-GPU host -- ONE process,
+    one host thread, n_dev devices (pbrcu_mg_*: csrc/mg.cu) -- instead of one torch.distributed rank per GPU: no torch symmetric
+    memory, no NCCL through torch.  Per frame every member clusters and shades its cost-balanced band; the gather is fused into K3's
+    stores (P2P), done by grouped ncclBroadcasts, or left out.  Timed with CUDA events on member 0's stream (the call's closing event
+    barrier makes it wait for every member), so the host's launch overhead for n_dev devices is inside the number."""
+    pbr, lib = scene.pbr, scene.dev.lib
+    W8, H8, NL = 7680, 4320, 256
+    from pbr_b200.synth import synth_lights
+    lights = synth_lights(NL, seed=4, ranged=True)
+    mg = C.c_void_p()
+    lib.mg_create((C.c_int * n_dev)(*range(n_dev)), n_dev, C.byref(mg))
+    keep, gbs, ibls, tiles, frames = [], (pbr.GBuffer * n_dev)(), (pbr.Ibl * n_dev)(), (pbr.LightTiles * n_dev)(), []
+    for i in range(n_dev):
+        lib.mg_set_device(mg, i)
+        ctx = lib.mg_ctx(mg, i)
+        lib.gbuffer_alloc(ctx, W8, H8, 1, C.byref(gbs[i]))
+        lib.synth_gbuffer(ctx, C.byref(gbs[i]), 1, SEED + 40, pbr.f3(*CAM), pbr.f3(0, 0, 0), None)
+        cuda_i = torch.device("cuda", lib.mg_device(mg, i))
+        copies = [t.to(cuda_i, copy=True) for t in (scene.irr, scene.pref, scene.lut)]  # every member holds the IBL set
+        keep += copies
+        ibls[i].irradiance, ibls[i].irr_res = copies[0].data_ptr(), IRR_RES
+        ibls[i].prefiltered, ibls[i].pref_res, ibls[i].pref_mips = copies[1].data_ptr(), CUBE_RES, CUBE_MIPS
+        ibls[i].lut, ibls[i].lut_res = copies[2].data_ptr(), LUT_RES
+        a = C.c_void_p()
+        lib.ibl_accel_build(ctx, C.byref(ibls[i]), C.byref(a), None)
+        ibls[i].accel = a
+        lib.light_tiles_alloc(ctx, W8, H8, NL, C.byref(tiles[i]))
+        f = torch.zeros(W8 * H8 * 8, dtype=torch.uint8, device=cuda_i)
+        keep.append(f)
+        frames.append(f)
+        lib.stream_synchronize(None)
+    frame_ptrs = (C.c_void_p * n_dev)(*[f.data_ptr() for f in frames])
+    # "the previous frame's light lists": one whole-frame clustering on member 0 gives the tile-row costs every band cut derives from
+    lib.mg_set_device(mg, 0)
+    ctx0 = lib.mg_ctx(mg, 0)
+    ld = scene.buf(lights.nbytes) if scene.dev.ordinal == lib.mg_device(mg, 0) else torch.empty(lights.nbytes, dtype=torch.uint8, device=frames[0].device)
+    ld.copy_(torch.from_numpy(lights.view(np.uint8).reshape(-1)))
+    lib.cluster_lights(ctx0, C.byref(gbs[0]), ld.data_ptr(), NL, C.byref(tiles[0]), None)
+    counts = np.empty(tiles[0].tiles_x * tiles[0].tiles_y, np.uint32)
+    lib.memcpy_d2h(counts.ctypes.data, tiles[0].counts, counts.nbytes, None)
+    lib.stream_synchronize(None)
+    costs = (9.0 + counts.reshape(tiles[0].tiles_y, tiles[0].tiles_x)).sum(axis=1).astype(np.float32)
+    bands = (C.c_uint32 * (2 * n_dev))()
+    lib.mg_row_bands(H8, n_dev, costs.ctypes.data_as(C.POINTER(C.c_float)), bands)
+    # the unsharded frame on member 0 (untimed): what every gathered frame must equal bit for bit
+    whole = torch.empty(W8 * H8 * 8, dtype=torch.uint8, device=frames[0].device)
+    lib.shade_ggx_ibl(ctx0, C.byref(gbs[0]), pbr.f3(*CAM), ld.data_ptr(), NL, C.byref(tiles[0]), C.byref(ibls[0]), pbr.WHOLE, whole.data_ptr(), W8 * 8, None)
+    lib.stream_synchronize(None)
+    timer = C.c_void_p()
+    lib.timer_create(C.byref(timer))
+    out = {"n_devices": n_dev, "host": "one process, one host thread, pbrcu_mg_shade_frame (csrc/mg.cu); CUDA events on member 0's stream around 10 frames"}
+    modes = [("ms_per_frame_no_gather", 0), ("ms_per_frame_fused_gather_p2p", 1)] + ([("ms_per_frame_nccl_gather", 2)] if n_dev > 1 else [])
+    for key, gather in modes:
+        try:
+            for _ in range(3):
+                lib.mg_shade_frame(mg, gbs, pbr.f3(*CAM), lights.ctypes.data, NL, tiles, ibls, bands, frame_ptrs, W8 * 8, gather)
+            lib.mg_synchronize(mg)
+            lib.mg_set_device(mg, 0)
+            lib.timer_start(timer, lib.mg_stream(mg, 0))
+            for _ in range(10):
+                lib.mg_shade_frame(mg, gbs, pbr.f3(*CAM), lights.ctypes.data, NL, tiles, ibls, bands, frame_ptrs, W8 * 8, gather)
+            lib.mg_set_device(mg, 0)
+            lib.timer_stop(timer, lib.mg_stream(mg, 0))
+            ms = C.c_float()
+            lib.timer_elapsed_ms(timer, C.byref(ms))
+            lib.mg_synchronize(mg)
+            out[key] = round(ms.value / 10, 4)
+            if gather:
+                out[key.replace("ms_per_frame_", "") + "_equals_unsharded"] = all(bool(torch.equal(f.to(whole.device), whole)) for f in frames)
+                for f in frames:
+                    f.zero_()
+        except pbr.PbrcuError as e:
+            out[key] = None
+            out[key + "_error"] = str(e)[:160]
+    lib.timer_destroy(timer)
+    for i in range(n_dev):
+        lib.mg_set_device(mg, i)
+        ctx = lib.mg_ctx(mg, i)
+        lib.light_tiles_free(ctx, C.byref(tiles[i]))
+        lib.ibl_accel_free(ctx, ibls[i].accel)
+        lib.gbuffer_free(ctx, C.byref(gbs[i]))
+    lib.mg_destroy(mg)
+    torch.cuda.set_device(scene.dev.ordinal)
+    return out
+
+
+
 def timed(torch, dist, fn, steps, warmup):
     """W untimed + exactly K timed calls of fn(i), barrier + synchronize on both sides, CUDA events on the
     launching stream; returns max-over-ranks milliseconds for the K steps."""
@@ -820,6 +908,24 @@ def main_ours(args):
 
     extra = None if args.no_extra else extra_configs(scene, torch, dist, world, rank)
 
+    mg_host = None
+    if args.mg_host == "c" and not args.no_extra:
+        flag = Path(os.environ.get("TMPDIR", "/tmp")) / f"pbr_bench_mg_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}"
+        if rank == 0:
+            try:
+                mg_host = mg_host_leg(scene, torch, min(world, torch.cuda.device_count()))
+            except Exception as e:  # the leg must not take the headline down with it
+                mg_host = {"error": f"{type(e).__name__}: {e}"[:300]}
+            if world > 1:
+                flag.write_text("done")
+        else:  # the other ranks keep their GPUs idle until rank 0 is through (a host-side wait, no spinning collective)
+            t_wait = time.time()
+            while not flag.exists() and time.time() - t_wait < 900:
+                time.sleep(0.05)
+        if dist is not None:
+            dist.barrier()
+            if rank == 0:
+                flag.unlink(missing_ok=True)
     cpu, parity = (None, None)
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu, parity = cpu_sample(scene, torch)
@@ -852,6 +958,7 @@ def main_ours(args):
                        "frame_host": "pbrcu_frame_host: three pinned host planes in (24 B/px), lighting + ACES tonemap, HDR and LDR frames out (12 B/px), 4 tapered row bands"},
             "other_configs": extra,
             "strong_scaling": strong_scaling_block(extra, scene, world),
+            "mg_host_c": mg_host,
             "ibl_precompute_ms": scene.ibl_ms,
             "ibl_precompute_roofline": scene.ibl_roofline,
             "prefilter_error": scene.prefilter_error,
@@ -928,6 +1035,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--mg-host", choices=["none", "c"], default="c",
+                    help="c: also run configs[3] through the C multi-GPU host (pbrcu_mg_*), one process over the run's GPUs (rank 0)")
     ap.add_argument("--no-extra", action="store_true", help="skip the config[3]/[4] measurements (profiling runs)")
     args = ap.parse_args()
     if args.warmup < 3:
