@@ -372,7 +372,9 @@ int pbrcu_mg_synchronize(pbrcu_mg* mg);            /* host-side: all streams dra
 int pbrcu_mg_row_bands(uint32_t height, int n, const float* tile_row_costs, uint32_t* bands_y0y1);
 #define PBRCU_MG_GATHER_NONE 0 /* member i's frame holds its own band only */
 #define PBRCU_MG_GATHER_P2P 1  /* fused: K3 stores each finished texel into every member's frame (NVLink P2P stores) */
-#define PBRCU_MG_GATHER_NCCL 2 /* after the shading, one grouped ncclBroadcast per band (libnccl resolved with dlopen) */
+#define PBRCU_MG_GATHER_NCCL 2 /* after the shading, one grouped ncclBroadcast per band.  libnccl is resolved with dlopen at first
+                                * use: the file PBRCU_NCCL_LIB names, else the copy already loaded in the process (e.g. PyTorch's),
+                                * else the system's libnccl.so.2 -- a host that loads its own NCCL LATER must set PBRCU_NCCL_LIB */
 /* One frame: member i clusters (tiles != NULL) and shades rows bands[2i] .. bands[2i+1] of ITS G-buffer g[i] with ITS IBL set
  * ibl[i] into ITS frame frames[i] (+ the gather).  g, tiles, ibl, frames: arrays of n entries; lights_host: HOST array. */
 int pbrcu_mg_shade_frame(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host,

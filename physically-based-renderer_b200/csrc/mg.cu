@@ -18,6 +18,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -38,9 +39,14 @@ struct Nccl {
   const char* (*GetErrorString)(int) = nullptr;
   bool load() {
     if (lib) return true;
+    // Which NCCL: (1) the file PBRCU_NCCL_LIB names; (2) the copy the process ALREADY carries (a host with PyTorch loaded has its
+    // own, newer libnccl.so.2 -- loading a second one under the same SONAME would make later loads of the host's libraries bind
+    // to the wrong version); (3) the system's.  A host that imports its NCCL user later should set PBRCU_NCCL_LIB to that copy.
+    if (const char* path = getenv("PBRCU_NCCL_LIB")) lib = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
     for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
-      lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
       if (lib) break;
+      lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
     }
     if (!lib) return false;
     CommInitAll = reinterpret_cast<decltype(CommInitAll)>(dlsym(lib, "ncclCommInitAll"));

@@ -9,7 +9,24 @@ sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
 
 
+def _bundled_nccl():
+    """PyTorch's own libnccl (found without importing torch): the C multi-GPU host must use the copy a later `import torch` in the
+    same process will need, not the system's older one under the same SONAME (include/pbrcu.h, PBRCU_MG_GATHER_NCCL)."""
+    import importlib.util
+    import os
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except (ImportError, ValueError):
+        spec = None
+    for base in (spec.submodule_search_locations if spec and spec.submodule_search_locations else []):
+        lib = Path(base) / "lib" / "libnccl.so.2"
+        if lib.exists():
+            os.environ.setdefault("PBRCU_NCCL_LIB", str(lib))
+            return
+
+
 def pytest_configure(config):
+    _bundled_nccl()
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box via gpurun)")
 
 

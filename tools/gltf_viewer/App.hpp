@@ -5,7 +5,7 @@
 // is written to a PNG at the end, the ImGui performance overlay ("Frame time %.3f ms", ui/PerformanceOverlay.cpp:15-19)
 // is a JSON list of the same per-frame times, input events come from the command line (Options).
 #pragma once
-#include "CameraController.hpp"
+#include "FlyCamera.hpp"
 #include "WriteImage.hpp"
 
 #include "pbr/AsyncSubmitter.hpp"
@@ -27,7 +27,7 @@ struct Options {
   vk::Extent2D extent {1280, 720};
   std::uint32_t frames {60};
   std::optional<double> fixedDeltaTime;  // default: the measured frame duration, like the reference
-  Input input {};
+  HeldKeys input {};
   double lookX {}, lookY {}, scroll {};  // per frame: cursor movement in pixels, scroll offset
   std::optional<glm::vec3> position;
   std::optional<float> yaw, pitch, fov;
@@ -46,7 +46,7 @@ class App {
   pbr::HdrImage _hdrImage;
   pbr::Image2D _outputImage;  // stands in for the swapchain image
   pbrcu_stream _stream {};
-  CameraController _controller;
+  FlyCamera _camera;
   pbr::Scene _scene;
   std::shared_ptr<pbr::Environment> _environment;
   pbr::Allocation _envSource;
@@ -94,7 +94,7 @@ public:
       , _hdrImage(_tonemapper.allocateHdrImage(*_allocator, _opt.extent))
       , _outputImage(*_allocator, vk::Format::eR8G8B8A8Unorm, _opt.extent)
       , _stream(makeStream())
-      , _controller(_opt.extent.width, _opt.extent.height) {
+      , _camera(makeFlyCamera(_opt.extent.width, _opt.extent.height)) {
     vk::CommandBuffer cmd {_stream};
     {  // App.cpp:262-283: load the asset's first scene through one TransferStager batch
       pbr::TransferStager stager {_gpu, _allocator};
@@ -117,9 +117,8 @@ public:
         _scene.addLight({.position = {6.0f * std::cos(a), -4.0f, 6.0f * std::sin(a)}, .range = 0.0f, .color = {1.0f, 0.95f, 0.9f}, .intensity = 80.0f});
       }
     }
-    _controller.setPose(_opt.position.value_or(CameraController::DEFAULT_POSITION), _opt.yaw.value_or(CameraController::DEFAULT_YAW),
-                        _opt.pitch.value_or(CameraController::DEFAULT_PITCH), _opt.fov.value_or(CameraController::DEFAULT_FOV));
-    _controller.setInput(_opt.input);
+    place(_camera, _opt.position.value_or(glm::vec3 {0.0f}), _opt.yaw.value_or(Limits::startYaw), _opt.pitch.value_or(Limits::startPitch),
+          _opt.fov.value_or(Limits::startFov));
   }
   App(App const&) = delete;
   auto operator=(App const&) -> App& = delete;
@@ -140,12 +139,12 @@ public:
       // "pollEvents": the scripted per-frame input
       if (_opt.lookX != 0.0 || _opt.lookY != 0.0) {
         cursorX += _opt.lookX; cursorY += _opt.lookY;
-        _controller.onCursorMove(cursorX, cursorY);
+        cursorTo(_camera, _opt.input, cursorX, cursorY);
       }
-      if (_opt.scroll != 0.0) _controller.onScroll(0.0, _opt.scroll);
+      if (_opt.scroll != 0.0) scrollBy(_camera, _opt.scroll);
 
-      _controller.update(deltaTime);
-      if (auto const camera = _scene.findCamera(); camera) camera.value()->set(_controller.getCameraData());
+      advance(_camera, _opt.input, deltaTime);
+      if (auto const camera = _scene.findCamera(); camera) camera.value()->set(cameraData(_camera));
       if (_opt.spin) {
         int taken = 0;
         for (auto& node : _scene.iterateAllNodes()) {

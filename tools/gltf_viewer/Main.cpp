@@ -45,17 +45,17 @@ auto main(int const argc, char const* const* const argv) -> int {
       else if (a == "--keys") {
         for (char const c : next()) {
           switch (c) {
-            case 'W': case 'w': opt.input.w = true; break;
-            case 'A': case 'a': opt.input.a = true; break;
-            case 'S': case 's': opt.input.s = true; break;
-            case 'D': case 'd': opt.input.d = true; break;
-            case 'Q': case 'q': opt.input.q = true; break;
-            case 'E': case 'e': opt.input.e = true; break;
+            case 'W': case 'w': opt.input.thrust = 1; break;
+            case 'A': case 'a': opt.input.strafe = -1; break;
+            case 'S': case 's': if (opt.input.thrust == 0) opt.input.thrust = -1; break;
+            case 'D': case 'd': if (opt.input.strafe == 0) opt.input.strafe = 1; break;
+            case 'Q': case 'q': if (opt.input.lift == 0) opt.input.lift = -1; break;
+            case 'E': case 'e': opt.input.lift = 1; break;
             default: throw std::runtime_error("unknown key in --keys");
           }
         }
       }
-      else if (a == "--look") { auto const v = parseFloats(next(), 2, ','); opt.lookX = v[0]; opt.lookY = v[1]; opt.input.rightButton = true; }
+      else if (a == "--look") { auto const v = parseFloats(next(), 2, ','); opt.lookX = v[0]; opt.lookY = v[1]; opt.input.look = true; }
       else if (a == "--scroll") opt.scroll = std::stod(next());
       else if (a == "--position") { auto const v = parseFloats(next(), 3, ','); opt.position = glm::vec3 {float(v[0]), float(v[1]), float(v[2])}; }
       else if (a == "--yaw") opt.yaw = std::stof(next());
