@@ -128,6 +128,14 @@ int pbrcu_lighting_blinnphong_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, s
                                       const float* cam_pos_xyz /* host, n_views*3 */,
                                       void* out_rgba16f, size_t out_pitch, size_t out_view_stride,
                                       pbrcu_stream s);
+/* The batched form of pbrcu_lighting_tonemap_fused: the reference's per-view frame is lighting then tonemap
+ * (src/gltf_viewer/App.cpp:387-392), here one launch for the whole block of views.  View v reads its planes view_stride8
+ * bytes after view v-1's and writes its LDR frame ldr_view_stride bytes (and, when out_rgba16f is not NULL, its HDR frame
+ * hdr_view_stride bytes) after view v-1's.  Every view equals the two-pass result bit for bit. */
+int pbrcu_lighting_tonemap_fused_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, uint32_t n_views,
+                                         const float* cam_pos_xyz /* host, n_views*3 */, void* out_rgba16f, size_t hdr_pitch,
+                                         size_t hdr_view_stride, void* out_rgba8, size_t ldr_pitch, size_t ldr_view_stride,
+                                         pbrcu_stream s);
 /* One frame through HOST buffers (the end-to-end path): H2D of the three planes, K1 (+K2), D2H of
  * the HDR and/or LDR result.  Host pointers should be pinned (pbrcu_host_alloc) for full PCIe rate.
  * hdr_out_host / ldr_out_host may each be NULL.  Synchronises the stream before returning. */
@@ -347,6 +355,15 @@ typedef struct {
  * 0xFFFFFFFF.  Scratch (visibility buffer, piece set-ups) lives in the context and grows on demand. */
 int pbrcu_geometry_pass(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float view[16], const float proj[16],
                         const pbrcu_draw* draws, uint32_t n_draws, uint32_t* prim_id_dev, pbrcu_stream s);
+
+/* The geometry pass of n_views cameras over one set of draws (BASELINE configs[4]: many views of one scene): view v -- camera
+ * views16[16 v ..], projs16[16 v ..], column-major like pbrcu_geometry_pass -- fills the G-buffer view_stride8 / view_stride4
+ * bytes after view v-1's (all planes g0 has, depth included).  The draw tables are built and uploaded once, and consecutive
+ * views run on internal streams with a scratch set each, so their small kernels overlap on the device.  Bit-identical per view
+ * to pbrcu_geometry_pass.  Replaces n_views iterations of PbrRenderSystem::recordGeometryPass (PbrRenderSystem.cpp:367-465). */
+int pbrcu_geometry_pass_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
+                                uint32_t n_views, const float* views16, const float* projs16, const pbrcu_draw* draws,
+                                uint32_t n_draws, pbrcu_stream s);
 
 /* ---- multi-GPU host: ONE process drives the N GPUs of a box (csrc/mg.cu) ---------------------------------------------
  * No counterpart in the reference, which renders on one device from one host thread (core/GpuHandle.cpp:77-81,

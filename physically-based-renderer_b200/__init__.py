@@ -115,6 +115,7 @@ _SIGNATURES = {
     "pbrcu_tonemap_aces_gamma": (_i, [_vp, _vp, _sz, _u32, _u32, Rect, _vp, _sz, _vp]),
     "pbrcu_lighting_tonemap_fused": (_i, [_vp, _PG, _f3, Rect, _vp, _sz, _vp, _sz, _vp]),
     "pbrcu_lighting_blinnphong_batched": (_i, [_vp, _PG, _sz, _sz, _u32, _f3, _vp, _sz, _sz, _vp]),
+    "pbrcu_lighting_tonemap_fused_batched": (_i, [_vp, _PG, _sz, _u32, _f3, _vp, _sz, _sz, _vp, _sz, _sz, _vp]),
     "pbrcu_frame_host": (_i, [_vp, _vp, _vp, _vp, _u32, _u32, _f3, _vp, _vp, _vp]),
     "pbrcu_cube_chain_texels": (_sz, [_u32, _u32]),
     "pbrcu_cube_mip_offset": (_sz, [_u32, _u32]),
@@ -137,6 +138,7 @@ _SIGNATURES = {
     "pbrcu_ibl_set_exact_filtering": (_i, [_vp, _i]),
     "pbrcu_shade_set_texture_unit": (_i, [_vp, _i]),
     "pbrcu_geometry_pass": (_i, [_vp, C.POINTER(GBuffer), _vp, _vp, C.POINTER(Draw), C.c_uint32, _vp, _vp]),
+    "pbrcu_geometry_pass_batched": (_i, [_vp, C.POINTER(GBuffer), _sz, _sz, _u32, _vp, _vp, C.POINTER(Draw), _u32, _vp]),
     "pbrcu_ibl_prefilter_ggx": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, _vp]),
     "pbrcu_ibl_prefilter_ggx_replicated": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _u32, _u32, _u32, _u32, C.POINTER(_vp), _u32, _vp]),
     "pbrcu_ibl_source_create": (_i, [_vp, _vp, _u32, _u32, _vp, C.POINTER(_vp)]),

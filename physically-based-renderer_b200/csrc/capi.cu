@@ -85,6 +85,12 @@ extern "C" void pbrcu_ctx_destroy(pbrcu_ctx* ctx) {
     if (e) cudaEventDestroy(e);
   pbrcu::cube_tex_destroy(&ctx->cube);
   if (ctx->raster_scratch) cudaFree(ctx->raster_scratch);
+  for (int k = 0; k < pbrcu::kRasterSlots; ++k) {
+    if (ctx->raster_slot_stream[k]) { cudaStreamSynchronize(ctx->raster_slot_stream[k]); cudaStreamDestroy(ctx->raster_slot_stream[k]); }
+    if (ctx->raster_slot_done[k]) cudaEventDestroy(ctx->raster_slot_done[k]);
+    if (ctx->raster_slot_scratch[k]) cudaFree(ctx->raster_slot_scratch[k]);
+  }
+  if (ctx->raster_start) cudaEventDestroy(ctx->raster_start);
   if (ctx->cube_stage) cudaFree(ctx->cube_stage);
   if (ctx->cube_mm) cudaFree(ctx->cube_mm);
   delete ctx;

@@ -306,3 +306,42 @@ extern "C" int pbrcu_lighting_blinnphong_batched(pbrcu_ctx* ctx, const pbrcu_gbu
   p.hdr_view_stride = out_view_stride;
   return launch_tier_a<MODE_LIGHT>(ctx, p, n_views, st);
 }
+
+// The reference's per-view frame is lighting THEN tonemap (src/gltf_viewer/App.cpp:387-392); over a block of views both passes
+// run as ONE launch: blockIdx.y selects the view, the tonemapper consumes the fp16-rounded lighting value, so every view equals the
+// two-pass result bit for bit.  out_rgba16f may be NULL (LDR only: 28 B/px instead of 36).
+extern "C" int pbrcu_lighting_tonemap_fused_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, uint32_t n_views,
+                                                    const float* cam_pos_xyz, void* out_rgba16f, size_t hdr_pitch, size_t hdr_view_stride,
+                                                    void* out_rgba8, size_t ldr_pitch, size_t ldr_view_stride, pbrcu_stream s) {
+  PBRCU_REQUIRE(ctx && g0 && cam_pos_xyz && out_rgba8, "NULL argument");
+  PBRCU_REQUIRE(n_views >= 1 && n_views <= 65535, "n_views must be in [1, 65535]");
+  PBRCU_REQUIRE(ldr_pitch >= size_t(g0->width) * 4 && ldr_pitch % 4 == 0, "ldr_pitch too small or not a multiple of 4");
+  PBRCU_REQUIRE(view_stride8 >= g0->pitch8 * g0->height && view_stride8 % 8 == 0 && ldr_view_stride >= ldr_pitch * g0->height && ldr_view_stride % 4 == 0,
+                "view stride smaller than one view or misaligned");
+  if (out_rgba16f)
+    PBRCU_REQUIRE(hdr_pitch >= size_t(g0->width) * 8 && hdr_pitch % 8 == 0 && hdr_view_stride >= hdr_pitch * g0->height && hdr_view_stride % 8 == 0,
+                  "hdr pitch / view stride too small or misaligned");
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (ctx->cams_cap < n_views) {
+    if (ctx->cams_dev) PBRCU_CUDA(cudaFree(ctx->cams_dev));
+    ctx->cams_dev = nullptr; ctx->cams_cap = 0;
+    PBRCU_CUDA(cudaMalloc(&ctx->cams_dev, size_t(n_views) * 3 * sizeof(float)));
+    ctx->cams_cap = n_views;
+  }
+  PBRCU_CUDA(cudaMemcpyAsync(ctx->cams_dev, cam_pos_xyz, size_t(n_views) * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+  pbrcu_rect rect{0, 0, g0->width, g0->height};
+  TierAParams p{};
+  if (int rc = fill_gbuffer_params(g0, rect, p)) return rc;
+  p.ldr = static_cast<uint8_t*>(out_rgba8);
+  p.ldr_pitch = ldr_pitch;
+  p.ldr_view_stride = ldr_view_stride;
+  p.cams = ctx->cams_dev;
+  p.view_stride8 = view_stride8;
+  if (out_rgba16f) {
+    p.hdr = static_cast<uint8_t*>(out_rgba16f);
+    p.hdr_pitch = hdr_pitch;
+    p.hdr_view_stride = hdr_view_stride;
+    return launch_tier_a<MODE_FUSED_HDR_LDR>(ctx, p, n_views, st);
+  }
+  return launch_tier_a<MODE_FUSED_LDR>(ctx, p, n_views, st);
+}

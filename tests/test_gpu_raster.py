@@ -228,3 +228,31 @@ def test_chunk_queue_overflow_falls_back(pbr, dev, oracle, monkeypatch):
     for cap in ("0", "1", "17", "35", "36", "71"):
         monkeypatch.setenv("PBRCU_RASTER_QUEUE_CAP", cap)
         assert_same(device_pass(pbr, dev, walls, view, proj, W, H), want, f"chunk queue cap {cap}")
+
+
+def test_batched_views_equal_single_passes(pbr, dev, oracle):
+    """pbrcu_geometry_pass_batched: six cameras (more than the four internal streams / scratch sets, so sets are re-used) over one
+    scene, one of them close enough that the ground plane is clipped -- every view's planes equal a pbrcu_geometry_pass call with
+    that camera bit for bit, and the first view the oracle's; run twice (the scratch sets and tables of the first call are re-used)."""
+    W, H, nv = 200, 112, 6
+    draws = raster_scene(1)
+    cams = [camera((0.5, -1.5, -6.0), (0, 0, 0), aspect=W / H)] + [camera((8 * np.cos(a), -1.0 - a, 8 * np.sin(a)), (0, 0, 0), aspect=W / H) for a in np.linspace(0.3, 5.5, nv - 1)]
+    singles = [device_pass(pbr, dev, draws, v, p, W, H) for v, p in cams]
+    assert_same(singles[0], oracle.geometry_pass(draws, cams[0][0], cams[0][1], W, H, extended=True), "view 0 vs oracle")
+    s8, s4 = W * H * 8, W * H * 4
+    stale8, stale4 = np.full((nv, H, W, 4), 0x1234, np.uint16), np.full((nv, H, W, 4), 0x55, np.uint8)
+    bufs = dict(pos=dev.upload(stale8), nrm=dev.upload(stale8), alb=dev.upload(stale8), emi=dev.upload(stale8), orm=dev.upload(stale4),
+                depth=dev.upload(np.full((nv, H, W), 0.5, np.float32)))
+    g0 = pbr.GBuffer()
+    g0.width, g0.height, g0.pitch8, g0.pitch4 = W, H, W * 8, W * 4
+    g0.positions, g0.normals, g0.albedo, g0.emissive, g0.orm, g0.depth = (bufs[k].ptr for k in ("pos", "nrm", "alb", "emi", "orm", "depth"))
+    arr, keep = upload_draws(pbr, dev, draws)
+    views = np.ascontiguousarray(np.stack([np.asarray(v, np.float32).reshape(16) for v, _ in cams]))
+    projs = np.ascontiguousarray(np.stack([np.asarray(p, np.float32).reshape(16) for _, p in cams]))
+    for attempt in range(2):
+        dev.lib.geometry_pass_batched(dev.ctx, C.byref(g0), s8, s4, nv, views.ctypes.data, projs.ctypes.data, arr, len(draws), None)
+        dev.sync()
+        got = dict(pos=bufs["pos"].download((nv, H, W, 4), np.uint16), nrm=bufs["nrm"].download((nv, H, W, 4), np.uint16), alb=bufs["alb"].download((nv, H, W, 4), np.uint16),
+                   emi=bufs["emi"].download((nv, H, W, 4), np.uint16), orm=bufs["orm"].download((nv, H, W, 4), np.uint8), depth=bufs["depth"].download((nv, H, W), np.float32))
+        for v in range(nv):
+            assert_same({k: a[v] for k, a in got.items()}, {k: a for k, a in singles[v].items() if k != "prim"}, f"attempt {attempt}, view {v}")

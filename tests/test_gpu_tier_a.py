@@ -148,6 +148,36 @@ def test_batched_views(pbr, dev, oracle):
         assert_hdr_parity(got[v], want, peak=2.0, what=f"view {v}")
 
 
+def test_batched_fused_views_equal_two_passes(pbr, dev, oracle):
+    """pbrcu_lighting_tonemap_fused_batched (the reference's per-view lighting -> tonemap, App.cpp:387-392, over a block of views in
+    one launch): every view's HDR equals the batched lighting pass bit for bit, its LDR the tonemap pass of that HDR bit for bit
+    (so it inherits their pin to the reference's shaders); LDR-only gives the same LDR; odd width exercises the scalar path."""
+    for w, h in ((64, 32), (37, 11)):
+        nv = 4
+        gs = [synth_gbuffer(w, h, seed=200 + v) for v in range(nv)]
+        pos = np.stack([g["pos"] for g in gs]); nrm = np.stack([g["nrm"] for g in gs]); alb = np.stack([g["alb"] for g in gs])
+        gb = pbr.GBuffer()
+        gb.width, gb.height, gb.pitch8, gb.pitch4 = w, h, w * 8, w * 4
+        gb.positions, gb.normals, gb.albedo = dev.upload(pos.view(np.uint16)).ptr, dev.upload(nrm.view(np.uint16)).ptr, dev.upload(alb).ptr
+        cams = np.array([[0, 0, 12], [12, 0, 0], [0, 3, -12], [0, 0, 0]], np.float32)
+        cp = cams.ctypes.data_as(C.POINTER(C.c_float))
+        s8, s4 = w * h * 8, w * h * 4
+        hdr2, hdr, ldr, ldr_only, ldr2 = dev.alloc(nv * s8), dev.alloc(nv * s8), dev.alloc(nv * s4), dev.alloc(nv * s4), dev.alloc(s4)
+        dev.lib.lighting_blinnphong_batched(dev.ctx, C.byref(gb), s8, s4, nv, cp, hdr2.ptr, w * 8, s8, None)
+        dev.lib.lighting_tonemap_fused_batched(dev.ctx, C.byref(gb), s8, nv, cp, hdr.ptr, w * 8, s8, ldr.ptr, w * 4, s4, None)
+        dev.lib.lighting_tonemap_fused_batched(dev.ctx, C.byref(gb), s8, nv, cp, None, 0, 0, ldr_only.ptr, w * 4, s4, None)
+        dev.sync()
+        got_hdr, got_ldr = hdr.download((nv, h, w, 4), np.uint16), ldr.download((nv, h, w, 4), np.uint8)
+        assert np.array_equal(got_hdr, hdr2.download((nv, h, w, 4), np.uint16))
+        assert np.array_equal(ldr_only.download((nv, h, w, 4), np.uint8), got_ldr)
+        for v in range(nv):
+            dev.lib.tonemap_aces_gamma(dev.ctx, hdr2.ptr + v * s8, w * 8, w, h, pbr.WHOLE, ldr2.ptr, w * 4, None)
+            dev.sync()
+            assert np.array_equal(got_ldr[v], ldr2.download((h, w, 4), np.uint8)), f"view {v}"
+            _, want = oracle.lighting(gs[v]["pos"], gs[v]["nrm"], gs[v]["alb"], cams[v])
+            assert_hdr_parity(got_hdr[v], want, peak=2.0, what=f"fused batched view {v}")
+
+
 def test_frame_host(pbr, dev, oracle):
     w, h = 200, 50
     g = synth_gbuffer(w, h, seed=3)
