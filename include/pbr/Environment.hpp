@@ -14,14 +14,20 @@ struct EnvironmentCreateInfo {
   std::uint32_t sampleCount {1024};
   std::uint32_t irradianceResolution {64};
   std::uint32_t lutResolution {512};
+  bool exactFiltering {false};  // fp32 filter weights for every ambient tap of the shading pass (pbrcu_ibl.flags)
 };
 
 class Environment {
   core::SharedGpuHandle _gpu;
   EnvironmentCreateInfo _info;
   Allocation _source, _prefiltered, _irradiance, _lut;
+  pbrcu_ibl_accel* _accel {};  // footprint records + texture copies the fast shading kernels sample (built by precompute)
 
 public:
+  Environment(Environment const&) = delete;
+  auto operator=(Environment const&) -> Environment& = delete;
+  ~Environment() { (void)pbrcu_ibl_accel_free(_gpu ? _gpu->getContext() : nullptr, _accel); }
+
   Environment(core::SharedGpuHandle gpu, IAllocator& allocator, EnvironmentCreateInfo info)
       : _gpu(std::move(gpu)), _info(info) {
     auto const chainBytes = pbrcu_cube_chain_texels(info.cubeResolution, info.mipLevels) * 8;
@@ -38,9 +44,21 @@ public:
     auto* s = cmd.stream();
     core::check(pbrcu_ibl_equirect_to_cube(ctx, equirectRgba32fDevice, width, height, _info.cubeResolution, _source.get(), s), "Environment: equirect_to_cube");
     core::check(pbrcu_ibl_cube_mipgen(ctx, _source.get(), _info.cubeResolution, _info.mipLevels, s), "Environment: cube_mipgen");
-    core::check(pbrcu_ibl_prefilter_ggx(ctx, _source.get(), _info.cubeResolution, _info.mipLevels, _info.sampleCount, _prefiltered.get(), 0, _info.mipLevels - 1, 0, 1, s), "Environment: prefilter_ggx");
-    core::check(pbrcu_ibl_irradiance(ctx, _source.get(), _info.cubeResolution, _info.mipLevels, _info.irradianceResolution, _info.sampleCount, _irradiance.get(), s), "Environment: irradiance");
+    // K6 and K7 convolve the same environment: its texture copy is prepared once for both
+    pbrcu_ibl_source* source = nullptr;
+    core::check(pbrcu_ibl_source_create(ctx, _source.get(), _info.cubeResolution, _info.mipLevels, s, &source), "Environment: source texture");
+    int const rcPrefilter = pbrcu_ibl_prefilter_ggx_prepared(ctx, source, _info.sampleCount, _prefiltered.get(), 0, _info.mipLevels - 1, 0, 1, nullptr, 0, s);
+    int const rcIrradiance = pbrcu_ibl_irradiance_prepared(ctx, source, _info.irradianceResolution, _info.sampleCount, _irradiance.get(), s);
+    (void)pbrcu_stream_synchronize(s);  // the source object must outlive the work that samples it
+    (void)pbrcu_ibl_source_free(ctx, source);
+    core::check(rcPrefilter, "Environment: prefilter_ggx");
+    core::check(rcIrradiance, "Environment: irradiance");
     core::check(pbrcu_ibl_brdf_lut(ctx, _info.lutResolution, _info.sampleCount, static_cast<float*>(_lut.get()), s), "Environment: brdf_lut");
+    // the records / texture copies of the finished textures (a snapshot: rebuilt by every precompute)
+    (void)pbrcu_ibl_accel_free(ctx, _accel);
+    _accel = nullptr;
+    auto const plain = raw();
+    core::check(pbrcu_ibl_accel_build(ctx, &plain, &_accel, s), "Environment: footprint records");
   }
 
   [[nodiscard]] auto getInfo() const noexcept -> EnvironmentCreateInfo const& { return _info; }
@@ -53,6 +71,8 @@ public:
     i.irradiance = _irradiance.get(); i.irr_res = _info.irradianceResolution;
     i.prefiltered = _prefiltered.get(); i.pref_res = _info.cubeResolution; i.pref_mips = _info.mipLevels;
     i.lut = static_cast<float const*>(_lut.get()); i.lut_res = _info.lutResolution;
+    i.accel = _accel;
+    i.flags = _info.exactFiltering ? PBRCU_IBL_EXACT : 0u;
     return i;
   }
 };

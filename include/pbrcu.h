@@ -161,7 +161,12 @@ typedef struct {
    * memory (1.07 GB for a 2048^2 12-mip chain: sized for 180 GB of HBM) for a quarter of the L1
    * wavefronts and no address clamping in the shading kernel.  Results are bit-identical. */
   const pbrcu_ibl_accel* accel;
+  /* per-call filtering of the ambient term (K3), OR-ed with the context's defaults (pbrcu_ibl_set_exact_filtering /
+   * pbrcu_shade_set_texture_unit): 0 = default (prefiltered cube with fp32 weights, irradiance + LUT through the texture unit) */
+  uint32_t flags;
 } pbrcu_ibl;
+#define PBRCU_IBL_EXACT 1u        /* fp32 weights for all four taps (bit-identical to the plain four-load filter) */
+#define PBRCU_IBL_TEXTURE_UNIT 2u /* prefiltered + irradiance cubes through the texture unit, records where the contrast flag is set */
 
 /* tile light lists built by pbrcu_cluster_lights: tiles of PBRCU_TILE x PBRCU_TILE pixels */
 #define PBRCU_TILE 16
@@ -275,14 +280,14 @@ int pbrcu_ibl_cube_mipgen(pbrcu_ctx* ctx, void* chain_dev, uint32_t base_res, ui
  * irradiance copy carries the same kind of flag at 12 % footprint range with the record as fallback;
  * within 5e-4 relative of the fp32-weight filter), the prefiltered cube always from the fp32-weight
  * footprint records; exact != 0 takes all four taps from the records. */
-int pbrcu_ibl_set_exact_filtering(pbrcu_ctx* ctx, int exact);
+int pbrcu_ibl_set_exact_filtering(pbrcu_ctx* ctx, int exact); /* context default; per call for K3: pbrcu_ibl.flags */
 /* K3 (when ibl->accel is set): on != 0 fetches the prefiltered and irradiance cubes through the texture
  * unit (one TEX each; flagged copies, 12 % footprint range -> within 7e-4 relative of the fp32-weight
  * filter) and falls back to the fp32-weight footprint records where the filtered flag is set.  Default
  * off: with per-pixel random roughness almost every warp holds a flagged lane (coarse levels differ by
  * more than 12 % texel to texel), so the fallback runs anyway; measured 229 us vs 219 us per 4K frame.
  * Worth it only for content whose materials are coherent over a warp (179 us with no fallback). */
-int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on);
+int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on); /* context default; per call: pbrcu_ibl.flags */
 /* K7: GGX prefilter of levels [first_mip,last_mip] (level 0 = copy), nsamples per texel.
  * shard/nshards split each level's texels into contiguous blocks for multi-GPU (0,1 = all). */
 int pbrcu_ibl_prefilter_ggx(pbrcu_ctx* ctx, const void* src_chain_dev, uint32_t base_res,

@@ -22,6 +22,7 @@ LIB_PATH = HERE / "lib" / "libpbrcu.so"
 HEADER = ROOT / "include" / "pbrcu.h"
 
 PBRCU_TILE = 16
+IBL_EXACT, IBL_TEXTURE_UNIT = 1, 2  # pbrcu_ibl.flags
 
 
 class PbrcuError(RuntimeError):
@@ -51,7 +52,7 @@ class Light(C.Structure):
 class Ibl(C.Structure):
     _fields_ = [("irradiance", C.c_void_p), ("irr_res", C.c_uint32),
                 ("prefiltered", C.c_void_p), ("pref_res", C.c_uint32), ("pref_mips", C.c_uint32),
-                ("lut", C.c_void_p), ("lut_res", C.c_uint32), ("accel", C.c_void_p)]
+                ("lut", C.c_void_p), ("lut_res", C.c_uint32), ("accel", C.c_void_p), ("flags", C.c_uint32)]
 
 
 class Texture(C.Structure):

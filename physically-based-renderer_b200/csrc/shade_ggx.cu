@@ -612,7 +612,8 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   PBRCU_REQUIRE(uint64_t(p.ntiles) * p.ntx < (1ull << 31), "rect too large");  // 16x16 tiles: beyond 100k x 100k pixels
   p.ntx_magic = p.ntx == 1 ? 0u : uint32_t(((1ull << 32) + p.ntx - 1) / p.ntx);  // 0: one tile per row
   cudaStream_t st = static_cast<cudaStream_t>(s);
-  const bool tex = p.q_pref && ctx->shade_tex;
+  const bool exact = ctx->exact_ibl_filter || (ibl && (ibl->flags & PBRCU_IBL_EXACT));
+  const bool tex = p.q_pref && !exact && (ctx->shade_tex || (ibl && (ibl->flags & PBRCU_IBL_TEXTURE_UNIT)));
   // ---- one light list the HOST holds (the headline frame, the batched views, the facade): lights in the kernel's
   // parameter block, IBL by texture gathers (shade_ggx_cl.cu) ----
   const bool host_lights = n_lights == 0 || is_host_pointer(lights_dev);
@@ -622,7 +623,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   const int cl_mode = cl_env ? atoi(cl_env) : 2;
   const bool use_cl = cl_mode != 0;
   if (use_cl && !tex && p.tile_counts == nullptr && n_lights <= uint32_t(kClMaxLights) && host_lights && (!p.has_ibl || (p.q_pref && ibl->accel->g_pref.tex))) {
-    int amb = !p.has_ibl ? 0 : (p.t_irr && p.t_lut && !ctx->exact_ibl_filter) ? 1 : 2;
+    int amb = !p.has_ibl ? 0 : (p.t_irr && p.t_lut && !exact) ? 1 : 2;
     if (amb != 0 && cl_mode != 1) amb += 2;  // footprint records instead of gathers
     return launch_shade_cl(p, lights_dev, n_lights, ibl ? ibl->accel : nullptr, amb, n_views > 1 ? LIST_ONE_BATCHED : LIST_ONE, ctx->sm_count, st);
   }
@@ -643,7 +644,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   const int lists = n_views > 1 ? LIST_ONE_BATCHED : one_list ? LIST_ONE : LIST_TILED;
   if (!tex && lists != LIST_TILED && (p.q_pref || !p.has_ibl)) {  // one list, footprint records or no IBL
     // irradiance and LUT through the texture unit unless the caller asked for fp32 weights everywhere
-    const bool ambtex = p.has_ibl && p.t_irr && p.t_lut && !ctx->exact_ibl_filter;
+    const bool ambtex = p.has_ibl && p.t_irr && p.t_lut && !exact;
     if (lists == LIST_ONE_BATCHED) {
       if (ambtex) shade_ggx_one_kernel<true, true><<<grid, kShadeThreads, 0, st>>>(p);
       else shade_ggx_one_kernel<true, false><<<grid, kShadeThreads, 0, st>>>(p);
@@ -657,7 +658,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
     return launch_check("shade_ggx_one_kernel");
   }
   if (tex) launch_shade<IBL_TEX>(p, lists, grid, st);
-  else if (p.q_pref && p.t_irr && p.t_lut && !ctx->exact_ibl_filter) launch_shade<IBL_RECORDS_AMBTEX>(p, lists, grid, st);
+  else if (p.q_pref && p.t_irr && p.t_lut && !exact) launch_shade<IBL_RECORDS_AMBTEX>(p, lists, grid, st);
   else if (p.q_pref) launch_shade<IBL_RECORDS>(p, lists, grid, st);
   else launch_shade<IBL_PLAIN>(p, lists, grid, st);
   return launch_check("shade_ggx_kernel");

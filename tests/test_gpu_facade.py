@@ -120,3 +120,14 @@ def test_facade_mesh_scene_geometry_and_lighting(oracle, tmp_path):
     _, want_hdr = oracle.lighting(want["pos"].view(np.float16), want["nrm"].view(np.float16), want["alb"], eye)
     assert np.abs(f16(hdr) - f16(want_hdr)).max() <= 1e-3
     assert np.abs(ldr.astype(int) - oracle.tonemap(hdr).astype(int)).max() <= 1
+
+
+def test_device_group_frame_from_cpp():
+    """tests/cpp/mg_frame.cpp: a frame over pbr::DeviceGroup (the C multi-GPU host behind the facade) -- two and three members on GPU 0,
+    and all GPUs with the NCCL gather when the box has several -- equals the single-device frame bit for bit."""
+    import os
+    subprocess.run(["make", "-C", str(CPP)], check=True, capture_output=True)
+    env = dict(os.environ)
+    r = subprocess.run([str(CPP / "build" / "mg_frame")], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0 and "mg_frame ok" in r.stdout, r.stdout + r.stderr
+

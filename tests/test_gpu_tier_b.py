@@ -708,3 +708,41 @@ def test_prepared_source_equals_the_plain_entry_points(dev, oracle):
     assert np.array_equal(got_shards.download(chain.shape, np.uint16), w)
     assert np.array_equal(got_irr.download((6, ires, ires, 4), np.uint16), want_irr.download((6, ires, ires, 4), np.uint16))
     dev.lib.ibl_source_free(dev.ctx, src)
+
+
+def test_per_call_filter_flags_equal_the_context_switches(pbr, dev, oracle):
+    """pbrcu_ibl.flags selects the ambient filtering per call: PBRCU_IBL_EXACT == pbrcu_ibl_set_exact_filtering(ctx, 1),
+    PBRCU_IBL_TEXTURE_UNIT == pbrcu_shade_set_texture_unit(ctx, 1), bit for bit, on the device-list, host-list and tiled kernels."""
+    host, bufs = build_ibl(dev, oracle)
+    w, h, nl = 70, 50, 6
+    g = synth_gbuffer(w, h, seed=91, tier_b=True)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    lights = synth_lights(nl, seed=3, ranged=True)
+    ld = dev.upload(lights)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    tiles = pbr.LightTiles()
+    dev.lib.light_tiles_alloc(dev.ctx, w, h, nl, C.byref(tiles))
+    dev.lib.cluster_lights(dev.ctx, C.byref(gb), ld.ptr, nl, C.byref(tiles), None)
+    out = dev.alloc(w * h * 8)
+
+    def run(ptr, use_tiles, flags):
+        ibl.flags = flags
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(0.5, -1.0, 12.0), ptr, nl, C.byref(tiles) if use_tiles else None, C.byref(ibl), pbr.WHOLE, out.ptr, w * 8, None)
+        dev.sync()
+        ibl.flags = 0
+        return out.download((h, w, 4), np.uint16)
+
+    for ptr, use_tiles in ((ld.ptr, False), (lights.ctypes.data, False), (ld.ptr, True)):
+        default = run(ptr, use_tiles, 0)
+        dev.lib.ibl_set_exact_filtering(dev.ctx, 1)
+        exact_ctx = run(ptr, use_tiles, 0)
+        dev.lib.ibl_set_exact_filtering(dev.ctx, 0)
+        assert np.array_equal(run(ptr, use_tiles, pbr.IBL_EXACT), exact_ctx)
+        assert not np.array_equal(exact_ctx, default), "the exact mode should differ from the default somewhere on this frame"
+        dev.lib.shade_set_texture_unit(dev.ctx, 1)
+        tex_ctx = run(ptr, use_tiles, 0)
+        dev.lib.shade_set_texture_unit(dev.ctx, 0)
+        assert np.array_equal(run(ptr, use_tiles, pbr.IBL_TEXTURE_UNIT), tex_ctx)
+        assert np.array_equal(run(ptr, use_tiles, 0), default), "flags must not stick"
+    dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
