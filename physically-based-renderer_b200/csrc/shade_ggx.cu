@@ -186,12 +186,12 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
       }
     }
     const float dr = lo(dr2) + hi(dr2), dg = lo(dg2) + hi(dg2), db = lo(db2) + hi(db2);
-    if (!inside) continue;
+    // every lane reaches the store at the end of the iteration together (`have`: it owns a texel of the rect; a cleared texel is
+    // stored as 0), so the peer-store instantiations can pair the texels of neighbouring lanes into 16-byte stores
     const size_t outo = size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
-    if (!lit) {
-      store_texel<PEERS>(p, outo, make_uint2(0u, 0u));
-      continue;
-    }
+    const bool have = inside;
+    uint2 texel = make_uint2(0u, 0u);
+    if (have && lit) {
     // ---- ambient: split-sum image-based lighting (Karis 2013) ----
     float ar = 0.f, ag = 0.f, ab = 0.f;
     if (p.has_ibl) {
@@ -239,7 +239,10 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     }
     // oracle order: (direct + ambient) + emissive
     Lr = fminf((dr + ar) + Lr, 65504.0f); Lg = fminf((dg + ag) + Lg, 65504.0f); Lb = fminf((db + ab) + Lb, 65504.0f);
-    store_texel<PEERS>(p, outo, make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a)));
+    texel = make_uint2(f2_to_h2(Lr, Lg), f2_to_h2(Lb, base_a));
+    }
+    if (PEERS) store_texel_paired(p, outo, texel, have);
+    else if (have) stg_stream8(p.out + outo, texel);
   }
   cp_async_wait<0>();
 }
@@ -579,6 +582,12 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   p.n_replicas = n_replicas;
   p.out_is_multicast = multicast ? 1 : 0;
   for (uint32_t k = 0; k < n_replicas; ++k) p.replica[k] = static_cast<uint8_t*>(replicas[k]);
+  {
+    bool aligned = reinterpret_cast<uintptr_t>(out_rgba16f) % 16 == 0 && out_pitch % 16 == 0;
+    for (uint32_t k = 0; k < n_replicas; ++k) aligned = aligned && reinterpret_cast<uintptr_t>(replicas[k]) % 16 == 0;
+    const char* e = getenv("PBRCU_PAIR_STORES");  // (0: 8-byte stores only -- the A/B switch of bench.py's fused-gather legs)
+    p.pair_stores = aligned && !(e && atoi(e) == 0) ? 1 : 0;
+  }
   p.pitch8 = g->pitch8; p.pitch4 = g->pitch4; p.out_pitch = out_pitch;
   p.x0 = rect.x0; p.y0 = rect.y0; p.x1 = rect.x0 + rect.w; p.y1 = rect.y0 + rect.h;
   p.tx0 = rect.x0 / kTile; p.ty0 = rect.y0 / kTile;

@@ -49,6 +49,7 @@ struct ShadeParams {
   uint32_t n_replicas;
   uint8_t* replica[PBRCU_MAX_REPLICAS];
   int out_is_multicast;  // pbrcu_shade_ggx_ibl_multicast: `out` is a multimem address
+  int pair_stores;       // every frame address and the pitch are 16-byte aligned: neighbouring texels may leave as one 16-byte store
 };
 
 // the finished texel: streamed to the local frame and to every replica; or ONE multimem store to a multicast address,
@@ -66,6 +67,29 @@ __device__ __forceinline__ void store_texel(const ShadeParams& p, size_t off, ui
   }
   stg_stream8(p.out + off, v);
   for (uint32_t k = 0; k < p.n_replicas; ++k) stg_stream8(p.replica[k] + off, v);
+}
+
+// The same for the kernels whose lanes all reach the store together (shade_ggx_kernel): lanes 2k / 2k+1 hold the horizontally
+// adjacent texels x (even) / x + 1 of one row, so where both exist the even lane stores BOTH as one 16-byte store -- half the
+// packets on NVLink for the peer frames (8-byte stores reached ~510 GB/s of ingress at N = 8).  `have`: this lane owns a texel.
+__device__ __forceinline__ void store_texel_paired(const ShadeParams& p, size_t off, uint2 v, bool have) {
+  const unsigned full = 0xffffffffu;
+  const uint32_t nx = __shfl_down_sync(full, v.x, 1), ny = __shfl_down_sync(full, v.y, 1);
+  const bool right_has = __shfl_down_sync(full, int(have), 1) != 0, left_has = __shfl_up_sync(full, int(have), 1) != 0;
+  const bool even = (threadIdx.x & 1u) == 0;
+  if (p.pair_stores && even && have && right_has) {
+    const uint4 w = make_uint4(v.x, v.y, nx, ny);
+    if (p.out_is_multicast) {
+      asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p.out + off), "f"(__uint_as_float(w.x)), "f"(__uint_as_float(w.y)),
+                   "f"(__uint_as_float(w.z)), "f"(__uint_as_float(w.w))
+                   : "memory");
+      return;
+    }
+    stg_stream(p.out + off, w);
+    for (uint32_t k = 0; k < p.n_replicas; ++k) stg_stream(p.replica[k] + off, w);
+    return;
+  }
+  if (have && !(p.pair_stores && !even && left_has)) store_texel<true>(p, off, v);  // (an odd lane whose left neighbour stored for it is done)
 }
 
 // how a work item gets its light list

@@ -1,0 +1,24 @@
+#!/bin/bash
+# Regenerates every round-2 file under profiles/ that comes from ONE GPU, from the build in the tree:
+#     gpurun --timeout 3000 -- 'bash scratch/make_profiles.sh'      (then: bash scratch/profiles_collect.sh here, where ncu -i works too)
+# Writes raw material to gpurun_out/prof/ (bench lines, the ncu launch list, .ncu-rep captures).  Each ncu command runs only after the
+# same command exited 0 without ncu.  Numbers printed under ncu are never bench values.
+set -u
+O=gpurun_out/prof
+mkdir -p $O
+python bench.py --impl reference > $O/bench_reference.json 2> $O/bench_reference.err; echo "reference arm exit $?"
+python bench.py > $O/bench_n1.json 2> $O/bench_n1.err; echo "bench n1 exit $?"
+CMD="python bench.py --steps 5 --warmup 3 --no-cpu --mg-host none"
+$CMD > $O/plain_launches.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1; echo "launch list exit $?"
+CMD2="python bench.py --steps 3 --warmup 3 --no-cpu --no-extra"
+$CMD2 > $O/plain_k3.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:shade_ggx_cl_kernel -s 3 -c 2 -o $O/k3_cl $CMD2 > $O/ncu_k3.log 2>&1; echo "ncu k3 exit $?"
+PBRCU_K3_CL=1 $CMD2 > $O/plain_k3_gather.log 2>&1 &&
+PBRCU_K3_CL=1 ncu --set full --clock-control none --import-source on -k regex:shade_ggx_cl_kernel -s 3 -c 1 -o $O/k3_cl_gather $CMD2 > $O/ncu_k3g.log 2>&1; echo "ncu k3 gather exit $?"
+$CMD2 > $O/plain_k7.log 2>&1 &&
+ncu --set full --clock-control none -k regex:conv_kernel -c 14 -o $O/k7 $CMD2 > $O/ncu_k7.log 2>&1; echo "ncu k7 exit $?"
+CMD3="python bench.py --steps 3 --warmup 3 --no-cpu --mg-host none"
+$CMD3 > $O/plain_misc.log 2>&1 &&
+ncu --set full --clock-control none -k regex:'cluster_lights_kernel|shade_ggx_kernel|equirect_to_cube_kernel|cube_mip_kernel|brdf_lut_kernel' -c 24 -o $O/misc $CMD3 > $O/ncu_misc.log 2>&1; echo "ncu misc exit $?"
+ls -la $O

@@ -64,4 +64,4 @@ def main(raw, src=None, max_kernels=4):
 
 
 if __name__ == "__main__":
-    main(*sys.argv[1:3])
+    main(sys.argv[1], (sys.argv[2] or None) if len(sys.argv) > 2 else None, int(sys.argv[3]) if len(sys.argv) > 3 else 4)

@@ -556,6 +556,13 @@ def test_shade_replicated_stores_equal_the_plain_frame(pbr, dev, oracle, mode):
     for what, buf in [("own frame", own)] + [(f"replica {k}", r) for k, r in enumerate(reps)]:
         got = buf.download((h, w, 4), np.uint16)
         assert np.array_equal(got, expect), f"{mode}: {what} differs in {np.count_nonzero(got != expect)} values"
+    # a replica that is only 8-byte aligned: the kernel must fall back from 16-byte pair stores to 8-byte stores, same bits
+    shifted = dev.upload(np.full((h * w + 1, 4), 0x7B7B, np.uint16))
+    one = (C.c_void_p * 1)(shifted.ptr + 8)
+    dev.lib.shade_ggx_ibl_replicated(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.Rect(*rect), own.ptr, w * 8, one, 1, None)
+    dev.sync()
+    got = shifted.download((h * w + 1, 4), np.uint16)
+    assert (got[0] == 0x7B7B).all() and np.array_equal(got[1:].reshape(h, w, 4), expect), f"{mode}: 8-byte aligned replica differs"
     # no replicas = the plain call
     dev.lib.shade_ggx_ibl_replicated(dev.ctx, C.byref(gb), cam, ld.ptr, nl, targ, iarg, pbr.WHOLE, own.ptr, w * 8, None, 0, None)
     dev.sync()
