@@ -40,7 +40,7 @@ N_LIGHTS = 4
 B_PER_PX_K3 = 44   # 36 read (pos 8 + nrm 8 + albedo 8 + emissive 8 + orm 4) + 8 written
 B_PER_PX_K1 = 32   # 24 read + 8 written
 # dram__bytes_read.sum + dram__bytes_write.sum of one shade_ggx_cl_kernel launch on this workload, from the committed
-# `ncu --set full` capture (profiles/r02_k3_cl_kernel_ncu.txt): 520.4 MB + 60.5 MB; the 216 MB above the
+# `ncu --set full` capture (profiles/r02_k3_cl_ncu.txt): 520.4 MB + 60.5 MB; the 216 MB above the
 # algorithmic 365 MB are the IBL footprint records / textures and write-allocate traffic
 K3_DRAM_TRAFFIC_BYTES = 580.9e6
 K3_KERNEL = "shade_ggx_cl_kernel<4 lights, records + texture-unit ambient>"

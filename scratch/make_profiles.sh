@@ -21,4 +21,14 @@ ncu --set full --clock-control none -k regex:conv_kernel -c 14 -o $O/k7 $CMD2 > 
 CMD3="python bench.py --steps 3 --warmup 3 --no-cpu --mg-host none"
 $CMD3 > $O/plain_misc.log 2>&1 &&
 ncu --set full --clock-control none -k regex:'cluster_lights_kernel|shade_ggx_kernel|equirect_to_cube_kernel|cube_mip_kernel|brdf_lut_kernel' -c 24 -o $O/misc $CMD3 > $O/ncu_misc.log 2>&1; echo "ncu misc exit $?"
+# the reports are too large to travel (64 MiB limit on gpurun_out/): export what profiles_collect.sh reads, keep only the K3 reports
+for rep in k3_cl k3_cl_gather k7 misc; do
+  [ -f $O/$rep.ncu-rep ] || continue
+  ncu -i $O/$rep.ncu-rep --page raw --csv > $O/$rep.raw.csv 2>/dev/null
+done
+for rep in k3_cl k3_cl_gather; do
+  [ -f $O/$rep.ncu-rep ] && ncu -i $O/$rep.ncu-rep --page source --csv --print-source sass > $O/$rep.src.csv 2>/dev/null
+done
+rm -f $O/k7.ncu-rep $O/misc.ncu-rep
+rm -f gpurun_out/*.ncu-rep
 ls -la $O

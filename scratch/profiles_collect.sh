@@ -7,14 +7,10 @@ tail -1 $O/bench_n1.json > $P/r02_bench_n1.json
 tail -1 $O/bench_reference.json > $P/r02_bench_reference.json
 cp $O/launches.csv $P/r02_launches_bench.csv
 python scratch/launch_summary.py $O/launches.csv > $P/r02_launches_summary.txt
-for rep in k3_cl k3_cl_gather k7 misc; do
-  [ -f $O/$rep.ncu-rep ] || continue
-  ncu -i $O/$rep.ncu-rep --page raw --csv > /tmp/$rep.raw.csv 2>/dev/null
-  if [ $rep = k3_cl ] || [ $rep = k3_cl_gather ]; then
-    ncu -i $O/$rep.ncu-rep --page source --csv --print-source sass > /tmp/$rep.src.csv 2>/dev/null
-    python scratch/summarize_ncu.py /tmp/$rep.raw.csv /tmp/$rep.src.csv > $P/r02_${rep}_ncu.txt
-  else
-    python scratch/summarize_ncu.py /tmp/$rep.raw.csv "" 30 > $P/r02_${rep}_ncu.txt
-  fi
+for rep in k3_cl k3_cl_gather; do
+  [ -f $O/$rep.raw.csv ] && python scratch/summarize_ncu.py $O/$rep.raw.csv $O/$rep.src.csv > $P/r02_${rep}_ncu.txt
+done
+for rep in k7 misc; do
+  [ -f $O/$rep.raw.csv ] && python scratch/summarize_ncu.py $O/$rep.raw.csv "" 30 > $P/r02_${rep}_ncu.txt
 done
 ls -la $P | grep r02
