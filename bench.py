@@ -245,6 +245,8 @@ class Scene:
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
+        if os.environ.get("PBRCU_BENCH_GATHER"):  # profiling runs of the opt-in gather mode (scratch/make_profiles.sh)
+            s.flags = pbr.IBL_GATHER
         lib.ibl_accel_build(ctx, C.byref(s), C.byref(self.accel), self.stream())
         b.record()
         torch.cuda.synchronize()

@@ -22,7 +22,7 @@ LIB_PATH = HERE / "lib" / "libpbrcu.so"
 HEADER = ROOT / "include" / "pbrcu.h"
 
 PBRCU_TILE = 16
-IBL_EXACT, IBL_TEXTURE_UNIT = 1, 2  # pbrcu_ibl.flags
+IBL_EXACT, IBL_TEXTURE_UNIT, IBL_GATHER = 1, 2, 4  # pbrcu_ibl.flags
 
 
 class PbrcuError(RuntimeError):

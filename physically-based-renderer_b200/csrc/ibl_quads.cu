@@ -187,6 +187,10 @@ extern "C" int pbrcu_ibl_accel_build(pbrcu_ctx* ctx, const pbrcu_ibl* ibl, pbrcu
     }
     a->bytes += n_lut * 8;
   }
+  if (!(ibl->flags & PBRCU_IBL_GATHER)) {  // the atlases serve the opt-in gather mode only
+    *out = a;
+    return PBRCU_OK;
+  }
   if ((rc = gather_tex_build(ctx, &a->g_pref, ibl->prefiltered, ibl->pref_res, ibl->pref_mips, 6, false, st)) ||
       (rc = gather_tex_build(ctx, &a->g_irr, ibl->irradiance, ibl->irr_res, 1, 6, false, st)) ||
       (rc = gather_tex_build(ctx, &a->g_lut, ibl->lut, ibl->lut_res, 1, 1, true, st))) {

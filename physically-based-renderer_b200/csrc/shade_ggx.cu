@@ -626,14 +626,17 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   // ---- one light list the HOST holds (the headline frame, the batched views, the facade): lights in the kernel's
   // parameter block, IBL by texture gathers (shade_ggx_cl.cu) ----
   const bool host_lights = n_lights == 0 || is_host_pointer(lights_dev);
-  // PBRCU_K3_CL: 0 = never (upload the list, shade_ggx_one_kernel), 1 = IBL taps by tld4 gathers (measured slower: 218 vs 169 us
-  // on the bench frame), 2 or unset = footprint records (158.6 us) -- profiles/r02_k3_variants_*.txt
+  // PBRCU_K3_CL=0 (test switch): never -- upload the list and run shade_ggx_one_kernel.  IBL taps: footprint records (158.6 us on the
+  // bench frame), or tld4 gathers where the caller asked for them and the accel carries the atlases (PBRCU_IBL_GATHER: 218 us) --
+  // profiles/r02_k3_variants_*.txt, r02_k3_cl_ncu.txt, r02_k3_cl_gather_ncu.txt
   const char* cl_env = getenv("PBRCU_K3_CL");
-  const int cl_mode = cl_env ? atoi(cl_env) : 2;
-  const bool use_cl = cl_mode != 0;
-  if (use_cl && !tex && p.tile_counts == nullptr && n_lights <= uint32_t(kClMaxLights) && host_lights && (!p.has_ibl || (p.q_pref && ibl->accel->g_pref.tex))) {
+  const bool use_cl = !(cl_env && atoi(cl_env) == 0);
+  const bool gathers = p.has_ibl && ibl->accel && ibl->accel->g_pref.tex && (ibl->flags & PBRCU_IBL_GATHER);
+  // (single frames only: over a block of views -- one long launch -- shade_ggx_one_kernel measured faster, 12.1 vs 12.8 ms for 256 x 1080p,
+  // scratch/batched_ab.py, so a batched call uploads its host list like any other)
+  if (use_cl && n_views == 1 && !tex && p.tile_counts == nullptr && n_lights <= uint32_t(kClMaxLights) && host_lights && (!p.has_ibl || p.q_pref)) {
     int amb = !p.has_ibl ? 0 : (p.t_irr && p.t_lut && !exact) ? 1 : 2;
-    if (amb != 0 && cl_mode != 1) amb += 2;  // footprint records instead of gathers
+    if (amb != 0 && !gathers) amb += 2;  // footprint records instead of gathers
     return launch_shade_cl(p, lights_dev, n_lights, ibl ? ibl->accel : nullptr, amb, n_views > 1 ? LIST_ONE_BATCHED : LIST_ONE, ctx->sm_count, st);
   }
   if (n_lights != 0 && host_lights) {  // the kernels below read the list from device memory

@@ -325,18 +325,25 @@ static void fill_level(float4& o, const AtlasLevel& a) { o = make_float4(float(a
 
 template <int NL, int AMB, bool BRANCH, int CTAS>
 static void launch_cl_modes(const ShadeClParams& q, int lists, bool peers, uint32_t grid, cudaStream_t st) {
-  if (lists == LIST_ONE_BATCHED) shade_ggx_cl_kernel<NL, AMB, true, false, BRANCH, CTAS><<<grid, kShadeThreads, 0, st>>>(q);
-  else if (peers) shade_ggx_cl_kernel<NL, AMB, false, true, BRANCH, CTAS><<<grid, kShadeThreads, 0, st>>>(q);
+  (void)lists;  // (single frames only: shade_common keeps batched calls on shade_ggx_one_kernel)
+  if (peers) shade_ggx_cl_kernel<NL, AMB, false, true, BRANCH, CTAS><<<grid, kShadeThreads, 0, st>>>(q);
   else shade_ggx_cl_kernel<NL, AMB, false, false, BRANCH, CTAS><<<grid, kShadeThreads, 0, st>>>(q);
 }
 
+template <int NL, bool BRANCH>
+static void launch_cl_amb2(const ShadeClParams& q, int amb, int lists, bool peers, uint32_t grid, cudaStream_t st) {
+  if (amb == 0) launch_cl_modes<NL, 0, BRANCH, kClCtasPerSm>(q, lists, peers, grid, st);
+  else if (amb == 1) launch_cl_modes<NL, 1, BRANCH, kClCtasPerSm>(q, lists, peers, grid, st);
+  else if (amb == 2) launch_cl_modes<NL, 2, BRANCH, kClCtasPerSm>(q, lists, peers, grid, st);
+  else if (amb == 3) launch_cl_modes<NL, 3, BRANCH, kClCtasPerSm>(q, lists, peers, grid, st);
+  else launch_cl_modes<NL, 4, BRANCH, kClCtasPerSm>(q, lists, peers, grid, st);
+}
+// BRANCH: skip the back half of a light that reaches no lane of the warp.  Off for single frames (straight-line code for the four
+// lights: 158.6 vs 169.0 us on the 4K frame); see launch_shade_cl for the batched launches.
 template <int NL>
-static void launch_cl_amb(const ShadeClParams& q, int amb, int lists, bool peers, uint32_t grid, cudaStream_t st) {
-  if (amb == 0) launch_cl_modes<NL, 0, false, kClCtasPerSm>(q, lists, peers, grid, st);
-  else if (amb == 1) launch_cl_modes<NL, 1, false, kClCtasPerSm>(q, lists, peers, grid, st);
-  else if (amb == 2) launch_cl_modes<NL, 2, false, kClCtasPerSm>(q, lists, peers, grid, st);
-  else if (amb == 3) launch_cl_modes<NL, 3, false, kClCtasPerSm>(q, lists, peers, grid, st);
-  else launch_cl_modes<NL, 4, false, kClCtasPerSm>(q, lists, peers, grid, st);
+static void launch_cl_amb(const ShadeClParams& q, int amb, int lists, bool peers, uint32_t grid, cudaStream_t st, bool branch) {
+  (void)branch;
+  launch_cl_amb2<NL, false>(q, amb, lists, peers, grid, st);
 }
 
 // p: the parameters shade_common filled (rect, planes, textures, views, replicas); lights: HOST array.
@@ -390,9 +397,10 @@ int launch_shade_cl(const ShadeParams& p, const pbrcu_light* lights_host, uint32
       return launch_check("shade_ggx_cl_kernel (experiment)");
     }
   }
-  if (n_eval == 2) launch_cl_amb<2>(q, amb, lists, peers, grid, st);
-  else if (n_eval == 4) launch_cl_amb<4>(q, amb, lists, peers, grid, st);
-  else launch_cl_amb<-1>(q, amb, lists, peers, grid, st);
+  const bool branch = false;
+  if (n_eval == 2) launch_cl_amb<2>(q, amb, lists, peers, grid, st, branch);
+  else if (n_eval == 4) launch_cl_amb<4>(q, amb, lists, peers, grid, st, branch);
+  else launch_cl_amb<-1>(q, amb, lists, peers, grid, st, branch);
   return launch_check("shade_ggx_cl_kernel");
 }
 

@@ -1,4 +1,6 @@
-"""A/B of the K3 variants on the bench's 4K frame (one GPU):  python scratch/k3_cl_exp.py
+"""(Ran on the build of commit 3f889c4+: PBRCU_K3_CL then selected 1 = gathers / 2 = records; today the gather mode is pbrcu_ibl.flags &
+PBRCU_IBL_GATHER.  Results: profiles/r02_k3_variants_a.txt, _b.txt.)
+A/B of the K3 variants on the bench's 4K frame (one GPU):  python scratch/k3_cl_exp.py
 old = lights in device memory (shade_ggx_one_kernel: footprint records), new = lights on the host (shade_ggx_cl_kernel: gathers),
 PBRCU_K3_EXP selects the experimental instantiations of shade_ggx_cl.cu's dispatch.  Prints time, and the differences
 to the old kernel's frame of the same filtering mode."""

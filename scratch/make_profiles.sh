@@ -14,8 +14,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-fi
 CMD2="python bench.py --steps 3 --warmup 3 --no-cpu --no-extra"
 $CMD2 > $O/plain_k3.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:shade_ggx_cl_kernel -s 3 -c 2 -o $O/k3_cl $CMD2 > $O/ncu_k3.log 2>&1; echo "ncu k3 exit $?"
-PBRCU_K3_CL=1 $CMD2 > $O/plain_k3_gather.log 2>&1 &&
-PBRCU_K3_CL=1 ncu --set full --clock-control none --import-source on -k regex:shade_ggx_cl_kernel -s 3 -c 1 -o $O/k3_cl_gather $CMD2 > $O/ncu_k3g.log 2>&1; echo "ncu k3 gather exit $?"
+PBRCU_BENCH_GATHER=1 $CMD2 > $O/plain_k3_gather.log 2>&1 &&
+PBRCU_BENCH_GATHER=1 ncu --set full --clock-control none --import-source on -k regex:shade_ggx_cl_kernel -s 3 -c 1 -o $O/k3_cl_gather $CMD2 > $O/ncu_k3g.log 2>&1; echo "ncu k3 gather exit $?"
 $CMD2 > $O/plain_k7.log 2>&1 &&
 ncu --set full --clock-control none -k regex:conv_kernel -c 14 -o $O/k7 $CMD2 > $O/ncu_k7.log 2>&1; echo "ncu k7 exit $?"
 CMD3="python bench.py --steps 3 --warmup 3 --no-cpu --mg-host none"

@@ -136,15 +136,18 @@ def build_ibl(dev, oracle, res=32, nmips=6, ns=256, ires=16, lres=32):
     return host, (irr_d, pref_d, lut_d)
 
 
-def make_ibl_struct(pbr, host, bufs, dev=None, accel=False):
-    """accel=True also builds the footprint-record copies (pbrcu_ibl_accel_build) the fast K3 path samples."""
+def make_ibl_struct(pbr, host, bufs, dev=None, accel=False, gather=False):
+    """accel=True also builds the footprint-record copies (pbrcu_ibl_accel_build) the fast K3 path samples; gather=True the
+    texture-gather atlases as well (PBRCU_IBL_GATHER; the flag is cleared again: a test sets it per call)."""
     s = pbr.Ibl()
     s.irradiance, s.irr_res = bufs[0].ptr, host["irr"].shape[1]
     s.prefiltered, s.pref_res, s.pref_mips = bufs[1].ptr, host["pref_res"], host["pref_mips"]
     s.lut, s.lut_res = bufs[2].ptr, host["lut"].shape[0]
     if accel:
         h = C.c_void_p()
+        s.flags = pbr.IBL_GATHER if gather else 0
         dev.lib.ibl_accel_build(dev.ctx, C.byref(s), C.byref(h), None)
+        s.flags = 0
         s.accel = h
     return s
 
@@ -169,9 +172,9 @@ def test_shade_matches_oracle(pbr, dev, oracle, w, h, nl, use_ibl):
     if use_ibl:
         ibl2 = make_ibl_struct(pbr, host, bufs, dev, accel=True)
         n_cube = oracle.chain_texels(host["pref_res"], host["pref_mips"]) + host["irr"].size // 4
-        # at least: 32-byte footprint records of the three maps + the flagged RGBA16F texture copies of the two cubes + the LUT
-        # as a float2 texture (+ the gather atlases: every face of every level with a one-texel gutter)
-        assert dev.lib.ibl_accel_bytes(ibl2.accel) >= 32 * (n_cube + host["lut"].size // 2) + 8 * n_cube + 8 * (host["lut"].size // 2)
+        # 32-byte footprint records of the three maps + the flagged RGBA16F texture copies of the two cubes + the LUT as a float2
+        # texture (no gather atlases: they are built on request only, PBRCU_IBL_GATHER)
+        assert dev.lib.ibl_accel_bytes(ibl2.accel) == 32 * (n_cube + host["lut"].size // 2) + 8 * n_cube + 8 * (host["lut"].size // 2)
         out2 = dev.alloc(w * h * 8)
         # opt-in: texture-unit fetches (8-bit weights), fp32-weight records where the contrast flag is set
         dev.lib.shade_set_texture_unit(dev.ctx, 1)
@@ -643,7 +646,7 @@ def test_shade_frame_host_equals_the_device_path(pbr, dev, oracle, w, h, bands):
 @pytest.mark.parametrize("nl", [0, 1, 3, 4, 7, 16])
 def test_shade_host_light_list_kernels(pbr, dev, oracle, nl, monkeypatch):
     """Lights passed as a HOST array (what the facade, the bench and pbrcu_shade_frame_host do) travel in the kernel's parameter
-    block (shade_ggx_cl.cu).  Default: IBL taps from the footprint records; PBRCU_K3_CL=1: tld4 gathers; PBRCU_K3_CL=0: the list
+    block (shade_ggx_cl.cu).  Default: IBL taps from the footprint records; pbrcu_ibl.flags & PBRCU_IBL_GATHER: tld4 gathers; PBRCU_K3_CL=0: the list
     is uploaded and the device-list kernel runs, bit for bit.  Every mode against the oracle in both filter modes; the exact
     modes against the device-list kernel within one fp16 ulp (the lights are summed in another contraction order)."""
     host, bufs = build_ibl(dev, oracle)
@@ -652,11 +655,12 @@ def test_shade_host_light_list_kernels(pbr, dev, oracle, nl, monkeypatch):
     gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
     lights = synth_lights(max(nl, 1), seed=30 + nl)[:nl]
     ld = dev.upload(lights) if nl else None
-    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True, gather=True)
     cam = (0.5, -1.0, 12.0)
     out = dev.alloc(w * h * 8)
 
-    def run(ptr, use_ibl=True):
+    def run(ptr, use_ibl=True, gather=False):
+        ibl.flags = pbr.IBL_GATHER if gather else 0
         dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), ptr, nl, None, C.byref(ibl) if use_ibl else None, pbr.WHOLE, out.ptr, w * 8, None)
         dev.sync()
         return out.download((h, w, 4), np.uint16)
@@ -670,12 +674,9 @@ def test_shade_host_light_list_kernels(pbr, dev, oracle, nl, monkeypatch):
         from_dev = run(ld.ptr if ld else None)
         monkeypatch.setenv("PBRCU_K3_CL", "0")
         assert np.array_equal(run(host_ptr), from_dev), "uploaded host light list != device light list"
-        for mode in (None, "1"):
-            if mode is None:
-                monkeypatch.delenv("PBRCU_K3_CL", raising=False)
-            else:
-                monkeypatch.setenv("PBRCU_K3_CL", mode)
-            got = run(host_ptr)
+        monkeypatch.delenv("PBRCU_K3_CL", raising=False)
+        for mode in ("records", "gathers"):
+            got = run(host_ptr, gather=mode == "gathers")
             assert_hdr_parity(got, want, peak=peak, rel_tol=REL, what=f"parameter-block kernel nl={nl} exact={exact} mode={mode}")
             assert (got[g["bg"]] == 0).all()
             if exact:
