@@ -283,6 +283,15 @@ class Scene:
         self.dev.lib.lighting_blinnphong(self.dev.ctx, C.byref(g), self.pbr.f3(*CAM), self.pbr.WHOLE,
                                          self.outs[i % len(self.outs)].data_ptr(), W4K * 8, self.stream())
 
+    def shade_then_tonemap(self, i):
+        self.shade(i)
+        self.dev.lib.tonemap_aces_gamma(self.dev.ctx, self.outs[i % len(self.outs)].data_ptr(), W4K * 8, W4K, H4K, self.pbr.WHOLE, self.ldr.data_ptr(), W4K * 4, self.stream())
+
+    def shade_ldr(self, i):
+        g, _ = self.gbufs[i % len(self.gbufs)]
+        self.dev.lib.shade_ggx_ibl_ldr(self.dev.ctx, C.byref(g), self.pbr.f3(*CAM), self.lights_host.ctypes.data, N_LIGHTS, None, C.byref(self.ibl), self.pbr.WHOLE,
+                                       self.ldr.data_ptr(), W4K * 4, None, 0, self.stream())
+
     def fused(self, i):
         g, _ = self.gbufs[i % len(self.gbufs)]
         self.dev.lib.lighting_tonemap_fused(self.dev.ctx, C.byref(g), self.pbr.f3(*CAM), self.pbr.WHOLE, None, 0,
@@ -772,6 +781,31 @@ def mg_host_leg(scene, torch, n_dev):
         except pbr.PbrcuError as e:
             out[key] = None
             out[key + "_error"] = str(e)[:160]
+    # display-ready frames: the tonemap fused into K3's stores, 4-byte texels on the links (pbrcu_mg_shade_frame_ldr)
+    try:
+        ldr_frames = [torch.zeros(W8 * H8 * 4, dtype=torch.uint8, device=f.device) for f in frames]
+        ldr_ptrs = (C.c_void_p * n_dev)(*[f.data_ptr() for f in ldr_frames])
+        lib.mg_set_device(mg, 0)
+        whole_ldr = torch.empty(W8 * H8 * 4, dtype=torch.uint8, device=frames[0].device)
+        lib.tonemap_aces_gamma(ctx0, whole.data_ptr(), W8 * 8, W8, H8, pbr.WHOLE, whole_ldr.data_ptr(), W8 * 4, None)
+        lib.stream_synchronize(None)
+        for _ in range(3):
+            lib.mg_shade_frame_ldr(mg, gbs, pbr.f3(*CAM), lights.ctypes.data, NL, tiles, ibls, bands, ldr_ptrs, W8 * 4, 1)
+        lib.mg_synchronize(mg)
+        lib.mg_set_device(mg, 0)
+        lib.timer_start(timer, lib.mg_stream(mg, 0))
+        for _ in range(10):
+            lib.mg_shade_frame_ldr(mg, gbs, pbr.f3(*CAM), lights.ctypes.data, NL, tiles, ibls, bands, ldr_ptrs, W8 * 4, 1)
+        lib.mg_set_device(mg, 0)
+        lib.timer_stop(timer, lib.mg_stream(mg, 0))
+        ms = C.c_float()
+        lib.timer_elapsed_ms(timer, C.byref(ms))
+        lib.mg_synchronize(mg)
+        out["ms_per_frame_fused_gather_p2p_ldr"] = round(ms.value / 10, 4)
+        out["fused_gather_p2p_ldr_equals_tonemap_of_unsharded"] = all(bool(torch.equal(f.to(whole_ldr.device), whole_ldr)) for f in ldr_frames)
+        del ldr_frames, whole_ldr
+    except pbr.PbrcuError as e:
+        out["ms_per_frame_fused_gather_p2p_ldr_error"] = str(e)[:160]
     lib.timer_destroy(timer)
     for i in range(n_dev):
         lib.mg_set_device(mg, i)
@@ -929,6 +963,9 @@ def main_ours(args):
     # Tier A (reference-pinned) kernels, same protocol
     ms_k1 = timed(torch, dist, scene.lighting, args.steps, args.warmup)
     ms_fused = timed(torch, dist, scene.fused, args.steps, args.warmup)
+    # Tier B display frame (GGX + IBL -> RGBA8): K3 then K2, and K3 with the tonemap fused into its stores
+    ms_b_two = timed(torch, dist, scene.shade_then_tonemap, args.steps, args.warmup)
+    ms_b_ldr = timed(torch, dist, scene.shade_ldr, args.steps, args.warmup)
 
     host, out = host_frame(scene, torch)
     e2e_steps = max(3, min(args.steps, 20))
@@ -1010,6 +1047,10 @@ def main_ours(args):
                        "fused_ldr_roofline_frac": round(28 * px_step * args.steps / (ms_fused * 1e-3) / 1e9 / peak, 4),
                        "frame_host_mpix_s": round(world * px_step * e2e_steps / (ms_a_e2e * 1e-3) / 1e6, 1),
                        "frame_host": "pbrcu_frame_host: three pinned host planes in (24 B/px), lighting + ACES tonemap, HDR and LDR frames out (12 B/px), 4 tapered row bands"},
+            "display_frame_ggx_ibl_4k": {"what": "GGX + 4 lights + IBL to a display-ready RGBA8 frame: pbrcu_shade_ggx_ibl + pbrcu_tonemap_aces_gamma (44 + 12 B/px) vs "
+                                                 "pbrcu_shade_ggx_ibl_ldr (tonemap fused into K3's stores, 40 B/px), bit-identical",
+                                         "ms_two_passes": round(ms_b_two / args.steps, 5), "ms_fused": round(ms_b_ldr / args.steps, 5),
+                                         "mpix_s_fused": round(world * px_step * args.steps / (ms_b_ldr * 1e-3) / 1e6, 1)},
             "other_configs": extra,
             "strong_scaling": strong_scaling_block(extra, scene, world),
             "mg_host_c": mg_host,

@@ -74,6 +74,20 @@ public:
                 "pbr::DeviceGroup::shadeFrame");
   }
 
+  // The same frame display-ready: RGBA8 frames, the ACES + gamma tonemap fused into the shading kernel's stores (half the gather's bytes).
+  auto shadeFrameLdr(std::span<pbrcu_gbuffer const> gBuffers, glm::vec3 cameraPosition, std::span<PointLight const> lights,
+                     std::span<pbrcu_light_tiles const> tiles, std::span<pbrcu_ibl const> ibls, std::span<RowBand const> bands,
+                     std::span<void* const> ldrFrames, std::size_t pitch, Gather gather) -> void {
+    if (gBuffers.size() != size() || bands.size() != size() || ldrFrames.size() != size() || (!tiles.empty() && tiles.size() != size()) ||
+        (!ibls.empty() && ibls.size() != size()))
+      throw std::runtime_error("pbr::DeviceGroup::shadeFrameLdr: one entry per member expected");
+    float const cam[3] = {cameraPosition.x, cameraPosition.y, cameraPosition.z};
+    core::check(pbrcu_mg_shade_frame_ldr(_mg, gBuffers.data(), cam, reinterpret_cast<pbrcu_light const*>(lights.data()), static_cast<std::uint32_t>(lights.size()),
+                                         tiles.empty() ? nullptr : tiles.data(), ibls.empty() ? nullptr : ibls.data(), &bands.data()->y0, ldrFrames.data(), pitch,
+                                         static_cast<int>(gather)),
+                "pbr::DeviceGroup::shadeFrameLdr");
+  }
+
   // Batched views: member i shades viewCounts[i] views laid out viewStride8 / viewStride4 bytes apart from firstViews[i]'s planes.
   auto shadeViews(std::span<pbrcu_gbuffer const> firstViews, std::size_t viewStride8, std::size_t viewStride4, std::span<std::uint32_t const> viewCounts,
                   std::span<float const* const> cameraPositions, std::span<PointLight const> lights, std::span<pbrcu_ibl const> ibls,

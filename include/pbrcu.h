@@ -217,6 +217,14 @@ int pbrcu_shade_ggx_ibl_multicast(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const 
                                   const pbrcu_light* lights_dev, uint32_t n_lights,
                                   const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
                                   void* out_multicast, size_t out_pitch, pbrcu_stream s);
+/* K3 with the reference's tonemap pass fused into its stores (K2: TonemapperSystem::run, TonemapperSystem.cpp:97-134 running
+ * assets/shaders/tonemappers/aces+gamma.glsl:30-40): the display-ready RGBA8 frame in ONE pass, bit-identical to pbrcu_shade_ggx_ibl followed by
+ * pbrcu_tonemap_aces_gamma (the tonemapper sees the fp16-rounded lighting value either way), 40 B/px of traffic instead of 44 + 12.
+ * out_pitch counts bytes of 4-byte texels.  replica_outs / n_replicas as in pbrcu_shade_ggx_ibl_replicated (NULL, 0 = none): a row band
+ * delivered to every peer's LDR frame at half the bytes of the HDR gather. */
+int pbrcu_shade_ggx_ibl_ldr(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights,
+                            uint32_t n_lights, const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect,
+                            void* out_rgba8, size_t out_pitch, void* const* replica_outs, uint32_t n_replicas, pbrcu_stream s);
 /* One GGX+IBL frame through HOST buffers (the end-to-end path of the headline metric): the frame is
  * cut into n_bands row bands (0 = 4; the last three shrink by halves so little is left to do after
  * the last byte has arrived) pipelined over two internal streams, so the H2D copy of band i+1 overlaps the
@@ -405,6 +413,10 @@ int pbrcu_mg_row_bands(uint32_t height, int n, const float* tile_row_costs, uint
 int pbrcu_mg_shade_frame(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host,
                          uint32_t n_lights, const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, const uint32_t* bands_y0y1,
                          void* const* frames, size_t pitch, int gather);
+/* pbrcu_mg_shade_frame with RGBA8 frames: the tonemap fused into K3's stores (pbrcu_shade_ggx_ibl_ldr); pitch in bytes of 4-byte texels */
+int pbrcu_mg_shade_frame_ldr(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host,
+                             uint32_t n_lights, const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, const uint32_t* bands_y0y1,
+                             void* const* frames, size_t pitch, int gather);
 /* Batched views: member i shades its block of n_views[i] views (pbrcu_shade_ggx_ibl_batched per member); no exchange. */
 int pbrcu_mg_shade_views(pbrcu_mg* mg, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
                          const uint32_t* n_views, const float* const* cam_pos_xyz, const pbrcu_light* lights_host,

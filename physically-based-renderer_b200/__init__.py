@@ -123,6 +123,7 @@ _SIGNATURES = {
     "pbrcu_shade_ggx_ibl": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, _vp]),
     "pbrcu_shade_ggx_ibl_multicast": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, _vp]),
     "pbrcu_shade_ggx_ibl_replicated": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, C.POINTER(_vp), _u32, _vp]),
+    "pbrcu_shade_ggx_ibl_ldr": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, Rect, _vp, _sz, C.POINTER(_vp), _u32, _vp]),
     "pbrcu_shade_ggx_ibl_batched": (_i, [_vp, _PG, _sz, _sz, _u32, _f3, _vp, _u32, _PI, _vp, _sz, _sz, _vp]),
     "pbrcu_shade_ggx_ibl_batched_static": (_i, [_vp, _PG, _sz, _sz, _u32, _f3, _vp, _u32, _PI, _vp, _sz, _sz, _vp]),
     "pbrcu_shade_frame_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32, _f3, _vp, _u32, _PI, _vp, _u32, _vp]),
@@ -158,6 +159,7 @@ _SIGNATURES = {
     "pbrcu_mg_synchronize": (_i, [_vp]),
     "pbrcu_mg_row_bands": (_i, [_u32, _i, _f3, C.POINTER(_u32)]),
     "pbrcu_mg_shade_frame": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, C.POINTER(_u32), C.POINTER(_vp), _sz, _i]),
+    "pbrcu_mg_shade_frame_ldr": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, C.POINTER(_u32), C.POINTER(_vp), _sz, _i]),
     "pbrcu_mg_shade_views": (_i, [_vp, _PG, _sz, _sz, C.POINTER(_u32), C.POINTER(_f3), _vp, _u32, _PI, C.POINTER(_vp), _sz, _sz]),
     "pbrcu_mg_prefilter": (_i, [_vp, C.POINTER(_vp), _u32, _u32, C.POINTER(_vp), _i]),
     "pbrcu_synth_gbuffer": (_i, [_vp, _PG, _i, _u64, _f3, _f3, _vp]),

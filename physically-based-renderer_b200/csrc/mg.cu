@@ -235,9 +235,9 @@ static int ensure_comms(pbrcu_mg* mg) {
 // row, all in member i's memory.  bands = 2 n rows from pbrcu_mg_row_bands.  lights: HOST array.
 // gather: PBRCU_MG_GATHER_NONE (member i's frame holds its band), _P2P (K3 stores every texel into every member's frame),
 // _NCCL (one grouped ncclBroadcast per band after the shading).  Returns after enqueueing; ends with pbrcu_mg_barrier.
-extern "C" int pbrcu_mg_shade_frame(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host, uint32_t n_lights,
-                                    const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, const uint32_t* bands_y0y1, void* const* frames, size_t pitch,
-                                    int gather) {
+static int mg_shade_frame_impl(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host, uint32_t n_lights,
+                               const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, const uint32_t* bands_y0y1, void* const* frames, size_t pitch,
+                               int gather, bool ldr) {
   PBRCU_REQUIRE(mg && g && cam_pos && bands_y0y1 && frames, "NULL argument");
   PBRCU_REQUIRE(n_lights == 0 || lights_host, "lights_host is NULL");
   PBRCU_REQUIRE(gather == PBRCU_MG_GATHER_NONE || gather == PBRCU_MG_GATHER_P2P || gather == PBRCU_MG_GATHER_NCCL, "unknown gather mode");
@@ -270,13 +270,17 @@ extern "C" int pbrcu_mg_shade_frame(pbrcu_mg* mg, const pbrcu_gbuffer* g, const 
       if (n_lights) PBRCU_CUDA(cudaMemcpyAsync(mg->lights[i], lights_host, size_t(n_lights) * sizeof(pbrcu_light), cudaMemcpyHostToDevice, mg->stream[i]));
       const pbrcu_light_tiles tb = band_of(tiles[i], y0, y1);
       if ((rc = pbrcu_cluster_lights(mg->ctx[i], &gb, mg->lights[i], n_lights, &tb, mg->stream[i]))) return rc;
-      rc = nrep ? pbrcu_shade_ggx_ibl_replicated(mg->ctx[i], &gb, cam_pos, mg->lights[i], n_lights, &tb, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch,
-                                                 reps, nrep, mg->stream[i])
-                : pbrcu_shade_ggx_ibl(mg->ctx[i], &gb, cam_pos, mg->lights[i], n_lights, &tb, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch, mg->stream[i]);
+      rc = ldr    ? pbrcu_shade_ggx_ibl_ldr(mg->ctx[i], &gb, cam_pos, mg->lights[i], n_lights, &tb, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch,
+                                            nrep ? reps : nullptr, nrep, mg->stream[i])
+           : nrep ? pbrcu_shade_ggx_ibl_replicated(mg->ctx[i], &gb, cam_pos, mg->lights[i], n_lights, &tb, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch,
+                                                   reps, nrep, mg->stream[i])
+                  : pbrcu_shade_ggx_ibl(mg->ctx[i], &gb, cam_pos, mg->lights[i], n_lights, &tb, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch, mg->stream[i]);
     } else {
-      rc = nrep ? pbrcu_shade_ggx_ibl_replicated(mg->ctx[i], &gb, cam_pos, lights_host, n_lights, nullptr, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch, reps,
-                                                 nrep, mg->stream[i])
-                : pbrcu_shade_ggx_ibl(mg->ctx[i], &gb, cam_pos, lights_host, n_lights, nullptr, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch, mg->stream[i]);
+      rc = ldr    ? pbrcu_shade_ggx_ibl_ldr(mg->ctx[i], &gb, cam_pos, lights_host, n_lights, nullptr, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch,
+                                            nrep ? reps : nullptr, nrep, mg->stream[i])
+           : nrep ? pbrcu_shade_ggx_ibl_replicated(mg->ctx[i], &gb, cam_pos, lights_host, n_lights, nullptr, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch, reps,
+                                                   nrep, mg->stream[i])
+                  : pbrcu_shade_ggx_ibl(mg->ctx[i], &gb, cam_pos, lights_host, n_lights, nullptr, ibl ? &ibl[i] : nullptr, pbrcu_rect{0, 0, 0, 0}, out, pitch, mg->stream[i]);
     }
     if (rc) return rc;
   }
@@ -295,6 +299,19 @@ extern "C" int pbrcu_mg_shade_frame(pbrcu_mg* mg, const pbrcu_gbuffer* g, const 
     if (r != 0 || r2 != 0) { set_error("NCCL gather failed: %s", mg->nccl.GetErrorString(r ? r : r2)); return PBRCU_ERR_CUDA; }
   }
   return mg_barrier(mg);
+}
+
+extern "C" int pbrcu_mg_shade_frame(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host, uint32_t n_lights,
+                                    const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, const uint32_t* bands_y0y1, void* const* frames, size_t pitch,
+                                    int gather) {
+  return mg_shade_frame_impl(mg, g, cam_pos, lights_host, n_lights, tiles, ibl, bands_y0y1, frames, pitch, gather, false);
+}
+// The same frame delivered display-ready: RGBA8 frames (pitch in bytes of 4-byte texels), the reference's ACES + gamma tonemap fused into K3's stores
+// (pbrcu_shade_ggx_ibl_ldr) -- half the bytes of the HDR gather on NVLink, no separate tonemap pass.
+extern "C" int pbrcu_mg_shade_frame_ldr(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_host, uint32_t n_lights,
+                                        const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, const uint32_t* bands_y0y1, void* const* frames, size_t pitch,
+                                        int gather) {
+  return mg_shade_frame_impl(mg, g, cam_pos, lights_host, n_lights, tiles, ibl, bands_y0y1, frames, pitch, gather, true);
 }
 
 // Batched multi-view over the group (BASELINE config 5): member i shades ITS block of views -- n_views[i] G-buffers of one shape laid

@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_kern
     const float dr = lo(dr2) + hi(dr2), dg = lo(dg2) + hi(dg2), db = lo(db2) + hi(db2);
     // every lane reaches the store at the end of the iteration together (`have`: it owns a texel of the rect; a cleared texel is
     // stored as 0), so the peer-store instantiations can pair the texels of neighbouring lanes into 16-byte stores
-    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
+    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * (PEERS ? p.out_texel : 8u) + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
     const bool have = inside;
     uint2 texel = make_uint2(0u, 0u);
     if (have && lit) {
@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(kShadeThreads, kShadeCtasPerSm) shade_ggx_one_
 
     const uint32_t x = ip.x, y = ip.y;
     if (!(x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1)) continue;
-    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
+    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * (PEERS ? p.out_texel : 8u) + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
     const TileStage& st = s_tile[stage];
     const uint2 tn = st.px[1][threadIdx.x];
     const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
@@ -552,7 +552,7 @@ extern "C" int pbrcu_shade_set_texture_unit(pbrcu_ctx* ctx, int on) {
 
 template <int IBL>
 static void launch_shade(const ShadeParams& p, int lists, uint32_t grid, cudaStream_t st) {
-  const bool peers = p.n_replicas != 0 || p.out_is_multicast;  // single view only (shade_common)
+  const bool peers = p.n_replicas != 0 || p.out_is_multicast || p.out_texel == 4;  // single view only (shade_common)
   if (lists == LIST_ONE_BATCHED) shade_ggx_kernel<IBL, LIST_ONE_BATCHED><<<grid, kShadeThreads, 0, st>>>(p);
   else if (lists == LIST_ONE && peers) shade_ggx_kernel<IBL, LIST_ONE, true><<<grid, kShadeThreads, 0, st>>>(p);
   else if (lists == LIST_ONE) shade_ggx_kernel<IBL, LIST_ONE><<<grid, kShadeThreads, 0, st>>>(p);
@@ -564,13 +564,16 @@ static void launch_shade(const ShadeParams& p, int lists, uint32_t grid, cudaStr
 static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights_dev, uint32_t n_lights,
                         const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba16f, size_t out_pitch,
                         uint32_t n_views, size_t view_stride8, size_t view_stride4, size_t out_view_stride, pbrcu_stream s,
-                        void* const* replicas = nullptr, uint32_t n_replicas = 0, bool multicast = false, const float* cams_table = nullptr) {
+                        void* const* replicas = nullptr, uint32_t n_replicas = 0, bool multicast = false, const float* cams_table = nullptr, bool ldr = false) {
   PBRCU_REQUIRE(ctx && g && cam_pos && out_rgba16f, "NULL argument");
   PBRCU_REQUIRE(n_replicas <= PBRCU_MAX_REPLICAS && (n_replicas == 0 || replicas), "too many replicas or replicas NULL");
-  for (uint32_t k = 0; k < n_replicas; ++k) PBRCU_REQUIRE(replicas[k] && reinterpret_cast<uintptr_t>(replicas[k]) % 8 == 0, "replica NULL or not 8-byte aligned");
+  for (uint32_t k = 0; k < n_replicas; ++k)
+    PBRCU_REQUIRE(replicas[k] && reinterpret_cast<uintptr_t>(replicas[k]) % (ldr ? 4 : 8) == 0, "replica NULL or not aligned to the texel size");
   PBRCU_REQUIRE(g->positions && g->normals && g->albedo && g->orm && g->emissive, "gbuffer plane is NULL (K3 needs the tier-1 planes)");
   PBRCU_REQUIRE(g->pitch8 >= size_t(g->width) * 8 && g->pitch8 % 8 == 0 && g->pitch4 >= size_t(g->width) * 4 && g->pitch4 % 4 == 0, "bad gbuffer pitch");
-  PBRCU_REQUIRE(out_pitch >= size_t(g->width) * 8 && out_pitch % 8 == 0, "out_pitch too small or not a multiple of 8");
+  const uint32_t texel = ldr ? 4u : 8u;
+  PBRCU_REQUIRE(out_pitch >= size_t(g->width) * texel && out_pitch % texel == 0, "out_pitch too small or not a multiple of the texel size");
+  PBRCU_REQUIRE(!ldr || (n_views == 1 && !multicast), "the LDR output is for single frames without multicast");
   PBRCU_REQUIRE(n_lights <= 65535 && (n_lights == 0 || lights_dev), "n_lights out of range or lights NULL");
   if (rect.w == 0 && rect.h == 0) rect = pbrcu_rect{0, 0, g->width, g->height};
   PBRCU_REQUIRE(uint64_t(rect.x0) + rect.w <= g->width && uint64_t(rect.y0) + rect.h <= g->height, "rect outside the image");
@@ -581,12 +584,13 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
   p.emi = static_cast<const uint8_t*>(g->emissive); p.out = static_cast<uint8_t*>(out_rgba16f);
   p.n_replicas = n_replicas;
   p.out_is_multicast = multicast ? 1 : 0;
+  p.out_texel = texel;
   for (uint32_t k = 0; k < n_replicas; ++k) p.replica[k] = static_cast<uint8_t*>(replicas[k]);
   {
     bool aligned = reinterpret_cast<uintptr_t>(out_rgba16f) % 16 == 0 && out_pitch % 16 == 0;
     for (uint32_t k = 0; k < n_replicas; ++k) aligned = aligned && reinterpret_cast<uintptr_t>(replicas[k]) % 16 == 0;
     const char* e = getenv("PBRCU_PAIR_STORES");  // (0: 8-byte stores only -- the A/B switch of bench.py's fused-gather legs)
-    p.pair_stores = aligned && !(e && atoi(e) == 0) ? 1 : 0;
+    p.pair_stores = aligned && !ldr && !(e && atoi(e) == 0) ? 1 : 0;
   }
   p.pitch8 = g->pitch8; p.pitch4 = g->pitch4; p.out_pitch = out_pitch;
   p.x0 = rect.x0; p.y0 = rect.y0; p.x1 = rect.x0 + rect.w; p.y1 = rect.y0 + rect.h;
@@ -660,7 +664,7 @@ static int shade_common(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_
     if (lists == LIST_ONE_BATCHED) {
       if (ambtex) shade_ggx_one_kernel<true, true><<<grid, kShadeThreads, 0, st>>>(p);
       else shade_ggx_one_kernel<true, false><<<grid, kShadeThreads, 0, st>>>(p);
-    } else if (p.n_replicas != 0 || p.out_is_multicast) {
+    } else if (p.n_replicas != 0 || p.out_is_multicast || p.out_texel == 4) {
       if (ambtex) shade_ggx_one_kernel<false, true, true><<<grid, kShadeThreads, 0, st>>>(p);
       else shade_ggx_one_kernel<false, false, true><<<grid, kShadeThreads, 0, st>>>(p);
     } else {
@@ -770,4 +774,14 @@ extern "C" int pbrcu_shade_ggx_ibl_batched_static(pbrcu_ctx* ctx, const pbrcu_gb
   PBRCU_CUDA(cudaMemcpyAsync(cams, cam_pos_xyz, size_t(n_views) * 3 * sizeof(float), cudaMemcpyHostToDevice, static_cast<cudaStream_t>(s)));
   return shade_common(ctx, g0, cam_pos_xyz, lights_dev, n_lights, nullptr, ibl, pbrcu_rect{0, 0, 0, 0}, out_rgba16f, out_pitch, n_views, view_stride8,
                       view_stride4, out_view_stride, s, nullptr, 0, false, cams);
+}
+
+// K3 with the reference's tonemap pass (K2: TonemapperSystem::run, src/pbr_engine/engine/pbr/TonemapperSystem.cpp:97-134, aces+gamma.glsl:30-40)
+// fused into its stores: the display-ready RGBA8 frame in one pass -- 40 B/px instead of 44 + 12 for K3 then K2 -- bit-identical to
+// pbrcu_shade_ggx_ibl followed by pbrcu_tonemap_aces_gamma (the tonemapper sees the fp16-rounded value either way).  replica_outs / n_replicas
+// as in pbrcu_shade_ggx_ibl_replicated (NULL, 0: none): a multi-GPU row band delivered to every peer at 4 bytes per texel.
+extern "C" int pbrcu_shade_ggx_ibl_ldr(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float cam_pos[3], const pbrcu_light* lights, uint32_t n_lights,
+                                       const pbrcu_light_tiles* tiles, const pbrcu_ibl* ibl, pbrcu_rect rect, void* out_rgba8, size_t out_pitch,
+                                       void* const* replica_outs, uint32_t n_replicas, pbrcu_stream s) {
+  return shade_common(ctx, g, cam_pos, lights, n_lights, tiles, ibl, rect, out_rgba8, out_pitch, 1, 0, 0, 0, s, replica_outs, n_replicas, false, nullptr, true);
 }

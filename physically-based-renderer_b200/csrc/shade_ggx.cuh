@@ -5,6 +5,7 @@
 
 #include "f32x2.cuh"
 #include "ibl_quads.cuh"
+#include "tier_a_math.cuh"
 
 namespace pbrcu {
 
@@ -49,6 +50,8 @@ struct ShadeParams {
   uint32_t n_replicas;
   uint8_t* replica[PBRCU_MAX_REPLICAS];
   int out_is_multicast;  // pbrcu_shade_ggx_ibl_multicast: `out` is a multimem address
+  uint32_t out_texel;    // bytes per output texel: 8 = RGBA16F HDR; 4 = RGBA8 LDR, the ACES + gamma tonemap (K2) fused into the store
+                         // (peer-store instantiations only: pbrcu_shade_ggx_ibl_ldr)
   int pair_stores;       // every frame address and the pitch are 16-byte aligned: neighbouring texels may leave as one 16-byte store
 };
 
@@ -58,6 +61,14 @@ template <bool PEERS>
 __device__ __forceinline__ void store_texel(const ShadeParams& p, size_t off, uint2 v) {
   if (!PEERS) {  // the single-GPU kernels carry none of the bookkeeping below
     stg_stream8(p.out + off, v);
+    return;
+  }
+  if (p.out_texel == 4) {
+    // K2 fused into the store: tonemap the fp16-ROUNDED texel, exactly what pbrcu_tonemap_aces_gamma would read back from the HDR frame
+    // (aces+gamma.glsl:30-40), so the LDR frame equals the two-pass result bit for bit; `off` was computed with 4-byte texels
+    const uint32_t ldr = tonemap_texel(unpack_rgba16f(v));
+    stg_stream4(p.out + off, ldr);
+    for (uint32_t k = 0; k < p.n_replicas; ++k) stg_stream4(p.replica[k] + off, ldr);
     return;
   }
   if (p.out_is_multicast) {

@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kShadeThreads, CTAS) shade_ggx_cl_kernel(const
 
     const uint32_t x = ip.x, y = ip.y;
     if (!(x >= p.x0 && x < p.x1 && y >= p.y0 && y < p.y1)) continue;
-    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * 8 + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
+    const size_t outo = size_t(y) * p.out_pitch + size_t(x) * (PEERS ? p.out_texel : 8u) + (BATCHED ? size_t(ip.view) * p.out_view_stride : 0);
     const TileStage& st = s_tile[stage];
     const uint2 tn = st.px[1][threadIdx.x];
     const float2 nxy = h2_to_f2(tn.x), nzw = h2_to_f2(tn.y);
@@ -372,7 +372,7 @@ int launch_shade_cl(const ShadeParams& p, const pbrcu_light* lights_host, uint32
       c = ClLight{0.f, 0.f, 0.f, 1e30f, 0.f, 0.f, 0.f, 0.f};  // null light: range 1e-15, its window is exactly 0 everywhere, so w = 0
     }
   }
-  const bool peers = p.n_replicas != 0 || p.out_is_multicast;
+  const bool peers = p.n_replicas != 0 || p.out_is_multicast || p.out_texel == 4;
   const uint64_t items = uint64_t(2) * p.ntiles * (lists == LIST_ONE_BATCHED ? p.n_views : 1);
   const uint32_t grid = uint32_t(std::min<uint64_t>(items, uint64_t(sm_count) * kClCtasPerSm));
   if (const char* e = getenv("PBRCU_K3_EXP")) {  // scratch/k3_cl_exp.py: A/B variants of the headline instantiation

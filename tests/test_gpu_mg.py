@@ -129,6 +129,10 @@ def test_mg_frame_equals_the_single_device_frame(pbr, dev, ibl_host, tiled):
         lib.shade_ggx_ibl(dev.ctx, C.byref(gb0), cam, lights.ctypes.data, nl, None, C.byref(ibl0), pbr.WHOLE, out0.ptr, w * 8, None)
         dev.sync()
     want = out0.download((h, w, 4), np.uint16)
+    ldr0 = dev.alloc(w * h * 4)
+    lib.tonemap_aces_gamma(dev.ctx, out0.ptr, w * 8, w, h, pbr.WHOLE, ldr0.ptr, w * 4, None)
+    dev.sync()
+    want_ldr = ldr0.download((h, w, 4), np.uint8)
     lib.ibl_accel_free(dev.ctx, ibl0.accel)
 
     for devices in groups(pbr):
@@ -167,6 +171,12 @@ def test_mg_frame_equals_the_single_device_frame(pbr, dev, ibl_host, tiled):
                     assert (got[:y0] == 0x5A5A).all() and (got[y1:] == 0x5A5A).all(), f"{devices} member {i}: wrote outside its band"
                 else:
                     assert np.array_equal(got, want), f"{devices} gather {gather} member {i}: {np.count_nonzero(got != want)} values differ from the single-device frame"
+        # the same frame delivered display-ready (tonemap fused into the stores, 4-byte texels on the links)
+        ldr_frames = [m.alloc(w * h * 4) for m in members]
+        lib.mg_shade_frame_ldr(mg, gbs, cam, lights.ctypes.data, nl, tiles, ibls, bands, (C.c_void_p * n)(*ldr_frames), w * 4, 1)
+        lib.mg_synchronize(mg)
+        for i, (m, f) in enumerate(zip(members, ldr_frames)):
+            assert np.array_equal(m.download(f, (h, w, 4), np.uint8), want_ldr), f"{devices} member {i}: LDR frame differs from tonemap(single-device frame)"
         for i, m in enumerate(members):
             m.on()
             if tiled:

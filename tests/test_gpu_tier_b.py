@@ -754,3 +754,51 @@ def test_per_call_filter_flags_equal_the_context_switches(pbr, dev, oracle):
         assert np.array_equal(run(ptr, use_tiles, 0), default), "flags must not stick"
     dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+
+
+@pytest.mark.parametrize("mode", ["device-list", "host-list", "tile-lists", "no-ibl"])
+def test_shade_ldr_equals_shade_then_tonemap(pbr, dev, oracle, mode):
+    """pbrcu_shade_ggx_ibl_ldr (the reference's tonemap pass, aces+gamma.glsl:30-40, fused into K3's stores) == pbrcu_shade_ggx_ibl followed by
+    pbrcu_tonemap_aces_gamma, bit for bit, on every K3 kernel; with two replicas and a rect that starts and ends inside tiles, texels outside
+    the rect untouched; and within 1 LSB of the oracle's tonemap of the oracle's frame."""
+    w, h, nl = 150, 70, 7
+    host, bufs = build_ibl(dev, oracle)
+    g = synth_gbuffer(w, h, seed=15, tier_b=True)
+    gb = dev.gbuffer(g["pos"], g["nrm"], g["alb"], orm=g["orm"], emissive=g["emi"])
+    lights = synth_lights(nl, seed=2)
+    ld = dev.upload(lights)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    tiles = pbr.LightTiles()
+    dev.lib.light_tiles_alloc(dev.ctx, w, h, 16, C.byref(tiles))
+    dev.lib.cluster_lights(dev.ctx, C.byref(gb), ld.ptr, nl, C.byref(tiles), None)
+    lptr = lights.ctypes.data if mode == "host-list" else ld.ptr
+    targ = C.byref(tiles) if mode == "tile-lists" else None
+    iarg = None if mode == "no-ibl" else C.byref(ibl)
+    cam = (0.5, -1.0, 12.0)
+    hdr, ldr2 = dev.alloc(w * h * 8), dev.alloc(w * h * 4)
+    dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(*cam), lptr, nl, targ, iarg, pbr.WHOLE, hdr.ptr, w * 8, None)
+    dev.lib.tonemap_aces_gamma(dev.ctx, hdr.ptr, w * 8, w, h, pbr.WHOLE, ldr2.ptr, w * 4, None)
+    dev.sync()
+    want = ldr2.download((h, w, 4), np.uint8)
+    got_whole = dev.alloc(w * h * 4)
+    dev.lib.shade_ggx_ibl_ldr(dev.ctx, C.byref(gb), pbr.f3(*cam), lptr, nl, targ, iarg, pbr.WHOLE, got_whole.ptr, w * 4, None, 0, None)
+    dev.sync()
+    got = got_whole.download((h, w, 4), np.uint8)
+    assert np.array_equal(got, want), f"{mode}: LDR frame differs from shade + tonemap in {np.count_nonzero(got != want)} values"
+    _, o16 = oracle.shade(g["pos"], g["nrm"], g["alb"], g["orm"], g["emi"], cam, lights, None if mode == "no-ibl" else host)
+    assert np.abs(got.astype(int) - oracle.tonemap(o16).astype(int)).max() <= 2  # 1 fp16 ulp of HDR + 1 LSB of rounding
+    # band with replicas
+    rect = (3, 17, 140, 37)
+    sentinel = np.full((h, w, 4), 0x7B, np.uint8)
+    own, reps = dev.upload(sentinel), [dev.upload(sentinel) for _ in range(2)]
+    ptrs = (C.c_void_p * 2)(*[r.ptr for r in reps])
+    dev.lib.shade_ggx_ibl_ldr(dev.ctx, C.byref(gb), pbr.f3(*cam), lptr, nl, targ, iarg, pbr.Rect(*rect), own.ptr, w * 4, ptrs, 2, None)
+    dev.sync()
+    expect = sentinel.copy()
+    expect[rect[1]:rect[1] + rect[3], rect[0]:rect[0] + rect[2]] = want[rect[1]:rect[1] + rect[3], rect[0]:rect[0] + rect[2]]
+    for what, buf in [("own frame", own)] + [(f"replica {k}", r) for k, r in enumerate(reps)]:
+        assert np.array_equal(buf.download((h, w, 4), np.uint8), expect), f"{mode}: {what}"
+    with pytest.raises(pbr.PbrcuError):  # a pitch smaller than a row of 4-byte texels
+        dev.lib.shade_ggx_ibl_ldr(dev.ctx, C.byref(gb), pbr.f3(*cam), lptr, nl, targ, iarg, pbr.WHOLE, own.ptr, w * 4 - 4, None, 0, None)
+    dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
