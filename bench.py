@@ -803,6 +803,7 @@ def mg_host_leg(scene, torch, n_dev):
         lib.mg_synchronize(mg)
         out["ms_per_frame_fused_gather_p2p_ldr"] = round(ms.value / 10, 4)
         out["fused_gather_p2p_ldr_equals_tonemap_of_unsharded"] = all(bool(torch.equal(f.to(whole_ldr.device), whole_ldr)) for f in ldr_frames)
+        out["fused_gather_p2p_ldr_differing_bytes"] = int(sum(int((f.to(whole_ldr.device) != whole_ldr).sum()) for f in ldr_frames))
         del ldr_frames, whole_ldr
     except pbr.PbrcuError as e:
         out["ms_per_frame_fused_gather_p2p_ldr_error"] = str(e)[:160]

@@ -70,10 +70,11 @@ __device__ __forceinline__ F4 unpack_rgba16f(uint2 t) {
   return F4{a.x, a.y, b.x, b.y};
 }
 
-// aces+gamma.glsl:20-24
+// aces+gamma.glsl:20-24.  Every multiply-add below is an EXPLICIT fma in the order tonemap_pair (the packed two-texel form further down) uses,
+// so a texel gets the same bits whichever form shades it -- the scalar tail of a row, the vector body, or K3's fused LDR store (shade_ggx.cuh).
 __device__ __forceinline__ float rrt_odt_fit(float c) {
-  float num = c * (c + 0.0245786f) - 0.000090537f;
-  float den = c * (0.983729f * c + 0.4329510f) + 0.238081f;
+  const float num = fmaf(c, c + 0.0245786f, -0.000090537f);
+  const float den = fmaf(c, fmaf(0.983729f, c, 0.4329510f), 0.238081f);
   return num * mufu_rcp(den);  // den >= 0.238 for c >= 0 and at most ~4e9 for fp16 inputs: no range fix-up needed
 }
 // Gamma.lib.glsl:4-6 with the pinned negative-base behaviour: pow(max(x,0), 1/2.2).
@@ -82,14 +83,14 @@ __device__ __forceinline__ float gamma22(float x) {
   return mufu_ex2(mufu_lg2(fmaxf(x, 0.0f)) * (1.0f / 2.2f));
 }
 // aces+gamma.glsl:30-40.  mat3x3(a,b,c,d,e,f,g,h,i) fills COLUMNS: (M v).x = a v.x + d v.y + g v.z.
-__device__ __forceinline__ uint32_t tonemap_texel(F4 hdr) {
-  float ax = 0.59719f * hdr.x + 0.07600f * hdr.y + 0.02840f * hdr.z;
-  float ay = 0.35458f * hdr.x + 0.90834f * hdr.y + 0.13383f * hdr.z;
-  float az = 0.04823f * hdr.x + 0.01566f * hdr.y + 0.83777f * hdr.z;
-  float fx = rrt_odt_fit(ax), fy = rrt_odt_fit(ay), fz = rrt_odt_fit(az);
-  float ox = 1.60475f * fx + -0.10208f * fy + -0.00327f * fz;
-  float oy = -0.53108f * fx + 1.10813f * fy + -0.07276f * fz;
-  float oz = -0.07367f * fx + -0.00605f * fy + 1.07602f * fz;
+__device__ __forceinline__ uint32_t tonemap_texel_scalar(F4 hdr) {
+  const float ax = fmaf(0.02840f, hdr.z, fmaf(0.07600f, hdr.y, 0.59719f * hdr.x));
+  const float ay = fmaf(0.13383f, hdr.z, fmaf(0.90834f, hdr.y, 0.35458f * hdr.x));
+  const float az = fmaf(0.83777f, hdr.z, fmaf(0.01566f, hdr.y, 0.04823f * hdr.x));
+  const float fx = rrt_odt_fit(ax), fy = rrt_odt_fit(ay), fz = rrt_odt_fit(az);
+  const float ox = fmaf(-0.00327f, fz, fmaf(-0.10208f, fy, 1.60475f * fx));
+  const float oy = fmaf(-0.07276f, fz, fmaf(1.10813f, fy, -0.53108f * fx));
+  const float oz = fmaf(1.07602f, fz, fmaf(-0.00605f, fy, -0.07367f * fx));
   return pack_unorm8x4(gamma22(ox), gamma22(oy), gamma22(oz), hdr.w);
 }
 
@@ -160,6 +161,14 @@ __device__ __forceinline__ uint2 tonemap_pair(const F4x2& hdr) {
     return __byte_perm(rg, ba, 0x5410);
   };
   return make_uint2(pack(lo(r), lo(g), lo(b), lo(a)), pack(hi(r), hi(g), hi(b), hi(a)));
+}
+
+// One texel, CANONICAL form: the packed code above on a duplicated texel.  The packed and the scalar arithmetic agree except on exact
+// rounding ties of the UNORM8 store (measured: 5 bytes of a full-HD frame, 1 LSB -- scratch/ldr_diag.py), so every path that tonemaps a
+// single texel -- the tail of a row, an image that is not 16-byte aligned, K3's fused LDR store (shade_ggx.cuh) -- goes through the packed
+// code too and a pixel's bits do not depend on which path shaded it.  (tonemap_texel_scalar is kept for reference and for the diagnosis.)
+__device__ __forceinline__ uint32_t tonemap_texel(F4 hdr) {
+  return tonemap_pair(F4x2{dup(hdr.x), dup(hdr.y), dup(hdr.z), dup(hdr.w)}).x;
 }
 
 }  // namespace pbrcu

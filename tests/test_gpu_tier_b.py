@@ -802,3 +802,31 @@ def test_shade_ldr_equals_shade_then_tonemap(pbr, dev, oracle, mode):
         dev.lib.shade_ggx_ibl_ldr(dev.ctx, C.byref(gb), pbr.f3(*cam), lptr, nl, targ, iarg, pbr.WHOLE, own.ptr, w * 4 - 4, None, 0, None)
     dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
     dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+
+
+def test_shade_ldr_full_hd_equals_two_passes(pbr, dev, oracle):
+    """The same identity on a full-HD device-generated frame (2 M texels: rare rounding cases that a small frame does not meet -- the fused
+    store tonemaps one texel at a time, pbrcu_tonemap_aces_gamma two at a time in packed arithmetic; both must give the same bits),
+    host list and tile lists."""
+    w, h, nl = 1920, 1080, 24
+    host, bufs = build_ibl(dev, oracle)
+    gb = pbr.GBuffer()
+    dev.lib.gbuffer_alloc(dev.ctx, w, h, 1, C.byref(gb))
+    dev.lib.synth_gbuffer(dev.ctx, C.byref(gb), 1, 0x5EED0099, pbr.f3(0.0, -1.0, -12.0), pbr.f3(0, 0, 0), None)
+    ibl = make_ibl_struct(pbr, host, bufs, dev, accel=True)
+    lights = synth_lights(nl, seed=4, ranged=True)
+    ld = dev.upload(lights)
+    tiles = pbr.LightTiles()
+    dev.lib.light_tiles_alloc(dev.ctx, w, h, nl, C.byref(tiles))
+    dev.lib.cluster_lights(dev.ctx, C.byref(gb), ld.ptr, nl, C.byref(tiles), None)
+    hdr, two, one = dev.alloc(gb.pitch8 * h), dev.alloc(w * h * 4), dev.alloc(w * h * 4)
+    for lptr, n, targ in ((lights.ctypes.data, 4, None), (ld.ptr, nl, C.byref(tiles))):
+        dev.lib.shade_ggx_ibl(dev.ctx, C.byref(gb), pbr.f3(0.0, -1.0, -12.0), lptr, n, targ, C.byref(ibl), pbr.WHOLE, hdr.ptr, gb.pitch8, None)
+        dev.lib.tonemap_aces_gamma(dev.ctx, hdr.ptr, gb.pitch8, w, h, pbr.WHOLE, two.ptr, w * 4, None)
+        dev.lib.shade_ggx_ibl_ldr(dev.ctx, C.byref(gb), pbr.f3(0.0, -1.0, -12.0), lptr, n, targ, C.byref(ibl), pbr.WHOLE, one.ptr, w * 4, None, 0, None)
+        dev.sync()
+        a, b = two.download((h, w, 4), np.uint8), one.download((h, w, 4), np.uint8)
+        assert a.any() and np.array_equal(a, b), f"{np.count_nonzero(a != b)} bytes differ (max {np.abs(a.astype(int) - b.astype(int)).max()})"
+    dev.lib.light_tiles_free(dev.ctx, C.byref(tiles))
+    dev.lib.ibl_accel_free(dev.ctx, ibl.accel)
+    dev.lib.gbuffer_free(dev.ctx, C.byref(gb))
