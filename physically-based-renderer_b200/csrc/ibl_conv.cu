@@ -235,8 +235,10 @@ __global__ void __launch_bounds__(256) contrast_flags_kernel(const uint2* __rest
     }
     if (mm_down != nullptr) {
       const int r0 = res * 2;
-      for (int cy = 2 * y - 1; cy <= 2 * y + 2; ++cy)
-        for (int cx = 2 * x - 1; cx <= 2 * x + 2; ++cx)
+      // the 3x3 windows around the 4x4 block of children [2x-1, 2x+2]^2 cover the texels [2x-2, 2x+3]^2; min / max are idempotent, so the
+      // FOUR windows centred on the block's corners cover the same texels ([2x-2, 2x] and [2x+1, 2x+3] per axis, clamped alike): 4 loads, not 16
+      for (int cy = 2 * y - 1; cy <= 2 * y + 2; cy += 3)
+        for (int cx = 2 * x - 1; cx <= 2 * x + 2; cx += 3)
           mm_merge(a, mm_down + (face * r0 + min(max(cy, 0), r0 - 1)) * r0 + min(max(cx, 0), r0 - 1));
     }
     bool flag = false;
