@@ -101,6 +101,19 @@ public:
                 "pbr::DeviceGroup::shadeViews");
   }
 
+  // The geometry pass of view blocks: member i rasterises viewCounts[i] cameras over its own copy of the scene (draws[i]) into the G-buffers
+  // that start at firstViews[i]; follow with shadeViews on the same blocks.
+  auto geometryViews(std::span<pbrcu_gbuffer const> firstViews, std::size_t viewStride8, std::size_t viewStride4, std::span<std::uint32_t const> viewCounts,
+                     std::span<float const* const> viewMatrices, std::span<float const* const> projMatrices, std::span<pbrcu_draw const* const> draws,
+                     std::span<std::uint32_t const> drawCounts) -> void {
+    if (firstViews.size() != size() || viewCounts.size() != size() || viewMatrices.size() != size() || projMatrices.size() != size() || draws.size() != size() ||
+        drawCounts.size() != size())
+      throw std::runtime_error("pbr::DeviceGroup::geometryViews: one entry per member expected");
+    core::check(pbrcu_mg_geometry_views(_mg, firstViews.data(), viewStride8, viewStride4, viewCounts.data(), viewMatrices.data(), projMatrices.data(), draws.data(),
+                                        drawCounts.data()),
+                "pbr::DeviceGroup::geometryViews");
+  }
+
   // GGX prefilter sharded over the members; gather = true leaves the whole chain in every member's destination.
   auto prefilter(std::span<pbrcu_ibl_source const* const> sources, std::uint32_t mipLevels, std::uint32_t sampleCount, std::span<void* const> chains,
                  bool gather) -> void {

@@ -421,6 +421,11 @@ int pbrcu_mg_shade_frame_ldr(pbrcu_mg* mg, const pbrcu_gbuffer* g, const float c
 int pbrcu_mg_shade_views(pbrcu_mg* mg, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
                          const uint32_t* n_views, const float* const* cam_pos_xyz, const pbrcu_light* lights_host,
                          uint32_t n_lights, const pbrcu_ibl* ibl, void* const* outs, size_t out_pitch, size_t out_view_stride);
+/* The geometry pass of view blocks: member i rasterises n_views[i] cameras (views16[i] / projs16[i], host, 16 floats per view) over its own copy
+ * of the scene (draws[i]: buffers in member i's memory) into the G-buffers starting at g0[i] (pbrcu_geometry_pass_batched per member). */
+int pbrcu_mg_geometry_views(pbrcu_mg* mg, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4, const uint32_t* n_views,
+                            const float* const* views16, const float* const* projs16, const pbrcu_draw* const* draws,
+                            const uint32_t* n_draws);
 /* GGX prefilter: member i convolves row block i of n of levels 1.. from its prepared source; gather != 0 stores every
  * finished texel into every member's chain, so all n chains are complete (and bit-identical to the unsharded one). */
 int pbrcu_mg_prefilter(pbrcu_mg* mg, const pbrcu_ibl_source* const* sources, uint32_t nmips, uint32_t nsamples,

@@ -161,6 +161,7 @@ _SIGNATURES = {
     "pbrcu_mg_shade_frame": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, C.POINTER(_u32), C.POINTER(_vp), _sz, _i]),
     "pbrcu_mg_shade_frame_ldr": (_i, [_vp, _PG, _f3, _vp, _u32, _PT, _PI, C.POINTER(_u32), C.POINTER(_vp), _sz, _i]),
     "pbrcu_mg_shade_views": (_i, [_vp, _PG, _sz, _sz, C.POINTER(_u32), C.POINTER(_f3), _vp, _u32, _PI, C.POINTER(_vp), _sz, _sz]),
+    "pbrcu_mg_geometry_views": (_i, [_vp, _PG, _sz, _sz, C.POINTER(_u32), C.POINTER(_f3), C.POINTER(_f3), C.POINTER(C.POINTER(Draw)), C.POINTER(_u32)]),
     "pbrcu_mg_prefilter": (_i, [_vp, C.POINTER(_vp), _u32, _u32, C.POINTER(_vp), _i]),
     "pbrcu_synth_gbuffer": (_i, [_vp, _PG, _i, _u64, _f3, _f3, _vp]),
     "pbrcu_synth_environment": (_i, [_vp, _vp, _u32, _u32, _u64, _vp]),

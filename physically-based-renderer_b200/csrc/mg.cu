@@ -331,6 +331,22 @@ extern "C" int pbrcu_mg_shade_views(pbrcu_mg* mg, const pbrcu_gbuffer* g0, size_
   return mg_barrier(mg);
 }
 
+// The geometry pass of a block of views per member (BASELINE configs[4]: "256 camera views ... of the glTF scene, views partitioned across the
+// GPUs"): member i rasterises n_views[i] cameras (views16[i], projs16[i]: 16 floats each, host) over ITS copy of the scene -- draws[i], whose
+// vertex / index / texture pointers live in member i's memory -- into the G-buffers that start at g0[i] (pbrcu_geometry_pass_batched per member).
+// Follow it with pbrcu_mg_shade_views on the same blocks.  No exchange.
+extern "C" int pbrcu_mg_geometry_views(pbrcu_mg* mg, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4, const uint32_t* n_views,
+                                       const float* const* views16, const float* const* projs16, const pbrcu_draw* const* draws, const uint32_t* n_draws) {
+  PBRCU_REQUIRE(mg && g0 && n_views && views16 && projs16 && draws && n_draws, "NULL argument");
+  for (int i = 0; i < mg->n; ++i) {
+    if (n_views[i] == 0) continue;
+    PBRCU_MG_ON(mg, i);
+    if (int rc = pbrcu_geometry_pass_batched(mg->ctx[i], &g0[i], view_stride8, view_stride4, n_views[i], views16[i], projs16[i], draws[i], n_draws[i], mg->stream[i]))
+      return rc;
+  }
+  return mg_barrier(mg);
+}
+
 // The GGX prefilter over the group: member i convolves row block i of n of every level 1.. from ITS prepared source (every member
 // holds the environment: K4 / K5 are replicated) and copies level 0 whole.  gather != 0 stores every finished texel into every
 // member's chain (pbrcu_ibl_prefilter_ggx_prepared's replicas), so all chains are complete after the barrier.

@@ -265,3 +265,93 @@ def test_mg_views_and_prefilter(pbr, dev, oracle, ibl_host):
             m.free()
         lib.mg_destroy(mg)
     _device0_current(lib)
+
+
+def test_mg_geometry_views_then_shading(pbr, dev, oracle, ibl_host):
+    """BASELINE configs[4] as written, through the C multi-GPU host: every member rasterises its block of camera views of one scene
+    (pbrcu_mg_geometry_views) and shades them (pbrcu_mg_shade_views).  G-buffer planes and HDR frames of every view must equal the
+    single-device pbrcu_geometry_pass + pbrcu_shade_ggx_ibl_batched results bit for bit (which test_gpu_raster pins to the oracle)."""
+    from oracle import raster_scene
+    from test_gpu_raster import camera, upload_draws
+    lib = pbr.load()
+    W, H, nv, nl = 96, 64, 5, 3
+    scene = raster_scene(1)
+    cams_eye = [(8 * np.cos(a), -1.0 - 0.5 * a, 8 * np.sin(a)) for a in np.linspace(0.2, 5.0, nv)]
+    cams = [camera(e, (0, 0, 0), aspect=W / H) for e in cams_eye]
+    views = np.ascontiguousarray(np.stack([np.asarray(v, np.float32).reshape(16) for v, _ in cams]))
+    projs = np.ascontiguousarray(np.stack([np.asarray(p, np.float32).reshape(16) for _, p in cams]))
+    eyes = np.ascontiguousarray(np.array(cams_eye, np.float32))
+    lights = synth_lights(nl, seed=21)
+    s8, s4 = W * H * 8, W * H * 4
+    names8, names4 = ("positions", "normals", "albedo", "emissive"), ("orm", "depth")
+
+    def gbuffers(m, n):
+        g0 = pbr.GBuffer()
+        g0.width, g0.height, g0.pitch8, g0.pitch4 = W, H, W * 8, W * 4
+        for k in names8:
+            setattr(g0, k, m.alloc(max(n, 1) * s8))
+        for k in names4:
+            setattr(g0, k, m.alloc(max(n, 1) * s4))
+        return g0
+
+    def planes(m, g0, n):
+        return {k: m.download(getattr(g0, k), (n, H, W, 4) if k != "depth" else (n, H, W), np.uint16 if k in names8 else (np.uint8 if k == "orm" else np.float32))
+                for k in names8 + names4}
+
+    # single device: the reference for every view
+    one = Member.single(pbr, lib, dev.ctx)
+    arr0, keep0 = upload_draws(pbr, dev, scene)
+    g_all = gbuffers(one, nv)
+    lib.geometry_pass_batched(dev.ctx, C.byref(g_all), s8, s4, nv, views.ctypes.data, projs.ctypes.data, arr0, len(scene), None)
+    ibl0 = one.ibl(ibl_host)
+    out0 = dev.alloc(nv * s8)
+    lib.shade_ggx_ibl_batched(dev.ctx, C.byref(g_all), s8, s4, nv, eyes.ctypes.data_as(C.POINTER(C.c_float)), lights.ctypes.data, nl, C.byref(ibl0), out0.ptr, W * 8, s8, None)
+    dev.sync()
+    want_planes, want_hdr = planes(one, g_all, nv), out0.download((nv, H, W, 4), np.uint16)
+    assert (want_planes["normals"] != 0).any()
+    lib.ibl_accel_free(dev.ctx, ibl0.accel)
+
+    class MemberDev:  # what upload_draws needs of a device: upload() into this member's memory
+        def __init__(self, m):
+            self.m = m
+
+        def upload(self, a):
+            class B:
+                pass
+            b = B()
+            b.ptr = self.m.upload(np.ascontiguousarray(a))
+            return b
+
+    for devices in groups(pbr):
+        n = len(devices)
+        mg = C.c_void_p()
+        lib.mg_create((C.c_int * n)(*devices), n, C.byref(mg))
+        members = [Member(pbr, lib, mg, i) for i in range(n)]
+        cuts = [nv * k // n for k in range(n + 1)]
+        counts = [cuts[k + 1] - cuts[k] for k in range(n)]
+        g0s = (pbr.GBuffer * n)(*[gbuffers(m, c) for m, c in zip(members, counts)])
+        draw_arrays = [upload_draws(pbr, MemberDev(m), scene) for m in members]
+        draws = (C.POINTER(pbr.Draw) * n)(*[C.cast(a, C.POINTER(pbr.Draw)) for a, _ in draw_arrays])
+        vblocks = [np.ascontiguousarray(views[cuts[k]:cuts[k + 1]]) if counts[k] else np.zeros((1, 16), np.float32) for k in range(n)]
+        pblocks = [np.ascontiguousarray(projs[cuts[k]:cuts[k + 1]]) if counts[k] else np.zeros((1, 16), np.float32) for k in range(n)]
+        eblocks = [np.ascontiguousarray(eyes[cuts[k]:cuts[k + 1]]) if counts[k] else np.zeros((1, 3), np.float32) for k in range(n)]
+        fptr = lambda blocks: (C.POINTER(C.c_float) * n)(*[b.ctypes.data_as(C.POINTER(C.c_float)) for b in blocks])
+        lib.mg_geometry_views(mg, g0s, s8, s4, (C.c_uint32 * n)(*counts), fptr(vblocks), fptr(pblocks), draws, (C.c_uint32 * n)(*[len(scene)] * n))
+        ibls = (pbr.Ibl * n)(*[m.ibl(ibl_host) for m in members])
+        outs = [m.alloc(max(c, 1) * s8) for m, c in zip(members, counts)]
+        lib.mg_shade_views(mg, g0s, s8, s4, (C.c_uint32 * n)(*counts), fptr(eblocks), lights.ctypes.data, nl, ibls, (C.c_void_p * n)(*outs), W * 8, s8)
+        lib.mg_synchronize(mg)
+        for k, (m, c) in enumerate(zip(members, counts)):
+            if not c:
+                continue
+            got = planes(m, g0s[k], c)
+            for name in got:
+                a, b = got[name], want_planes[name][cuts[k]:cuts[k + 1]]
+                assert np.array_equal(a.view(np.uint32) if name == "depth" else a, b.view(np.uint32) if name == "depth" else b), f"{devices} member {k}: plane {name} differs"
+            assert np.array_equal(m.download(outs[k], (c, H, W, 4), np.uint16), want_hdr[cuts[k]:cuts[k + 1]]), f"{devices} member {k}: shaded views differ"
+        for i, m in enumerate(members):
+            m.on()
+            lib.ibl_accel_free(m.ctx, ibls[i].accel)
+            m.free()
+        lib.mg_destroy(mg)
+    _device0_current(lib)
