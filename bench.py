@@ -498,6 +498,29 @@ def extra_configs(scene, torch, dist, world, rank):
                                       "roofline": roof("hbm", B_PER_PX_K3 * NV * WV * HV / (ms / 3 * 1e-3) / 1e9, measured_peak_gbs()[0] * world, "GB/s", "44 B/px, all views, all ranks"),
                                       "views_per_rank": nv, "scaling": "strong (view blocks, no exchange)",
                                       "what": "pbrcu_shade_ggx_ibl_batched: the rank's views in one launch, 4 point lights + IBL"}
+    # the reference's own per-view frame over the same views (Tier A, pinned to its shaders): lighting (K1) batched, and lighting + tonemap fused
+    # (K1+K2, LDR only) batched -- one launch each for the rank's block
+    ldr_views = scene.buf(max(nv, 1) * stride4)
+
+    def step_views_k1(_):
+        if nv:
+            lib.lighting_blinnphong_batched(ctx, C.byref(g0), stride8, stride4, nv, cam_ptr, outs.data_ptr(), WV * 8, stride8, scene.stream())
+
+    def step_views_fused(_):
+        if nv:
+            lib.lighting_tonemap_fused_batched(ctx, C.byref(g0), stride8, nv, cam_ptr, None, 0, 0, ldr_views.data_ptr(), WV * 4, stride4, scene.stream())
+
+    ms_k1 = timed(torch, dist, step_views_k1, 3, 3) / 3
+    ms_fu = timed(torch, dist, step_views_fused, 3, 3) / 3
+    peak_v = measured_peak_gbs()[0] * world
+    out["config4_256_views_1080p_tier_a"] = {
+        "what": "the reference's per-view frame (lighting.glsl, then aces+gamma.glsl) over the same 256 views: pbrcu_lighting_blinnphong_batched and "
+                "pbrcu_lighting_tonemap_fused_batched (LDR only), the rank's views in one launch each",
+        "ms_lighting": round(ms_k1, 3), "ms_lighting_tonemap_fused_ldr": round(ms_fu, 3), "views_per_rank": nv,
+        "roofline_lighting": roof("hbm", B_PER_PX_K1 * NV * WV * HV / (ms_k1 * 1e-3) / 1e9, peak_v, "GB/s", "32 B/px, all views, all ranks"),
+        "roofline_fused_ldr": roof("hbm", 28 * NV * WV * HV / (ms_fu * 1e-3) / 1e9, peak_v, "GB/s", "28 B/px (24 read + 4 written), all views, all ranks")}
+    scene.keep = [t for t in scene.keep if t is not ldr_views]
+    del ldr_views
     out["geometry_pass_1080p"] = geometry_bench(scene, torch, dist, world, rank)
     out["config2_prefilter_sharded"] = prefilter_sharded(scene, torch, dist, world, rank)
     return out
