@@ -1,4 +1,5 @@
-"""K3 on the bench's 4K frame with L2 cache-policy hints (PBRCU_K3_L2: bit 0 = evict-first on the staged planes, bit 1 = evict-last on the
+"""(Ran on a build that carried the L2 cache-policy plumbing -- PBRCU_K3_L2 -- which was reverted after this measurement: profiles/r02_k3_l2_hints.txt.)
+K3 on the bench's 4K frame with L2 cache-policy hints (PBRCU_K3_L2: bit 0 = evict-first on the staged planes, bit 1 = evict-last on the
 prefiltered records), both filter modes; results must stay bit-identical (hints do not change values)."""
 import os, sys, ctypes as C
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

@@ -1,4 +1,5 @@
-"""K3 on the bench's 4K frame: default shade_ggx_cl_kernel vs the L2-prefetch pipelined form (PBRCU_K3_PIPE=1: 5 CTAs/SM, =2: 4 CTAs/SM), both filter modes."""
+"""(Ran on a build that carried scratch/shade_ggx_cl_pipe.cu.txt -- PBRCU_K3_PIPE -- which was removed after this measurement: profiles/r02_k3_pipe.txt.)
+K3 on the bench's 4K frame: default shade_ggx_cl_kernel vs the L2-prefetch pipelined form (PBRCU_K3_PIPE=1: 5 CTAs/SM, =2: 4 CTAs/SM), both filter modes."""
 import os, sys, ctypes as C
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, numpy as np
