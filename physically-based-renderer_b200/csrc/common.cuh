@@ -7,7 +7,7 @@
 #include "../../include/pbrcu.h"
 
 namespace pbrcu {
-constexpr int kRasterSlots = 4;
+constexpr int kRasterSlots = 8;  // most concurrent views of pbrcu_geometry_pass_batched (scratch sets are created on first use)
 // a cube-map mip chain as a hardware texture with contrast flags in alpha (cube_tex.cuh)
 struct CubeTex {
   cudaMipmappedArray_t array;
@@ -42,10 +42,10 @@ struct pbrcu_ctx {
   void* raster_scratch;  // K10: visibility buffer, piece set-ups, chunk queue, draw table (grown on demand)
   size_t raster_bytes;
   // pbrcu_geometry_pass_batched: consecutive views run on these internal streams, one scratch set each
-  void* raster_slot_scratch[4];
-  size_t raster_slot_bytes[4];
-  cudaStream_t raster_slot_stream[4];
-  cudaEvent_t raster_slot_done[4];
+  void* raster_slot_scratch[pbrcu::kRasterSlots];
+  size_t raster_slot_bytes[pbrcu::kRasterSlots];
+  cudaStream_t raster_slot_stream[pbrcu::kRasterSlots];
+  cudaEvent_t raster_slot_done[pbrcu::kRasterSlots];
   cudaEvent_t raster_start;
   bool shade_tex;         // K3: texture-unit fetches of the prefiltered / irradiance cubes (pbrcu_shade_set_texture_unit)
 };

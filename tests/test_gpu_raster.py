@@ -143,6 +143,35 @@ def test_clipping_near_plane_and_guard_band(pbr, dev, oracle):
     assert_same(device_pass(pbr, dev, d2, eye, eye, 40, 30), want2, "guard-band clipping")
 
 
+def test_edge_function_width_switch(pbr, dev, oracle):
+    """Pieces below 128 pixels of extent evaluate their edge functions in 32-bit integers, larger ones in 64-bit (csrc/raster.cu,
+    narrow_extent): triangles on either side of the switch, slivers that leave the frame with a small on-screen box, and a fan of
+    thin wedges whose extents straddle it, all against the oracle's 64-bit arithmetic."""
+    eye = np.eye(4, dtype=np.float32).reshape(-1)
+    W = H = 400  # NDC half-extent 1 = 200 pixels: an extent of e pixels is 2 e / 400 in NDC
+    cases = []
+    for e in (126.5, 127.9, 127.998, 128.0, 128.004, 129.3):
+        a = e / 200.0
+        cases.append([mesh_vertex((-0.4, -0.45, 0.3)), mesh_vertex((-0.4 + a, -0.45 + 0.11, 0.6)), mesh_vertex((-0.4 + 0.07, -0.45 + a, 0.9))])
+    # sliver through the corner: tiny box on screen, edges far longer than 128 pixels
+    cases.append([mesh_vertex((-1.004, -1.004, 0.5)), mesh_vertex((3.0, -1.3, 0.5)), mesh_vertex((-1.3, 3.0, 0.5))])
+    cases.append([mesh_vertex((0.99, 0.99, 0.2)), mesh_vertex((0.9975, 40.0, 0.2)), mesh_vertex((40.0, 0.9975, 0.2))])
+    for tri in cases:
+        d = [make_draw(tri, [0, 1, 2, 0, 2, 1])]
+        want = oracle.geometry_pass(d, eye, eye, W, H, extended=True)
+        assert (want["prim"] != EMPTY).any()
+        assert_same(device_pass(pbr, dev, d, eye, eye, W, H), want, "edge width switch")
+    n = 181
+    ang = np.linspace(0, 2 * np.pi, n + 1)
+    rad = 0.6 + 0.08 * np.cos(7 * ang)  # 120 .. 136 pixels from the hub
+    v = [mesh_vertex((0.003, -0.002, 0.5))] + [mesh_vertex((r * np.cos(a), r * np.sin(a), 0.25 + 0.2 * np.sin(a))) for a, r in zip(ang, rad)]
+    idx = []
+    for k in range(n):
+        idx += [0, 1 + k, 2 + k]
+    d = [make_draw(v, idx)]
+    assert_same(device_pass(pbr, dev, d, eye, eye, W, H), oracle.geometry_pass(d, eye, eye, W, H, extended=True), "wedge fan")
+
+
 def test_large_and_small_triangles_full_hd(pbr, dev, oracle):
     """1920x1080: screen-filling triangles go through the chunk queue, a dense sphere through the per-triangle warps;
     first_index / vertex_offset (MeshBuilder-style concatenated primitives) are honoured."""
