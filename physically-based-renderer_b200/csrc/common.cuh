@@ -41,9 +41,11 @@ struct pbrcu_ctx {
   bool exact_ibl_filter;  // K6/K7: software fp32-weight filtering instead of the texture unit
   void* raster_scratch;  // K10: visibility buffer, piece set-ups, chunk queue, draw table (grown on demand)
   size_t raster_bytes;
+  size_t raster_clean_px;  // leading entries of the scratch's visibility buffer that the last pass left empty (its resolve kernel resets what it reads)
   // pbrcu_geometry_pass_batched: consecutive views run on these internal streams, one scratch set each
   void* raster_slot_scratch[pbrcu::kRasterSlots];
   size_t raster_slot_bytes[pbrcu::kRasterSlots];
+  size_t raster_slot_clean_px[pbrcu::kRasterSlots];
   cudaStream_t raster_slot_stream[pbrcu::kRasterSlots];
   cudaEvent_t raster_slot_done[pbrcu::kRasterSlots];
   cudaEvent_t raster_start;

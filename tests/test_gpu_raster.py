@@ -143,6 +143,18 @@ def test_clipping_near_plane_and_guard_band(pbr, dev, oracle):
     assert_same(device_pass(pbr, dev, d2, eye, eye, 40, 30), want2, "guard-band clipping")
 
 
+def test_consecutive_passes_reuse_the_visibility_buffer(pbr, dev, oracle):
+    """The resolve kernel leaves the visibility buffer empty for the next pass over the same scratch (no fill of its own): passes of
+    changing extent and content through ONE context must each equal the oracle -- larger after smaller, smaller after larger, an empty
+    scene in between."""
+    view, proj = camera(aspect=1.0)
+    sv, si = uv_sphere(1.0, 12, 24)
+    ball = make_draw(sv, si, model_push_constant((0.3, -0.2, -3.0), (2, 2, 2), (0, 1, 0), 0.3), color_tex=checker_texture(8, 8, 3))
+    far = make_draw(sv, si, model_push_constant((-1.0, 0.5, 2.0), (4, 4, 4), (1, 0, 0), 1.1), color=(0.2, 0.9, 0.4, 1.0))
+    for draws, W, H in (([ball], 96, 96), ([ball, far], 200, 160), ([far], 64, 48), ([], 200, 160), ([ball, far], 200, 160), ([ball], 31, 17), ([far, ball], 96, 96)):
+        assert_same(device_pass(pbr, dev, draws, view, proj, W, H), oracle.geometry_pass(draws, view, proj, W, H, extended=True), f"{len(draws)} draws at {W}x{H}")
+
+
 def test_edge_function_width_switch(pbr, dev, oracle):
     """Pieces below 128 pixels of extent evaluate their edge functions in 32-bit integers, larger ones in 64-bit (csrc/raster.cu,
     narrow_extent): triangles on either side of the switch, slivers that leave the frame with a small on-screen box, and a fan of
