@@ -156,13 +156,13 @@ def test_consecutive_passes_reuse_the_visibility_buffer(pbr, dev, oracle):
 
 
 def test_edge_function_width_switch(pbr, dev, oracle):
-    """Pieces below 128 pixels of extent evaluate their edge functions in 32-bit integers, larger ones in 64-bit (csrc/raster.cu,
+    """Pieces below 64 pixels of extent evaluate their edge functions in 32-bit integers, larger ones in 64-bit (csrc/raster.cu,
     narrow_extent): triangles on either side of the switch, slivers that leave the frame with a small on-screen box, and a fan of
     thin wedges whose extents straddle it, all against the oracle's 64-bit arithmetic."""
     eye = np.eye(4, dtype=np.float32).reshape(-1)
     W = H = 400  # NDC half-extent 1 = 200 pixels: an extent of e pixels is 2 e / 400 in NDC
     cases = []
-    for e in (126.5, 127.9, 127.998, 128.0, 128.004, 129.3):
+    for e in (31.7, 62.5, 63.9, 63.998, 64.0, 64.004, 65.3, 126.5, 127.998, 128.004):
         a = e / 200.0
         cases.append([mesh_vertex((-0.4, -0.45, 0.3)), mesh_vertex((-0.4 + a, -0.45 + 0.11, 0.6)), mesh_vertex((-0.4 + 0.07, -0.45 + a, 0.9))])
     # sliver through the corner: tiny box on screen, edges far longer than 128 pixels
@@ -175,7 +175,7 @@ def test_edge_function_width_switch(pbr, dev, oracle):
         assert_same(device_pass(pbr, dev, d, eye, eye, W, H), want, "edge width switch")
     n = 181
     ang = np.linspace(0, 2 * np.pi, n + 1)
-    rad = 0.6 + 0.08 * np.cos(7 * ang)  # 120 .. 136 pixels from the hub
+    rad = 0.3 + 0.04 * np.cos(7 * ang)  # 52 .. 68 pixels from the hub
     v = [mesh_vertex((0.003, -0.002, 0.5))] + [mesh_vertex((r * np.cos(a), r * np.sin(a), 0.25 + 0.2 * np.sin(a))) for a, r in zip(ang, rad)]
     idx = []
     for k in range(n):
