@@ -56,8 +56,9 @@ def run(tag):
     lib.geometry_pass_batched(ctx, C.byref(gv), s8, s4, NV, views.ctypes.data, projs.ctypes.data, draws, 65, st)
     b.record(); torch.cuda.synchronize()
     ts = a.elapsed_time(b) / NV * 1e3
-    os.environ["PBRCU_RASTER_SLOTS"] = "4"
+    os.environ["PBRCU_RASTER_SLOTS"] = SLOTS
     print(f"{tag}: 4 concurrent {tb:.1f} us/view, serial {ts:.1f} us/view, same checksum {chk == ref}", flush=True)
-os.environ["PBRCU_RASTER_SLOTS"] = "4"
+SLOTS = "4"
+os.environ["PBRCU_RASTER_SLOTS"] = SLOTS
 for t in ("a", "b"):
     run(f"run {t}")
