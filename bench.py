@@ -682,7 +682,7 @@ def geometry_bench(scene, torch, dist, world, rank):
     views_entry = {"views": NV, "views_per_rank": nv, "ms_geometry_all_views": round(ms_geo_views, 3), "ms_geometry_plus_shading_all_views": round(ms_frames_views, 3),
                    "us_geometry_per_view": round(ms_geo_views * 1e3 / max(nv, 1), 2), "mpix_s": round(NV * W * H / (ms_frames_views * 1e-3) / 1e6, 1),
                    "sampled_views_equal_single_pass": same, "scaling": "strong (view blocks, no exchange)",
-                   "what": "pbrcu_geometry_pass_batched (draw tables uploaded once, views overlapped on 4 internal streams) + pbrcu_shade_ggx_ibl_batched, "
+                   "what": "pbrcu_geometry_pass_batched (draw tables uploaded once, camera-independent vertex attributes computed by view 0 and shared, views overlapped on 4 internal streams) + pbrcu_shade_ggx_ibl_batched, "
                            f"{n_tris} triangles per view at 1920x1080, 4 point lights + IBL; the scene is the mesh generator's (the reference's bundled .glb is "
                            "missing from its snapshot); glTF -> device import is exercised by tools/gltf_viewer and its tests"}
     for t in list(vplanes.values()) + [vout]:
