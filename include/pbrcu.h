@@ -374,9 +374,11 @@ int pbrcu_geometry_pass(pbrcu_ctx* ctx, const pbrcu_gbuffer* g, const float view
 
 /* The geometry pass of n_views cameras over one set of draws (BASELINE configs[4]: many views of one scene): view v -- camera
  * views16[16 v ..], projs16[16 v ..], column-major like pbrcu_geometry_pass -- fills the G-buffer view_stride8 / view_stride4
- * bytes after view v-1's (all planes g0 has, depth included).  The draw tables are built and uploaded once, and consecutive
- * views run on internal streams with a scratch set each, so their small kernels overlap on the device.  Bit-identical per view
- * to pbrcu_geometry_pass.  Replaces n_views iterations of PbrRenderSystem::recordGeometryPass (PbrRenderSystem.cpp:367-465). */
+ * bytes after view v-1's (all planes g0 has, depth included).  The draw tables are built and uploaded once, the vertex stage's
+ * camera-independent outputs (world position, N / T / B, texture coordinates) are computed by view 0 and shared by the others, and
+ * consecutive views run on internal streams (4; environment PBRCU_RASTER_SLOTS = 1..8) with a scratch set each, so their small
+ * kernels overlap on the device.  Bit-identical per view to pbrcu_geometry_pass.  Replaces n_views iterations of
+ * PbrRenderSystem::recordGeometryPass (PbrRenderSystem.cpp:367-465). */
 int pbrcu_geometry_pass_batched(pbrcu_ctx* ctx, const pbrcu_gbuffer* g0, size_t view_stride8, size_t view_stride4,
                                 uint32_t n_views, const float* views16, const float* projs16, const pbrcu_draw* draws,
                                 uint32_t n_draws, pbrcu_stream s);
