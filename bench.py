@@ -522,6 +522,7 @@ def extra_configs(scene, torch, dist, world, rank):
     scene.keep = [t for t in scene.keep if t is not ldr_views]
     del ldr_views
     out["geometry_pass_1080p"] = geometry_bench(scene, torch, dist, world, rank)
+    out["geometry_pass_1080p"]["config4_256_views_gltf"] = gltf_views_bench(torch, dist, world, rank)
     out["config2_prefilter_sharded"] = prefilter_sharded(scene, torch, dist, world, rank)
     return out
 
@@ -577,6 +578,72 @@ def prefilter_sharded(scene, torch, dist, world, rank):
     return {**fused, "ms_prefilter_and_gather": round(ms, 3), "ms_prefilter_shard_only": round(ms_conv, 3), "shards": world,
             "gathered_chain_equals_unsharded": same, "gather_bytes_per_rank": int((dst.numel() - 6 * CUBE_RES * CUBE_RES * 8) * (world - 1) // world),
             "scaling": "strong (row blocks of levels 1..; level 0 copied whole on every rank; NCCL all-gather of levels 1..)"}
+
+
+def gltf_views_bench(torch, dist, world, rank):
+    """BASELINE configs[4] through the glTF path: the 65-draw scene written as a .glb (tests/gltfwriter.py), imported by the C++ facade
+    (pbr::gltf::Loader -> Asset::loadScene -> TransferStager) inside tools/gltf_viewer, and 256 orbit cameras rendered by
+    PbrRenderSystem::renderViews (one batched geometry pass + one batched GGX shading pass per rank's view block).  The viewer is a process
+    of its own on this rank's GPU; it times enqueue + synchronise with the host clock (min of 3 repeats after a warm-up)."""
+    import subprocess
+    import tempfile
+    viewer = ROOT / "tools" / "gltf_viewer" / "build" / "gltf_viewer"
+    if not viewer.exists():
+        return {"unavailable": "tools/gltf_viewer/build/gltf_viewer is not built (python -c 'import __graft_entry__ as g; g.build()')"}
+    sys.path.insert(0, str(ROOT / "tests"))  # the glTF writer is test tooling (not the checker)
+    from gltfwriter import Builder
+    from pbr_b200.partition import view_block
+    from pbr_b200.synth import checker_texture, mesh_vertex, uv_sphere
+    rng = np.random.default_rng(7)
+    b = Builder()
+    sv, si = uv_sphere(1.0, 48, 96)
+    sv = np.asarray(sv, np.float32).reshape(-1, 12)
+    g = 40.0
+    quad = np.array([mesh_vertex((-g, 3.0, -g), (0, -1, 0), (1, 0, 0, 1), (0, 0)), mesh_vertex((g, 3.0, -g), (0, -1, 0), (1, 0, 0, 1), (16, 0)),
+                     mesh_vertex((g, 3.0, g), (0, -1, 0), (1, 0, 0, 1), (16, 16)), mesh_vertex((-g, 3.0, g), (0, -1, 0), (1, 0, 0, 1), (0, 16))], np.float32)
+    qi = np.array([0, 1, 2, 0, 2, 3, 0, 2, 1, 0, 3, 2], np.uint16)
+    ct, nt, flat = b.image(checker_texture(64, 64, 1), "checker"), b.image(checker_texture(32, 32, 2, normal_map=True), "bumps"), b.image(np.array([[[128, 128, 255, 255]]], np.uint8), "flat")
+    ball = b.primitive(sv, si, 0)  # one set of accessors, 64 materials
+    nodes = []
+    for k in range(64):
+        t, sc, axis, ang = rng.uniform(-8, 8, 3), rng.uniform(0.5, 1.5, 3), rng.standard_normal(3), rng.uniform(0, 6.28)
+        axis = axis / np.linalg.norm(axis)
+        m = b.material(f"m{k}", rng.uniform(0.3, 1.0, 4), ct, nt, metallic=float(rng.integers(0, 2)), roughness=float(rng.uniform(0.05, 1.0)))
+        nodes.append(b.node(f"ball{k}", mesh=b.mesh(f"ball{k}", [dict(ball, material=m)]), translation=t, rotation_xyzw=(*(axis * np.sin(ang / 2)), np.cos(ang / 2)), scale=sc))
+    mg = b.material("ground", (0.8, 0.8, 0.8, 1.0), ct, flat, metallic=0.0, roughness=0.6)
+    nodes.append(b.node("ground", mesh=b.mesh("ground", [b.primitive(quad, qi, mg)])))
+    b.scene(nodes)
+    NV, W, H = 256, 1920, 1080
+    v0, v1 = view_block(NV, world, rank)
+    out = None
+    with tempfile.TemporaryDirectory() as tmp:
+        path = Path(tmp) / "scene.glb"
+        b.write_glb(path)
+        glb_bytes = path.stat().st_size
+        if v1 > v0:
+            env = dict(os.environ)
+            local = int(os.environ.get("LOCAL_RANK", "0"))
+            visible = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d]
+            env["CUDA_VISIBLE_DEVICES"] = visible[local] if local < len(visible) else str(local)
+            r = subprocess.run([str(viewer), str(path), "--size", f"{W}x{H}", "--ggx", "--views", str(v1 - v0), "--view-first", str(v0), "--view-total", str(NV), "--frames", "3",
+                                "--orbit", "12,-2", "--times", str(Path(tmp) / "t.json")], capture_output=True, text=True, env=env, timeout=600)
+            if r.returncode != 0:
+                return {"unavailable": f"gltf_viewer failed: {r.stderr.strip()[-300:]}"}
+            out = json.loads((Path(tmp) / "t.json").read_text())
+    ms = torch.tensor([out["ms_geometry"] if out else 0.0, out["ms_geometry_plus_shading"] if out else 0.0], dtype=torch.float64, device="cuda")
+    if dist is not None and world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    tri = torch.tensor([out["triangles_per_view"] if out else 0, out["draws"] if out else 0], dtype=torch.int64, device="cuda")
+    if dist is not None and world > 1:
+        dist.all_reduce(tri, op=dist.ReduceOp.MAX)
+    ms_geo, ms_both = float(ms[0]), float(ms[1])
+    return {"views": NV, "views_per_rank": v1 - v0, "ms_geometry_all_views": round(ms_geo, 3), "ms_geometry_plus_shading_all_views": round(ms_both, 3),
+            "us_geometry_per_view": round(ms_geo * 1e3 / max(v1 - v0, 1), 2), "mpix_s": round(NV * W * H / (ms_both * 1e-3) / 1e6, 1),
+            "triangles_per_view": int(tri[0]), "draws": int(tri[1]), "glb_bytes": glb_bytes, "scaling": "strong (view blocks, no exchange)",
+            "timing": "host clock around enqueue + stream synchronise inside the viewer process, min of 3 repeats after a warm-up, max over ranks",
+            "what": "tests/gltfwriter.py scene (.glb: 64 textured spheres + a ground plane that crosses the near plane) -> pbr::gltf::Loader -> Asset::loadScene -> "
+                    "PbrRenderSystem::renderViews = pbrcu_geometry_pass_batched + pbrcu_shade_ggx_ibl_batched, 4 point lights + IBL, 1920x1080; parity of the path: "
+                    "tests/test_gpu_viewer.py::test_viewer_views_mode_matches_oracle (first / middle / last view bit-exact vs the oracle's geometry pass)"}
 
 
 def geometry_bench(scene, torch, dist, world, rank):

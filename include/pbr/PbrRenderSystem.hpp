@@ -12,14 +12,18 @@
 // The geometry pass (K10, a CUDA visibility-buffer rasteriser behind pbrcu_geometry_pass) runs when the scene
 // holds mesh nodes; a scene without meshes shades whatever the caller put into the G-buffer (the deferred hot
 // path on its own).
+// CUDA addition: renderViews() renders a block of camera views of one scene (BASELINE configs[4]) with ONE batched geometry pass
+// and ONE batched lighting pass (pbrcu_geometry_pass_batched + pbrcu_shade_ggx_ibl_batched / pbrcu_lighting_blinnphong_batched).
 #pragma once
 #include "pbr/Environment.hpp"
 #include "pbr/GBuffer.hpp"
 #include "pbr/ModelPushConstant.hpp"
 #include "pbr/Scene.hpp"
+#include "pbr/ViewBlock.hpp"
 
 #include <cstring>
 #include <memory>
+#include <span>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -69,13 +73,60 @@ public:
     recordLightingPass(cmdBuffer, scene, gBuffer, renderTarget, vk::Rect2D {.offset = {}, .extent = renderExtent});
   }
 
-private:
-  // PbrRenderSystem.cpp:367-465: clear, then one drawIndexed per primitive of every mesh node in iterateAllNodes()
-  // order, model / normal matrices from the node's own transform (makeModelPushConstant, :446-449).
-  // Runs when the scene holds mesh nodes; a scene without meshes keeps the caller-filled G-buffer.
-  auto recordGeometryPass(vk::CommandBuffer cmdBuffer, Scene const& scene, GBuffer const& gBuffer) -> void {
-    std::vector<pbrcu_draw> draws;
+  [[nodiscard]] auto allocateViewBlock(IAllocator& allocator, vk::Extent2D extent, std::uint32_t views) -> ViewBlock {
+    return ViewBlock {allocator, extent, views, _info.shadingModel == ShadingModel::MetallicRoughness};
+  }
+
+  // cameras.size() views of `scene` into the first cameras.size() views of `block`: what cameras.size() calls of render() with the
+  // scene's camera set to cameras[v] would leave in G-buffer and render target v, from one batched geometry pass (draw tables and
+  // camera-independent vertex work once) and one batched lighting pass.  The scene's own camera is not consulted.  MetallicRoughness
+  // shading loops the scene's lights per pixel (no clustering: the tile lists depend on the view).  lightingPass = false stops after the
+  // geometry pass (the G-buffers only).
+  auto renderViews(vk::CommandBuffer cmdBuffer, Scene const& scene, std::span<CameraData const> cameras, ViewBlock const& block, bool lightingPass = true)
+      -> void {
+    if (cameras.empty()) return;
+    if (cameras.size() > block.getViewCount()) throw std::runtime_error("pbr::PbrRenderSystem::renderViews: more cameras than the block has views");
+    if (block.isExtended() != (_info.shadingModel == ShadingModel::MetallicRoughness))
+      throw std::runtime_error("pbr::PbrRenderSystem::renderViews: the block was allocated for the other shading model");
+    auto* ctx = _gpu->getContext();
+    auto* stream = cmdBuffer.stream();
+    auto const n = static_cast<std::uint32_t>(cameras.size());
+    std::vector<float> views(16 * cameras.size()), projs(16 * cameras.size()), positions(3 * cameras.size());
+    for (std::size_t v = 0; v < cameras.size(); ++v) {
+      std::memcpy(views.data() + 16 * v, &cameras[v].view, 64);
+      std::memcpy(projs.data() + 16 * v, &cameras[v].proj, 64);
+      positions[3 * v] = cameras[v].position.x; positions[3 * v + 1] = cameras[v].position.y; positions[3 * v + 2] = cameras[v].position.z;
+    }
     bool anyMesh = false;
+    auto const draws = collectDraws(scene, anyMesh);
+    auto const g0 = block.raw();
+    if (anyMesh)
+      core::check(pbrcu_geometry_pass_batched(ctx, &g0, block.viewStride8(), block.viewStride4(), n, views.data(), projs.data(), draws.data(),
+                                              static_cast<std::uint32_t>(draws.size()), stream),
+                  "PbrRenderSystem: batched geometry pass");
+    if (!lightingPass) return;
+    if (_info.shadingModel == ShadingModel::BlinnPhong) {
+      core::check(pbrcu_lighting_blinnphong_batched(ctx, &g0, block.viewStride8(), block.viewStride4(), n, positions.data(), block.getFrames(), block.pitch8(),
+                                                    block.frameStride(), stream),
+                  "PbrRenderSystem: batched lighting pass");
+      return;
+    }
+    auto const lights = scene.getLights();
+    if (lights.size() > 128) throw std::runtime_error("pbr::PbrRenderSystem::renderViews: at most 128 lights (unclustered loop)");
+    pbrcu_ibl ibl {};
+    if (_environment) ibl = _environment->raw();
+    core::check(pbrcu_shade_ggx_ibl_batched(ctx, &g0, block.viewStride8(), block.viewStride4(), n, positions.data(), reinterpret_cast<pbrcu_light const*>(lights.data()),
+                                            static_cast<std::uint32_t>(lights.size()), _environment ? &ibl : nullptr, block.getFrames(), block.pitch8(),
+                                            block.frameStride(), stream),
+                "PbrRenderSystem: batched GGX shading pass");
+  }
+
+private:
+  // one pbrcu_draw per primitive of every mesh node in iterateAllNodes() order, model / normal matrices from the node's own
+  // transform (PbrRenderSystem.cpp:432-462, makeModelPushConstant :446-449)
+  [[nodiscard]] static auto collectDraws(Scene const& scene, bool& anyMesh) -> std::vector<pbrcu_draw> {
+    std::vector<pbrcu_draw> draws;
+    anyMesh = false;
     for (auto const& node : scene.iterateAllNodes()) {
       auto const& mesh = node.getMesh();
       if (!mesh) continue;
@@ -109,6 +160,14 @@ private:
         draws.push_back(d);
       }
     }
+    return draws;
+  }
+
+  // PbrRenderSystem.cpp:367-465: clear, then one drawIndexed per primitive.
+  // Runs when the scene holds mesh nodes; a scene without meshes keeps the caller-filled G-buffer.
+  auto recordGeometryPass(vk::CommandBuffer cmdBuffer, Scene const& scene, GBuffer const& gBuffer) -> void {
+    bool anyMesh = false;
+    auto draws = collectDraws(scene, anyMesh);
     if (!anyMesh) return;
     auto const camera = scene.findCamera();
     if (!camera) draws.clear();  // no camera bound: the pass still clears the attachments

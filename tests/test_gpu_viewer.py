@@ -68,7 +68,11 @@ def asset(tmp_path):
     return path, draws
 
 
-def check_frame(oracle, d, draws, W, H):
+def check_frame(oracle, d, draws, W, H, prefix="", ldr_frame=True):
+    class _Prefixed:  # d / "name" -> d / (prefix + "name")
+        def __truediv__(self, name):
+            return d_plain / (prefix + name)
+    d_plain, d = d, _Prefixed()
     mats = np.fromfile(d / "matrices.bin", np.float32)
     view, proj, eye, per_draw = mats[:16], mats[16:32], mats[32:35], mats[36:].reshape(-1, 28)
     assert len(per_draw) == len(draws)
@@ -82,9 +86,11 @@ def check_frame(oracle, d, draws, W, H):
         assert np.array_equal(got[name], want[name]), f"G-buffer plane {name} differs in {np.count_nonzero(got[name] != want[name])} values"
     assert np.array_equal(got["depth"].view(np.uint32), want["depth"].view(np.uint32))
     hdr = np.fromfile(d / "hdr.bin", np.uint16).reshape(H, W, 4)
-    ldr = np.fromfile(d / "ldr.bin", np.uint8).reshape(H, W, 4)
     _, want_hdr = oracle.lighting(want["pos"].view(np.float16), want["nrm"].view(np.float16), want["alb"], tuple(eye))
     assert np.abs(f16(hdr) - f16(want_hdr)).max() <= 1e-3
+    if not ldr_frame:
+        return covered, eye, per_draw, None
+    ldr = np.fromfile(d / "ldr.bin", np.uint8).reshape(H, W, 4)
     assert np.abs(ldr.astype(int) - oracle.tonemap(hdr).astype(int)).max() <= 1
     return covered, eye, per_draw, ldr
 
@@ -126,6 +132,36 @@ def test_viewer_frame_loop_moves_camera_and_spins_nodes(viewer, oracle, tmp_path
     assert np.allclose(parent_model[:3, :3], [[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]], atol=1e-5)
     times = json.loads((tmp_path / "times.json").read_text())
     assert times["frames"] == 5 and len(times["frame_time_ms"]) == 5 and all(t > 0 for t in times["frame_time_ms"])
+
+
+def test_viewer_views_mode_matches_oracle(viewer, oracle, tmp_path):
+    """--views: a block of orbit cameras of the glTF scene through PbrRenderSystem::renderViews (one batched geometry pass, one batched
+    lighting pass; BASELINE configs[4]).  First, middle and last view: G-buffer planes BIT FOR BIT the oracle's geometry pass on the
+    matrices the viewer computed, frames within the lighting tolerance; the views differ from each other; a shard of the same orbit
+    (--view-first / --view-total) reproduces the corresponding views of the whole one byte for byte."""
+    path, draws = asset(tmp_path)
+    W, H, N = 200, 120, 7
+    d = tmp_path / "views"; d.mkdir()
+    r = subprocess.run([viewer, str(path), "--size", f"{W}x{H}", "--views", str(N), "--frames", "1", "--orbit", "9,-2", "--dump", str(d), "--times", str(tmp_path / "v.json")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    t = json.loads((tmp_path / "v.json").read_text())
+    assert t["views"] == N and t["draws"] == len(draws) and t["triangles_per_view"] == sum(x["n"] // 3 for x in draws)
+    assert 0 < t["ms_geometry"] <= t["ms_geometry_plus_shading"] * 1.5
+    eyes = []
+    for v in (0, N // 2, N - 1):
+        covered, eye, _, _ = check_frame(oracle, d, draws, W, H, prefix=f"view{v}_", ldr_frame=False)
+        assert covered > 0.02
+        eyes.append(tuple(eye))
+    assert len(set(eyes)) == 3
+    # cameras 3..6 of the same orbit as a shard of their own
+    d2 = tmp_path / "shard"; d2.mkdir()
+    r = subprocess.run([viewer, str(path), "--size", f"{W}x{H}", "--views", "4", "--view-first", "3", "--view-total", str(N), "--frames", "1", "--orbit", "9,-2",
+                        "--dump", str(d2)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for name in ("pos", "nrm", "alb", "depth", "hdr", "matrices"):
+        assert (d2 / f"view0_{name}.bin").read_bytes() == (d / f"view{N // 2}_{name}.bin").read_bytes(), name
+        assert (d2 / f"view3_{name}.bin").read_bytes() == (d / f"view{N - 1}_{name}.bin").read_bytes(), name
 
 
 def test_viewer_ggx_mode_runs(viewer, tmp_path):

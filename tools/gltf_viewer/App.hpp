@@ -34,6 +34,10 @@ struct Options {
   bool spin {true};
   bool ggx {false};  // Tier B: GGX + point lights + IBL instead of the reference's Blinn-Phong lighting pass
   std::string outPng, outPfm, outTimes, dumpDir;
+  // CUDA addition (BASELINE configs[4], "256 camera views of the glTF scene"): views > 0 renders cameras viewFirst .. viewFirst + views - 1 of
+  // an orbit of viewTotal cameras around the origin through PbrRenderSystem::renderViews instead of running the frame loop
+  std::uint32_t views {}, viewFirst {}, viewTotal {};
+  float orbitRadius {12.0f}, orbitHeight {-2.0f};
 };
 
 class App {
@@ -168,6 +172,62 @@ public:
 
   [[nodiscard]] auto frameTimes() const noexcept -> std::vector<double> const& { return _frameMs; }
 
+  // --views: one batched geometry pass + one batched lighting pass over a block of orbit cameras; timed after a warm-up call (scratch
+  // growth, table uploads), geometry alone and geometry + lighting, host clock around enqueue + stream synchronise
+  auto runViews() -> void {
+    vk::CommandBuffer cmd {_stream};
+    auto const n = _opt.views, total = _opt.viewTotal ? _opt.viewTotal : _opt.views;
+    auto const block = _pbrSystem.allocateViewBlock(*_allocator, _opt.extent, n);
+    std::vector<pbr::CameraData> cameras(n);
+    float const aspect = float(_opt.extent.width) / float(_opt.extent.height);
+    for (std::uint32_t v = 0; v < n; ++v) {
+      float const a = 6.283185307179586f * float(_opt.viewFirst + v) / float(total);
+      cameras[v] = pbr::makeCameraData({_opt.orbitRadius * std::cos(a), _opt.orbitHeight, _opt.orbitRadius * std::sin(a)}, {0.0f, 0.0f, 0.0f},
+                                       _opt.fov.value_or(Limits::startFov), aspect);
+    }
+    auto const timed = [&](bool lighting) {
+      auto const t0 = std::chrono::high_resolution_clock::now();
+      _pbrSystem.renderViews(cmd, _scene, cameras, block, lighting);
+      pbr::core::check(pbrcu_stream_synchronize(_stream), "sync");
+      return std::chrono::duration_cast<std::chrono::duration<double, std::milli>>(std::chrono::high_resolution_clock::now() - t0).count();
+    };
+    (void)timed(true);
+    double msGeometry = 1e300, msBoth = 1e300;
+    for (std::uint32_t rep = 0; rep < (_opt.frames < 1 ? 1u : _opt.frames); ++rep) {
+      msGeometry = std::min(msGeometry, timed(false));
+      msBoth = std::min(msBoth, timed(true));
+    }
+    std::uint64_t triangles = 0, draws = 0;
+    for (auto const& node : _scene.iterateAllNodes())
+      if (node.getMesh())
+        for (auto const& primitive : node.getMesh()->getPrimitives()) { triangles += primitive.indexCount / 3; ++draws; }
+    if (!_opt.outTimes.empty()) {
+      std::ofstream f(_opt.outTimes);
+      f << "{\"views\": " << n << ", \"view_first\": " << _opt.viewFirst << ", \"view_total\": " << total << ", \"width\": " << _opt.extent.width
+        << ", \"height\": " << _opt.extent.height << ", \"triangles_per_view\": " << triangles << ", \"draws\": " << draws << ", \"repeats\": "
+        << (_opt.frames < 1 ? 1u : _opt.frames) << ", \"ms_geometry\": " << msGeometry << ", \"ms_geometry_plus_shading\": " << msBoth << "}\n";
+    }
+    if (!_opt.dumpDir.empty()) {  // for the parity tests: first, middle and last view -- planes, frame, and the matrices they were drawn with
+      auto const w = _opt.extent.width, h = _opt.extent.height;
+      for (std::uint32_t const v : {0u, n / 2, n - 1}) {
+        auto const g = block.raw(v);
+        auto const dump = [&](char const* name, void const* src, std::size_t texel) {
+          std::vector<std::uint8_t> host(std::size_t(w) * h * texel);
+          pbr::core::check(pbrcu_memcpy_d2h(host.data(), src, host.size(), _stream), "download");
+          pbr::core::check(pbrcu_stream_synchronize(_stream), "sync");
+          std::ofstream(_opt.dumpDir + "/view" + std::to_string(v) + "_" + name, std::ios::binary).write(reinterpret_cast<char const*>(host.data()), std::streamsize(host.size()));
+        };
+        dump("pos.bin", g.positions, 8);
+        dump("nrm.bin", g.normals, 8);
+        dump("alb.bin", g.albedo, 8);
+        dump("depth.bin", g.depth, 4);
+        dump("hdr.bin", block.getFrame(v).data, 8);
+        auto const m = matricesOf(cameras[v]);
+        std::ofstream(_opt.dumpDir + "/view" + std::to_string(v) + "_matrices.bin", std::ios::binary).write(reinterpret_cast<char const*>(m.data()), std::streamsize(m.size() * 4));
+      }
+    }
+  }
+
 private:
   auto writeOutputs() -> void {
     auto const w = _opt.extent.width, h = _opt.extent.height;
@@ -203,22 +263,26 @@ private:
       dump("depth.bin", _gBuffer.getDepth().getImage(), 4);
       dump("hdr.bin", _hdrImage.getImage().getImage(), 8);
       dump("ldr.bin", _hdrImage.getOutputImage(), 4);
-      std::vector<float> m;
-      auto const cam = _scene.findCamera().value()->get();
-      m.insert(m.end(), reinterpret_cast<float const*>(&cam.view), reinterpret_cast<float const*>(&cam.view) + 16);
-      m.insert(m.end(), reinterpret_cast<float const*>(&cam.proj), reinterpret_cast<float const*>(&cam.proj) + 16);
-      m.insert(m.end(), {cam.position.x, cam.position.y, cam.position.z, 0.0f});
-      for (auto const& node : _scene.iterateAllNodes()) {
-        if (!node.getMesh()) continue;
-        auto const tr = node.getTransform();
-        auto const pc = pbr::makeModelPushConstant(tr.position, tr.rotation, tr.scale);
-        for (std::size_t p = 0; p < node.getMesh()->getPrimitives().size(); ++p) {
-          m.insert(m.end(), reinterpret_cast<float const*>(&pc.model), reinterpret_cast<float const*>(&pc.model) + 16);
-          m.insert(m.end(), reinterpret_cast<float const*>(&pc.normalModel), reinterpret_cast<float const*>(&pc.normalModel) + 12);
-        }
-      }
+      auto const m = matricesOf(_scene.findCamera().value()->get());
       std::ofstream(_opt.dumpDir + "/matrices.bin", std::ios::binary).write(reinterpret_cast<char const*>(m.data()), std::streamsize(m.size() * 4));
     }
+  }
+  // view, proj, eye (+ pad), then model (16) and normal model (12) of every draw in render() order
+  auto matricesOf(pbr::CameraData const& cam) -> std::vector<float> {
+    std::vector<float> m;
+    m.insert(m.end(), reinterpret_cast<float const*>(&cam.view), reinterpret_cast<float const*>(&cam.view) + 16);
+    m.insert(m.end(), reinterpret_cast<float const*>(&cam.proj), reinterpret_cast<float const*>(&cam.proj) + 16);
+    m.insert(m.end(), {cam.position.x, cam.position.y, cam.position.z, 0.0f});
+    for (auto const& node : _scene.iterateAllNodes()) {
+      if (!node.getMesh()) continue;
+      auto const tr = node.getTransform();
+      auto const pc = pbr::makeModelPushConstant(tr.position, tr.rotation, tr.scale);
+      for (std::size_t p = 0; p < node.getMesh()->getPrimitives().size(); ++p) {
+        m.insert(m.end(), reinterpret_cast<float const*>(&pc.model), reinterpret_cast<float const*>(&pc.model) + 16);
+        m.insert(m.end(), reinterpret_cast<float const*>(&pc.normalModel), reinterpret_cast<float const*>(&pc.normalModel) + 12);
+      }
+    }
+    return m;
   }
 };
 }  // namespace app

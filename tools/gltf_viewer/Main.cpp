@@ -4,6 +4,8 @@
 //   gltf_viewer <asset.glb|asset.gltf> [-vulkan-validation] [--size WxH] [--frames N] [--dt SECONDS]
 //               [--keys WASDQE] [--look DX,DY] [--scroll Y] [--position X,Y,Z] [--yaw R] [--pitch R] [--fov R]
 //               [--no-spin] [--ggx] [--out frame.png] [--hdr frame.pfm] [--times times.json] [--dump DIR]
+//               [--views N [--view-first K] [--view-total M] [--orbit RADIUS,HEIGHT]]   (CUDA addition: a block of orbit views of the
+//                scene through PbrRenderSystem::renderViews -- BASELINE configs[4] -- instead of the frame loop; --frames = timed repeats)
 // No arguments: exits 0 without doing anything, like the reference.
 #include "App.hpp"
 
@@ -67,10 +69,19 @@ auto main(int const argc, char const* const* const argv) -> int {
       else if (a == "--hdr") opt.outPfm = next();
       else if (a == "--times") opt.outTimes = next();
       else if (a == "--dump") opt.dumpDir = next();
+      else if (a == "--views") opt.views = std::uint32_t(std::stoul(next()));
+      else if (a == "--view-first") opt.viewFirst = std::uint32_t(std::stoul(next()));
+      else if (a == "--view-total") opt.viewTotal = std::uint32_t(std::stoul(next()));
+      else if (a == "--orbit") { auto const v = parseFloats(next(), 2, ','); opt.orbitRadius = float(v[0]); opt.orbitHeight = float(v[1]); }
       else throw std::runtime_error("unknown option " + std::string(a));
     }
     if (opt.extent.width == 0 || opt.extent.height == 0 || opt.frames == 0) throw std::runtime_error("--size and --frames must be positive");
+    bool const viewsMode = opt.views > 0;
     app::App app(std::move(opt));
+    if (viewsMode) {  // a block of orbit views through the batched passes (--frames = timed repeats, default 60: pass a small number)
+      app.runViews();
+      return 0;
+    }
     app.run();
     double sum = 0.0;
     for (auto const t : app.frameTimes()) sum += t;
