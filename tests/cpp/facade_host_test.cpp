@@ -7,6 +7,7 @@
 #include "pbr/MeshBuilder.hpp"
 #include "pbr/ModelPushConstant.hpp"
 #include "pbr/Scene.hpp"
+#include "pbr/ViewBlock.hpp"
 
 #include <cmath>
 #include <cstdio>
@@ -132,7 +133,28 @@ void uniformRoundTrips() {
 }
 }  // namespace
 
+void viewBlockLayout() {
+  HeapAllocator alloc;
+  pbr::ViewBlock const block {alloc, {.width = 20, .height = 12}, 5, true};
+  EXPECT(block.getViewCount() == 5 && block.isExtended() && block.pitch8() == 160 && block.pitch4() == 80);
+  EXPECT(block.viewStride8() == 160 * 12 && block.viewStride4() == 80 * 12 && block.frameStride() == block.viewStride8());
+  auto const g0 = block.raw(), g3 = block.raw(3);
+  EXPECT(g0.width == 20 && g0.height == 12 && g0.pitch8 == 160 && g0.pitch4 == 80);
+  EXPECT(static_cast<char*>(g3.positions) - static_cast<char*>(g0.positions) == std::ptrdiff_t(3 * block.viewStride8()));
+  EXPECT(static_cast<char*>(g3.emissive) - static_cast<char*>(g0.emissive) == std::ptrdiff_t(3 * block.viewStride8()));
+  EXPECT(reinterpret_cast<char*>(g3.depth) - reinterpret_cast<char*>(g0.depth) == std::ptrdiff_t(3 * block.viewStride4()));
+  EXPECT(static_cast<char*>(g3.orm) - static_cast<char*>(g0.orm) == std::ptrdiff_t(3 * block.viewStride4()));
+  EXPECT(static_cast<char*>(block.getFrame(4).data) - static_cast<char*>(block.getFrames()) == std::ptrdiff_t(4 * block.frameStride()) && block.getFrame(4).pitch == 160);
+  pbr::ViewBlock const plain {alloc, {.width = 4, .height = 4}, 2, false};
+  EXPECT(plain.raw(1).orm == nullptr && plain.raw(1).emissive == nullptr && plain.raw(1).albedo != nullptr);
+  bool threw = false;
+  try { pbr::ViewBlock bad {alloc, {.width = 4, .height = 4}, 0, false}; } catch (std::runtime_error const&) { threw = true; }
+  EXPECT(threw);
+  std::printf("ok viewBlockLayout\n");
+}
+
 int main() {
+  viewBlockLayout();
   sceneTraversalIsPostOrder();
   findCameraReturnsFirstInPostOrder();
   meshBuilderConcatenatesWithRunningOffsets();
