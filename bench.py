@@ -790,6 +790,13 @@ def strong_scaling_block(extra, scene, world):
                       ("ms_per_frame_multicast_gather", "8k_256_lights_sharded_fused_gather_multicast")):
         if key in c3:
             out[name] = entry(c3["ms_per_frame_unsharded_on_one_gpu"], c3[key], "this run (same frame unsharded on this GPU)")
+    # BASELINE configs[4] as written: the 256 views rasterised and shaded (mesh generator's buffers / the .glb through the viewer)
+    geo = extra.get("geometry_pass_1080p", {})
+    for key, name in (("config4_256_views_scene", "256_views_1080p_rasterised_and_shaded"), ("config4_256_views_gltf", "256_views_1080p_gltf_rasterised_and_shaded")):
+        tn = geo.get(key, {}).get("ms_geometry_plus_shading_all_views")
+        if tn:
+            t1 = tn if world == 1 else cached.get("geometry_pass_1080p", {}).get(key, {}).get("ms_geometry_plus_shading_all_views")
+            out[name] = entry(t1, tn, "this run" if world == 1 else "profiles/r02_bench_n1.json")
     for key, name in (("ms_prefilter_and_gather", "prefilter_sharded_nccl_gather"), ("ms_prefilter_fused_gather", "prefilter_sharded_fused_gather")):
         if key in pf and world > 1:
             out[name] = entry(scene.ibl_ms["prefilter_ggx_prepared"], pf[key], "this run (ibl_precompute_ms.prefilter_ggx_prepared)")

@@ -11,6 +11,12 @@ python bench.py > $O/bench_n1.json 2> $O/bench_n1.err; echo "bench n1 exit $?"
 CMD="python bench.py --steps 5 --warmup 3 --no-cpu --mg-host none"
 $CMD > $O/plain_launches.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/launches.csv $CMD > $O/ncu_launches.log 2>&1; echo "launch list exit $?"
+# K10 (one pass of the bench scene through pbrcu_geometry_pass; scratch/prof_k10.py)
+python scratch/prof_k10.py > $O/plain_k10.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:raster_ -s 7 -c 7 -o $O/k10 python scratch/prof_k10.py > $O/ncu_k10.log 2>&1; echo "ncu k10 exit $?"
+[ -f $O/k10.ncu-rep ] && ncu -i $O/k10.ncu-rep --page raw --csv > $O/k10.raw.csv 2>/dev/null
+rm -f $O/k10.ncu-rep
+if [ "${PROFILES_LIGHT:-0}" = "1" ]; then ls -la $O; exit 0; fi   # the K3 / K7 / misc captures only change when those kernels do
 CMD2="python bench.py --steps 3 --warmup 3 --no-cpu --no-extra"
 $CMD2 > $O/plain_k3.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:shade_ggx_cl_kernel -s 3 -c 2 -o $O/k3_cl $CMD2 > $O/ncu_k3.log 2>&1; echo "ncu k3 exit $?"

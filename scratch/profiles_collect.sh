@@ -10,6 +10,11 @@ python scratch/launch_summary.py $O/launches.csv > $P/r02_launches_summary.txt
 for rep in k3_cl k3_cl_gather; do
   [ -f $O/$rep.raw.csv ] && python scratch/summarize_ncu.py $O/$rep.raw.csv $O/$rep.src.csv > $P/r02_${rep}_ncu.txt
 done
+if [ -f $O/k10.raw.csv ]; then
+  { echo "# ncu --set full --clock-control none --import-source on -k regex:raster_ -s 7 -c 7 python scratch/prof_k10.py   (scratch/make_profiles.sh)";
+    echo "# (second single-view geometry pass of the bench scene: 589,828 triangles in 65 draws at 1920x1080; final kernels of round 2; summary by scratch/summarize_ncu.py)";
+    python scratch/summarize_ncu.py $O/k10.raw.csv "" 30; } > $P/r02_k10_ncu.txt
+fi
 for rep in k7 misc; do
   [ -f $O/$rep.raw.csv ] && python scratch/summarize_ncu.py $O/$rep.raw.csv "" 30 > $P/r02_${rep}_ncu.txt
 done
