@@ -26,7 +26,8 @@ $CMD2 > $O/plain_k7.log 2>&1 &&
 ncu --set full --clock-control none -k regex:conv_kernel -c 14 -o $O/k7 $CMD2 > $O/ncu_k7.log 2>&1; echo "ncu k7 exit $?"
 CMD3="python bench.py --steps 3 --warmup 3 --no-cpu --mg-host none"
 $CMD3 > $O/plain_misc.log 2>&1 &&
-ncu --set full --clock-control none -k regex:'cluster_lights_kernel|shade_ggx_kernel|equirect_to_cube_kernel|cube_mip_kernel|brdf_lut_kernel' -c 24 -o $O/misc $CMD3 > $O/ncu_misc.log 2>&1; echo "ncu misc exit $?"
+ncu --set full --clock-control none -k regex:'equirect_to_cube_kernel|cube_mip_kernel' -c 24 -o $O/misc $CMD3 > $O/ncu_misc.log 2>&1; echo "ncu misc exit $?"
+bash scratch/prof_misc2.sh   # K3c, the tiled K3 kernel on the 8K frame, K8 -> misc2.raw.csv (profiles/r02_k3_tiled_8k_ncu.txt)
 # the reports are too large to travel (64 MiB limit on gpurun_out/): export what profiles_collect.sh reads, keep only the K3 reports
 for rep in k3_cl k3_cl_gather k7 misc; do
   [ -f $O/$rep.ncu-rep ] || continue
