@@ -590,9 +590,32 @@ def gltf_views_bench(torch, dist, world, rank):
     viewer = ROOT / "tools" / "gltf_viewer" / "build" / "gltf_viewer"
     if not viewer.exists():
         return {"unavailable": "tools/gltf_viewer/build/gltf_viewer is not built (python -c 'import __graft_entry__ as g; g.build()')"}
+    from pbr_b200.partition import view_block
+    NV, W, H = 256, 1920, 1080
+    v0, v1 = view_block(NV, world, rank)
+    out = None
+    with tempfile.TemporaryDirectory() as tmp:
+        path = Path(tmp) / "scene.glb"
+        write_views_glb(path)
+        glb_bytes = path.stat().st_size
+        if v1 > v0:
+            env = dict(os.environ)
+            local = int(os.environ.get("LOCAL_RANK", "0"))
+            visible = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d]
+            env["CUDA_VISIBLE_DEVICES"] = visible[local] if local < len(visible) else str(local)
+            r = subprocess.run([str(viewer), str(path), "--size", f"{W}x{H}", "--ggx", "--views", str(v1 - v0), "--view-first", str(v0), "--view-total", str(NV), "--frames", "3",
+                                "--orbit", "12,-2", "--times", str(Path(tmp) / "t.json")], capture_output=True, text=True, env=env, timeout=600)
+            if r.returncode != 0:
+                return {"unavailable": f"gltf_viewer failed: {r.stderr.strip()[-300:]}"}
+            out = json.loads((Path(tmp) / "t.json").read_text())
+    return _gltf_views_entry(torch, dist, world, out, NV, W, H, v1 - v0, glb_bytes)
+
+
+def write_views_glb(path):
+    """The 65-draw scene of geometry_bench as a .glb: 64 textured spheres (one set of accessors, 64 materials and node transforms) and a ground
+    plane that crosses the near plane; 589,828 triangles."""
     sys.path.insert(0, str(ROOT / "tests"))  # the glTF writer is test tooling (not the checker)
     from gltfwriter import Builder
-    from pbr_b200.partition import view_block
     from pbr_b200.synth import checker_texture, mesh_vertex, uv_sphere
     rng = np.random.default_rng(7)
     b = Builder()
@@ -613,23 +636,10 @@ def gltf_views_bench(torch, dist, world, rank):
     mg = b.material("ground", (0.8, 0.8, 0.8, 1.0), ct, flat, metallic=0.0, roughness=0.6)
     nodes.append(b.node("ground", mesh=b.mesh("ground", [b.primitive(quad, qi, mg)])))
     b.scene(nodes)
-    NV, W, H = 256, 1920, 1080
-    v0, v1 = view_block(NV, world, rank)
-    out = None
-    with tempfile.TemporaryDirectory() as tmp:
-        path = Path(tmp) / "scene.glb"
-        b.write_glb(path)
-        glb_bytes = path.stat().st_size
-        if v1 > v0:
-            env = dict(os.environ)
-            local = int(os.environ.get("LOCAL_RANK", "0"))
-            visible = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d]
-            env["CUDA_VISIBLE_DEVICES"] = visible[local] if local < len(visible) else str(local)
-            r = subprocess.run([str(viewer), str(path), "--size", f"{W}x{H}", "--ggx", "--views", str(v1 - v0), "--view-first", str(v0), "--view-total", str(NV), "--frames", "3",
-                                "--orbit", "12,-2", "--times", str(Path(tmp) / "t.json")], capture_output=True, text=True, env=env, timeout=600)
-            if r.returncode != 0:
-                return {"unavailable": f"gltf_viewer failed: {r.stderr.strip()[-300:]}"}
-            out = json.loads((Path(tmp) / "t.json").read_text())
+    b.write_glb(Path(path))
+
+
+def _gltf_views_entry(torch, dist, world, out, NV, W, H, nv, glb_bytes):
     ms = torch.tensor([out["ms_geometry"] if out else 0.0, out["ms_geometry_plus_shading"] if out else 0.0], dtype=torch.float64, device="cuda")
     if dist is not None and world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -637,8 +647,8 @@ def gltf_views_bench(torch, dist, world, rank):
     if dist is not None and world > 1:
         dist.all_reduce(tri, op=dist.ReduceOp.MAX)
     ms_geo, ms_both = float(ms[0]), float(ms[1])
-    return {"views": NV, "views_per_rank": v1 - v0, "ms_geometry_all_views": round(ms_geo, 3), "ms_geometry_plus_shading_all_views": round(ms_both, 3),
-            "us_geometry_per_view": round(ms_geo * 1e3 / max(v1 - v0, 1), 2), "mpix_s": round(NV * W * H / (ms_both * 1e-3) / 1e6, 1),
+    return {"views": NV, "views_per_rank": nv, "ms_geometry_all_views": round(ms_geo, 3), "ms_geometry_plus_shading_all_views": round(ms_both, 3),
+            "us_geometry_per_view": round(ms_geo * 1e3 / max(nv, 1), 2), "mpix_s": round(NV * W * H / (ms_both * 1e-3) / 1e6, 1),
             "triangles_per_view": int(tri[0]), "draws": int(tri[1]), "glb_bytes": glb_bytes, "scaling": "strong (view blocks, no exchange)",
             "timing": "host clock around enqueue + stream synchronise inside the viewer process, min of 3 repeats after a warm-up, max over ranks",
             "what": "tests/gltfwriter.py scene (.glb: 64 textured spheres + a ground plane that crosses the near plane) -> pbr::gltf::Loader -> Asset::loadScene -> "

@@ -191,3 +191,21 @@ def test_hostile_assets_are_rejected(tool, tmp_path):
 
     rc, _, err = variant("cycle.gltf", cycle)
     assert rc == 2 and ("cycle" in err or "more than one parent" in err), err
+
+
+def test_bench_views_scene_imports(tool, tmp_path):
+    """The .glb bench.py writes for `config4_256_views_gltf` (64 spheres sharing one set of accessors under 64 materials and node
+    transforms + the ground plane) goes through the import path: 65 mesh nodes, one primitive each, 589,828 triangles."""
+    import sys
+    sys.path.insert(0, str(ROOT))
+    import bench
+    path = tmp_path / "views.glb"
+    bench.write_views_glb(path)
+    rc, got, err = run(tool, path)
+    assert rc == 0, err
+    assert got[0].split()[-1] == "65"
+    prims = [line.split() for line in got if line.strip().startswith("prim ")]
+    assert len(prims) == 65
+    assert sum(int(p[p.index("indices") + 1]) // 3 for p in prims) == 589828
+    assert len({p[p.index("vhash") + 1] for p in prims}) == 2  # the spheres share their vertex data, the ground has its own
+    assert len({line.split()[1] for line in got if line.strip().startswith("material ")}) == 65
