@@ -26,8 +26,9 @@
  *
  * Ordering rules.  (1) The allocation calls (pbrcu_gbuffer_alloc, pbrcu_image_alloc) return with their
  * clears COMPLETE, so the memory may be used on any stream at once.  (2) One stream at a time per
- * pbrcu_ctx for the entry points that use scratch memory owned by the context: pbrcu_geometry_pass
- * (visibility buffer, vertex cache), pbrcu_ibl_prefilter_ggx / pbrcu_ibl_irradiance (the texture copy of
+ * pbrcu_ctx for the entry points that use scratch memory owned by the context: pbrcu_geometry_pass and
+ * pbrcu_geometry_pass_batched (visibility buffer -- each pass leaves it empty for the next one, which relies on
+ * that --, vertex cache, draw tables), pbrcu_ibl_prefilter_ggx / pbrcu_ibl_irradiance (the texture copy of
  * the source chain), the *_batched entries (camera table) and the *_host entries (staging planes).  Calls
  * of these on DIFFERENT streams of one context must be ordered by the caller (an event), or use one
  * context per stream -- contexts are cheap (no device memory until a scratch is first needed).
